@@ -1,0 +1,13 @@
+"""diceoptim_b200 — B200-native batched acquisition engine behind DiceOptim's function API.
+
+The package holds only the hot path of SURVEY.md section 8: csrc/ (CUDA kernels + C ABI,
+include/dk_b200.h), the ctypes binding, and the host-side mirror of the R interface
+(EI, EI_grad, kriging_quantile[_grad], screen_EI / max_crit, ...).  Model fitting stays in
+DiceKriging; ``synth`` only builds km objects with FIXED hyper-parameters for tests and bench.
+"""
+from .km import KM, Covariance, DeviceModel  # noqa: F401
+from .api import (EI, EI_grad, kriging_quantile, kriging_quantile_grad, max_crit, predict,  # noqa: F401
+                  screen_EI)
+
+__all__ = ["KM", "Covariance", "DeviceModel", "EI", "EI_grad", "kriging_quantile", "kriging_quantile_grad",
+           "max_crit", "predict", "screen_EI"]

@@ -1,0 +1,175 @@
+"""DiceOptim's acquisition functions with their reference signatures, evaluated by the CUDA engine.
+
+Each function mirrors the R function of the same name (argument names, defaults, error
+behaviour); matrices of candidates are evaluated in one fused kernel launch.  Differences from
+the reference are limited to what a GPU batch cannot give back: ``envir`` receives the
+per-candidate scalars (xcr, xcr.prob, xcr.dens, kriging.sd) but not the n x N matrices ``c`` and
+``Tinv.c`` (SURVEY 8(b) "envir contract").
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+from scipy.special import ndtr, ndtri
+
+from . import _lib
+from .km import KM, TYPE_IDS
+
+_INV_SQRT_2PI = 0.3989422804014326779399460599343818684758586311649
+
+
+def _as_candidates(x, d):
+    """R/EI.R:93-108: vector -> 1 x d, matrix -> N x d; column-major float64 for the C ABI."""
+    x = np.asarray(x, dtype=np.float64)
+    if x.ndim <= 1:
+        x = x.reshape(1, -1)
+    if x.ndim != 2 or x.shape[1] != d:
+        raise ValueError("x does not have the right size")
+    return np.asfortranarray(x)
+
+
+def _type_id(type):
+    if type not in TYPE_IDS:
+        raise ValueError(f"type must be 'UK' or 'SK', got {type!r}")
+    return TYPE_IDS[type]
+
+
+def _vp(a):
+    return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+def _default_plugin(model: KM, minimization: bool) -> float:
+    # R/EI.R:82-88
+    return float(np.min(model.y)) if minimization else float(-np.max(model.y))
+
+
+def predict(model: KM, newdata, type="UK", device=0):
+    """predict.km(..., light.return=TRUE): dict(mean=, sd=) (DiceKriging; call site R/EI.R:115)."""
+    x = _as_candidates(newdata, model.d)
+    N = x.shape[0]
+    mean = np.empty(N); sd = np.empty(N)
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_predict(h.ptr, _vp(x), N, _type_id(type), _vp(mean), _vp(sd)), "dk_predict")
+    return {"mean": mean, "sd": sd}
+
+
+def EI(x, model: KM, plugin=None, type="UK", minimization=True, envir=None, proxy=False, device=0):
+    """Expected improvement, R/EI.R:80-145.  Returns one value per row of ``x``."""
+    if plugin is None:
+        plugin = _default_plugin(model, minimization)
+    x = _as_candidates(x, model.d)
+    N = x.shape[0]
+    ei = np.empty(N)
+    want = envir is not None
+    mean = np.empty(N) if want else None
+    sd = np.empty(N) if want else None
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_ei(h.ptr, _vp(x), N, float(plugin), _type_id(type), int(bool(minimization)),
+                                 int(bool(proxy)), _vp(ei), _vp(mean), _vp(sd)), "dk_ei")
+    if want:
+        km = mean if minimization else -mean
+        if proxy:
+            xcr = prob = dens = None
+        else:
+            with np.errstate(divide="ignore", invalid="ignore"):
+                xcr = (plugin - km) / sd
+            prob = ndtr(xcr); dens = _INV_SQRT_2PI * np.exp(-0.5 * xcr * xcr)
+        envir.update({"xcr": xcr, "xcr.prob": prob, "xcr.dens": dens, "kriging.sd": sd,
+                      "kriging.mean": mean, "c": None, "Tinv.c": None})
+    return ei
+
+
+def EI_grad(x, model: KM, plugin=None, type="UK", minimization=True, envir=None, proxy=False, device=0):
+    """Analytic gradient of EI, R/EI.grad.R:97-186.  A length-d ``x`` gives a length-d gradient (the
+    reference's contract); an N x d matrix gives the N x d matrix of per-row gradients."""
+    if plugin is None:
+        plugin = _default_plugin(model, minimization)
+    single = np.asarray(x).ndim <= 1
+    x = _as_candidates(x, model.d)
+    N = x.shape[0]
+    grad = np.empty((N, model.d), order="F")
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_ei_grad(h.ptr, _vp(x), N, float(plugin), _type_id(type), int(bool(minimization)),
+                                      int(bool(proxy)), _vp(grad), None), "dk_ei_grad")
+    return grad[0].copy() if single else grad
+
+
+def kriging_quantile(x, model: KM, beta=0.1, type="UK", envir=None, device=0):
+    """Kriging quantile mk + qnorm(beta) sk, R/kriging.quantile.R:92-115."""
+    x = _as_candidates(x, model.d)
+    N = x.shape[0]
+    q = np.empty(N)
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_quantile(h.ptr, _vp(x), N, float(ndtri(beta)), _type_id(type), _vp(q), None),
+               "dk_quantile")
+    return q
+
+
+def kriging_quantile_grad(x, model: KM, beta=0.1, type="UK", envir=None, device=0):
+    """Gradient of the kriging quantile, R/kriging.quantile.grad.R:83-138 (rows batched like EI_grad)."""
+    single = np.asarray(x).ndim <= 1
+    x = _as_candidates(x, model.d)
+    N = x.shape[0]
+    q = np.empty(N)
+    grad = np.empty((N, model.d), order="F")
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_quantile(h.ptr, _vp(x), N, float(ndtri(beta)), _type_id(type), _vp(q), _vp(grad)),
+               "dk_quantile")
+    return grad[0].copy() if single else grad
+
+
+def screen_EI(x, model: KM, plugin=None, type="UK", minimization=True, proxy=False, k=1, device=0):
+    """The batched screen of R/max_crit.R:104-110 on the device: EI over the rows of ``x`` then
+    which.max (first maximal index, NaN skipped).  Returns (indices[k], values[k]), 0-based."""
+    if plugin is None:
+        plugin = _default_plugin(model, minimization)
+    x = _as_candidates(x, model.d)
+    N = x.shape[0]
+    idx = np.empty(k, dtype=np.int64); val = np.empty(k)
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_screen_ei(h.ptr, _vp(x), 0, N, float(plugin), _type_id(type), int(bool(minimization)),
+                                        int(bool(proxy)), int(k), _vp(idx), _vp(val), None), "dk_screen_ei")
+    return idx, val
+
+
+def max_crit(model: KM, type="UK", lower=None, upper=None, minimization=True, control=None, proxy=False,
+             trcontrol=None, n_cores=1, seed=None, device=0):
+    """R/max_crit.R:64-130: per restart, N uniform candidates -> EI screen on the GPU -> which.max ->
+    optional L-BFGS-B polish with EI / EI.grad; best restart wins.  ``n_cores`` must be 1: the
+    reference forks with mclapply and CUDA contexts do not survive fork()."""
+    from scipy.optimize import minimize
+    if n_cores != 1:
+        raise ValueError("n.cores must be 1 with the GPU engine (restarts are batched in-process)")
+    control = dict(control or {}); trcontrol = dict(trcontrol or {})
+    d = model.d
+    lower = np.zeros(d) if lower is None else np.asarray(lower, float)
+    upper = np.ones(d) if upper is None else np.asarray(upper, float)
+    trcontrol.setdefault("sigma", (upper - lower) / 2)
+    trcontrol.setdefault("x0", model.X[int(np.argmin(model.y))])
+    trcontrol.setdefault("crit", "EI")
+    trcontrol.setdefault("inTR", False)
+    if trcontrol["inTR"]:                                   # R/max_crit.R:76-82
+        lower = np.maximum(trcontrol["x0"] - trcontrol["sigma"], lower)
+        upper = np.minimum(trcontrol["x0"] + trcontrol["sigma"], upper)
+        if trcontrol["crit"] != "EI":
+            proxy = True
+    restarts = control.get("restarts", min(10, d))
+    bfgs = control.get("BFGS", True)
+    N = int(control.get("n.ei", min(2000, 500 * d)))
+    plugin = _default_plugin(model, minimization)
+    rng = np.random.default_rng(seed)
+    best = None
+    for _ in range(restarts):
+        x = lower + rng.random((N, d)) * (upper - lower)
+        idx, val = screen_EI(x, model, plugin=None, type=type, minimization=minimization, proxy=proxy, device=device)
+        par, value = x[idx[0]], val[0]
+        if bfgs:
+            # the reference polishes with minimization = TRUE whatever the caller asked (R/max_crit.R:119)
+            res = minimize(lambda t: -EI(t, model, plugin=plugin, type=type, minimization=True, proxy=proxy, device=device)[0],
+                           par, jac=lambda t: -EI_grad(t, model, plugin=plugin, type=type, minimization=True, proxy=proxy, device=device),
+                           method="L-BFGS-B", bounds=list(zip(lower, upper)), options={"maxiter": 100})
+            par, value = res.x, -res.fun
+        if best is None or value > best[1]:
+            best = (np.asarray(par, float), float(value))
+    return {"par": best[0], "value": best[1]}

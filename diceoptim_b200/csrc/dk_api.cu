@@ -1,0 +1,584 @@
+// dk_api.cu — host side of the C ABI (include/dk_b200.h): model upload + pre-tiling, launches.
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "dk_kernels.cuh"
+#include "dk_grad.cuh"
+#include "dk_reduce.cuh"
+
+namespace dk {
+
+std::string& last_error() {
+  static thread_local std::string e;
+  return e;
+}
+int fail(int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  last_error() = buf;
+  return code;
+}
+
+namespace {
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    int cur = -1;
+    cudaGetDevice(&cur);
+    if (prev >= 0 && cur != prev) cudaSetDevice(prev);
+  }
+};
+
+// Lower-triangular augmented factor  L_aug = [[T', 0, 0], [[z M]', I, 0], [0, 0, I]]  (n_pad square).
+struct AugFactor {
+  const double *T, *z, *M;
+  int n, p, n_aug;
+  double operator()(int i, int j) const {  // j <= i
+    if (i < n) return T[(size_t)j + (size_t)i * n];
+    if (i < n_aug) {
+      const int r = i - n;
+      if (j < n) return r == 0 ? z[j] : M[(size_t)j + (size_t)(r - 1) * n];
+    }
+    return i == j ? 1.0 : 0.0;
+  }
+};
+// Flipped upper factor for the backward solve  T w = v :  Lb[i'][j'] = T[n-1-i'][n-1-j'] (lower), identity pad.
+struct FlipFactor {
+  const double* T;
+  int n;
+  double operator()(int i, int j) const {  // j <= i
+    if (i < n) return T[(size_t)(n - 1 - i) + (size_t)(n - 1 - j) * n];
+    return i == j ? 1.0 : 0.0;
+  }
+};
+
+// Build the fragment-ordered tile array of a lower-triangular factor: for each block row I the
+// 8 I tiles of -L_IJ (J < I, k-chunks of 16 columns) followed by the 8 tiles of inv(L_II).
+// The 128 x 128 diagonal inverses are formed in long double and rounded once.
+template <class Factor>
+void build_tiles(const Factor& L, int nblk, std::vector<double>& tiles) {
+  tiles.assign(tile_base(nblk) * A_TILE, 0.0);
+  std::vector<long double> inv((size_t)BM * BM);
+#pragma omp parallel for schedule(dynamic) firstprivate(inv)
+  for (int I = 0; I < nblk; I++) {
+    double* base = tiles.data() + tile_base(I) * A_TILE;
+    const int r0 = I * BM;
+    for (int kc = 0; kc < CHUNKS_PER_BLOCK * I; kc++) {
+      double* t = base + (size_t)kc * A_TILE;
+      for (int r = 0; r < BM; r++)
+        for (int k = 0; k < KC; k++) t[a_tile_index(r, k)] = -L(r0 + r, kc * KC + k);
+    }
+    // inverse of the diagonal block by forward substitution, column by column
+    std::fill(inv.begin(), inv.end(), 0.0L);
+    for (int j = 0; j < BM; j++) {
+      inv[(size_t)j * BM + j] = 1.0L / (long double)L(r0 + j, r0 + j);
+      for (int i = j + 1; i < BM; i++) {
+        long double s = 0.0L;
+        for (int k = j; k < i; k++) s += (long double)L(r0 + i, r0 + k) * inv[(size_t)k * BM + j];
+        inv[(size_t)i * BM + j] = -s / (long double)L(r0 + i, r0 + i);
+      }
+    }
+    double* dt = base + (size_t)CHUNKS_PER_BLOCK * I * A_TILE;
+    for (int kc = 0; kc < CHUNKS_PER_BLOCK; kc++)
+      for (int r = 0; r < BM; r++)
+        for (int k = 0; k < KC; k++)
+          dt[(size_t)kc * A_TILE + a_tile_index(r, k)] = (double)inv[(size_t)r * BM + kc * KC + k];
+  }
+}
+
+template <class T>
+int dev_alloc(dk_model* m, T** ptr, size_t count) {
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, count * sizeof(T));
+  if (e != cudaSuccess)
+    return fail(DK_ERR_NOMEM, "cudaMalloc of %zu bytes failed: %s", count * sizeof(T), cudaGetErrorString(e));
+  m->device_bytes += count * sizeof(T);
+  *ptr = static_cast<T*>(p);
+  return DK_OK;
+}
+
+int ensure_io(dk_model* m, size_t doubles) {
+  if (m->io_doubles >= doubles) return DK_OK;
+  if (m->d_io) {
+    cudaFree(m->d_io);
+    m->device_bytes -= m->io_doubles * 8;
+    m->d_io = nullptr;
+    m->io_doubles = 0;
+  }
+  int rc = dev_alloc(m, &m->d_io, doubles);
+  if (rc) return rc;
+  m->io_doubles = doubles;
+  return DK_OK;
+}
+
+int ensure_red(dk_model* m, size_t bytes) {
+  if (m->red_bytes >= bytes) return DK_OK;
+  if (m->d_red) {
+    cudaFree(m->d_red);
+    m->device_bytes -= m->red_bytes;
+    m->d_red = nullptr;
+  }
+  unsigned char* p = nullptr;
+  int rc = dev_alloc(m, &p, bytes);
+  if (rc) return rc;
+  m->d_red = p;
+  m->red_bytes = bytes;
+  return DK_OK;
+}
+
+int ensure_bwd(dk_model* m) {
+  if (m->d_tiles_bwd) return DK_OK;
+  std::vector<double> tiles;
+  try {
+    FlipFactor L{m->h_T, m->n};
+    build_tiles(L, m->dm.nblk_b, tiles);
+  } catch (const std::bad_alloc&) {
+    return fail(DK_ERR_NOMEM, "host allocation for the backward tiles failed");
+  }
+  int rc = dev_alloc(m, &m->d_tiles_bwd, tiles.size());
+  if (rc) return rc;
+  DK_CUDA_TRY(cudaMemcpy(m->d_tiles_bwd, tiles.data(), tiles.size() * 8, cudaMemcpyHostToDevice));
+  rc = dev_alloc(m, &m->d_wscratch, (size_t)m->grid * (m->scratch_doubles_per_cta + COEF_DOUBLES));
+  if (rc) return rc;
+  m->dm.tiles_bwd = m->d_tiles_bwd;
+  return DK_OK;
+}
+
+bool g_attr_done[64] = {};
+int set_kernel_attrs(int device) {
+  if (device < 64 && g_attr_done[device]) return DK_OK;
+  DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+  DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+  if (device < 64) g_attr_done[device] = true;
+  return DK_OK;
+}
+
+int check_call(const dk_model* m, const void* x, int64_t N) {
+  if (!m) return fail(DK_ERR_ARG, "model handle is NULL");
+  if (!x) return fail(DK_ERR_ARG, "x is NULL");
+  if (N < 0) return fail(DK_ERR_ARG, "N = %lld is negative", (long long)N);
+  return DK_OK;
+}
+
+// forward pass over device-resident candidates
+int launch_predict(dk_model* m, const CritParams& P, const double* d_x, int64_t N, double* d_main, double* d_mean,
+                   double* d_sd, cudaStream_t st) {
+  if (N == 0) return DK_OK;
+  const int64_t ntiles = (N + BN - 1) / BN;
+  const int grid = (int)std::min<int64_t>(ntiles, m->grid);
+  k_predict_fused<<<grid, NT, SM_TOTAL, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->scratch_doubles_per_cta,
+                                               d_main, d_mean, d_sd);
+  m->launches++;
+  DK_CUDA_TRY(cudaGetLastError());
+  return DK_OK;
+}
+
+int launch_grad(dk_model* m, const CritParams& P, const double* d_x, int64_t N, double* d_grad, double* d_main,
+                cudaStream_t st) {
+  if (N == 0) return DK_OK;
+  int rc = ensure_bwd(m);
+  if (rc) return rc;
+  const int64_t ntiles = (N + BN - 1) / BN;
+  const int grid = (int)std::min<int64_t>(ntiles, m->grid);
+  k_grad_fused<<<grid, NT, SM_TOTAL, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->d_wscratch,
+                                            m->scratch_doubles_per_cta, d_grad, d_main);
+  m->launches++;
+  DK_CUDA_TRY(cudaGetLastError());
+  return DK_OK;
+}
+
+}  // namespace
+}  // namespace dk
+
+using namespace dk;
+
+extern "C" {
+
+const char* dk_last_error(void) { return dk::last_error().c_str(); }
+const char* dk_version(void) { return "dk_b200 0.1 sm_100a (FP64 DMMA m8n8k4 blocked TRSM)"; }
+
+int dk_model_create(const dk_model_desc* D, dk_model** out) {
+  if (!D || !out) return fail(DK_ERR_ARG, "dk_model_create: NULL argument");
+  *out = nullptr;
+  if (D->n < 1 || D->d < 1 || D->p < 1) return fail(DK_ERR_ARG, "bad dimensions n=%d d=%d p=%d", D->n, D->d, D->p);
+  if (D->d > DK_MAX_D) return fail(DK_ERR_ARG, "d=%d exceeds DK_MAX_D=%d", D->d, DK_MAX_D);
+  if (D->p > DK_MAX_P) return fail(DK_ERR_ARG, "p=%d exceeds DK_MAX_P=%d", D->p, DK_MAX_P);
+  if (D->kernel < DK_GAUSS || D->kernel > DK_POWEXP)
+    return fail(DK_ERR_ARG, "unsupported covariance kernel id %d (covTensorProduct gauss/exp/matern3_2/matern5_2/powexp only)", D->kernel);
+  if (D->trend != DK_TREND_CONST && D->trend != DK_TREND_LINEAR)
+    return fail(DK_ERR_ARG, "unsupported trend id %d (~1 and ~. only)", D->trend);
+  if (D->trend == DK_TREND_CONST && D->p != 1) return fail(DK_ERR_ARG, "trend ~1 needs p=1, got %d", D->p);
+  if (D->trend == DK_TREND_LINEAR && D->p != D->d + 1) return fail(DK_ERR_ARG, "trend ~. needs p=d+1, got p=%d d=%d", D->p, D->d);
+  if (!D->theta || !D->T || !D->z || !D->M || !D->X || !D->beta) return fail(DK_ERR_ARG, "a required model array is NULL");
+  if (D->kernel == DK_POWEXP && !D->shape) return fail(DK_ERR_ARG, "powexp needs shape.val");
+  if (!(D->sd2 > 0)) return fail(DK_ERR_ARG, "sd2 must be positive");
+  for (int k = 0; k < D->d; k++)
+    if (!(D->theta[k] > 0)) return fail(DK_ERR_ARG, "range.val[%d] must be positive", k);
+  for (int i = 0; i < D->n; i++)
+    if (!(D->T[(size_t)i + (size_t)i * D->n] > 0)) return fail(DK_ERR_ARG, "T[%d,%d] is not positive: not a Cholesky factor", i, i);
+
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(DK_ERR_UNSUPPORTED, "no CUDA device visible");
+  if (D->device < 0 || D->device >= ndev) return fail(DK_ERR_ARG, "device %d out of range (%d visible)", D->device, ndev);
+  cudaDeviceProp prop;
+  DK_CUDA_TRY(cudaGetDeviceProperties(&prop, D->device));
+  if (prop.major != 10) return fail(DK_ERR_UNSUPPORTED, "device %d is sm_%d%d; this library is built for sm_100a only", D->device, prop.major, prop.minor);
+  DeviceGuard guard(D->device);
+  int rc = set_kernel_attrs(D->device);
+  if (rc) return rc;
+
+  dk_model* m = new (std::nothrow) dk_model();
+  if (!m) return fail(DK_ERR_NOMEM, "host allocation failed");
+  m->device = D->device;
+  m->num_sms = prop.multiProcessorCount;
+  const int n = D->n, d = D->d, p = D->p;
+  m->n = n; m->d = d; m->p = p;
+  DevModel& dm = m->dm;
+  dm.n = n; dm.d = d; dm.p = p;
+  dm.n_aug = n + p + 1;
+  dm.nblk = (dm.n_aug + BM - 1) / BM;
+  dm.n_pad = dm.nblk * BM;
+  dm.nblk_b = (n + BM - 1) / BM;
+  dm.kernel = D->kernel; dm.trend = D->trend; dm.nugget_flag = D->nugget_flag ? 1 : 0;
+  dm.sd2 = D->sd2; dm.nugget = D->nugget;
+  dm.total_sd2 = D->sd2 + (D->nugget_flag ? D->nugget : 0.0);
+  for (int k = 0; k < DK_MAX_D; k++) { dm.w[k] = 0; dm.shape[k] = 1; dm.theta[k] = 1; }
+  for (int k = 0; k < d; k++) {
+    const double th = D->theta[k];
+    dm.theta[k] = th;
+    dm.w[k] = D->kernel == DK_MATERN3_2 ? std::sqrt(3.0) / th : D->kernel == DK_MATERN5_2 ? std::sqrt(5.0) / th : 1.0 / th;
+    if (D->shape) dm.shape[k] = D->shape[k];
+  }
+
+  auto bail = [&](int code) { dk_model_destroy(m); return code; };
+  try {
+    // ---- tiles of the augmented factor ----
+    std::vector<double> tiles;
+    AugFactor L{D->T, D->z, D->M, n, p, dm.n_aug};
+    build_tiles(L, dm.nblk, tiles);
+    if ((rc = dev_alloc(m, &m->d_tiles_fwd, tiles.size()))) return bail(rc);
+    if (cudaMemcpy(m->d_tiles_fwd, tiles.data(), tiles.size() * 8, cudaMemcpyHostToDevice) != cudaSuccess)
+      return bail(fail(DK_ERR_CUDA, "upload of the factor tiles failed: %s", cudaGetErrorString(cudaGetLastError())));
+    dm.tiles_fwd = m->d_tiles_fwd;
+    tiles.clear(); tiles.shrink_to_fit();
+
+    // ---- design, row-major, zero padded ----
+    std::vector<double> Xrm((size_t)dm.n_pad * d, 0.0);
+    for (int i = 0; i < n; i++)
+      for (int k = 0; k < d; k++) Xrm[(size_t)i * d + k] = D->X[(size_t)i + (size_t)k * n];
+    if ((rc = dev_alloc(m, &m->d_Xrm, Xrm.size()))) return bail(rc);
+    cudaMemcpy(m->d_Xrm, Xrm.data(), Xrm.size() * 8, cudaMemcpyHostToDevice);
+    dm.Xrm = m->d_Xrm;
+
+    // ---- small candidate-independent arrays (SURVEY 8(a1) "derived once per model") ----
+    // G = M'M ; RM = chol(G) upper (predict.km: T.M <- chol(t(M)%*%M)) ; tuuinv = solve(G) (R/EI.grad.R:169)
+    std::vector<double> G((size_t)p * p, 0.0), RM((size_t)p * p, 0.0), Ginv((size_t)p * p, 0.0);
+    for (int a = 0; a < p; a++)
+      for (int b = 0; b < p; b++) {
+        long double s = 0;
+        for (int i = 0; i < n; i++) s += (long double)D->M[(size_t)i + (size_t)a * n] * D->M[(size_t)i + (size_t)b * n];
+        G[a + (size_t)b * p] = (double)s;
+      }
+    for (int j = 0; j < p; j++) {  // upper Cholesky, column by column: G = RM' RM
+      for (int i = 0; i <= j; i++) {
+        double s = G[i + (size_t)j * p];
+        for (int k = 0; k < i; k++) s -= RM[k + (size_t)i * p] * RM[k + (size_t)j * p];
+        if (i < j) RM[i + (size_t)j * p] = s / RM[i + (size_t)i * p];
+        else {
+          if (!(s > 0)) return bail(fail(DK_ERR_ARG, "M'M is not positive definite (trend matrix rank deficient)"));
+          RM[j + (size_t)j * p] = std::sqrt(s);
+        }
+      }
+    }
+    {  // Ginv = RM^-1 RM^-T  via two triangular solves per unit vector
+      std::vector<double> col(p);
+      for (int e = 0; e < p; e++) {
+        for (int i = 0; i < p; i++) {  // RM' y = e_e (forward)
+          double s = (i == e) ? 1.0 : 0.0;
+          for (int k = 0; k < i; k++) s -= RM[k + (size_t)i * p] * col[k];
+          col[i] = s / RM[i + (size_t)i * p];
+        }
+        for (int i = p - 1; i >= 0; i--) {  // RM x = y (backward)
+          double s = col[i];
+          for (int k = i + 1; k < p; k++) s -= RM[i + (size_t)k * p] * col[k];
+          col[i] = s / RM[i + (size_t)i * p];
+        }
+        for (int i = 0; i < p; i++) Ginv[i + (size_t)e * p] = col[i];
+      }
+    }
+    // alpha = T^-1 z, KinvF = T^-1 M (back substitution with the upper factor)
+    std::vector<double> aK((size_t)n * (p + 1));
+    for (int c = 0; c <= p; c++) {
+      const double* rhs = c == 0 ? D->z : D->M + (size_t)(c - 1) * n;
+      double* o = aK.data() + (size_t)c * n;
+      for (int i = n - 1; i >= 0; i--) {
+        long double s = rhs[i];
+        for (int k = i + 1; k < n; k++) s -= (long double)D->T[(size_t)i + (size_t)k * n] * o[k];
+        o[i] = (double)(s / D->T[(size_t)i + (size_t)i * n]);
+      }
+    }
+    const size_t small_count = (size_t)p + 2 * (size_t)p * p + 2 * (size_t)n * (p + 1) + (D->noise_var ? n : 0);
+    std::vector<double> small(small_count);
+    size_t off = 0;
+    const size_t o_beta = off; std::memcpy(&small[off], D->beta, p * 8); off += p;
+    const size_t o_RM = off; std::memcpy(&small[off], RM.data(), (size_t)p * p * 8); off += (size_t)p * p;
+    const size_t o_tu = off; std::memcpy(&small[off], Ginv.data(), (size_t)p * p * 8); off += (size_t)p * p;
+    const size_t o_al = off; std::memcpy(&small[off], aK.data(), (size_t)n * (p + 1) * 8); off += (size_t)n * (p + 1);
+    const size_t o_zM = off;
+    std::memcpy(&small[off], D->z, (size_t)n * 8);
+    std::memcpy(&small[off + n], D->M, (size_t)n * p * 8);
+    off += (size_t)n * (p + 1);
+    const size_t o_nv = off;
+    if (D->noise_var) std::memcpy(&small[off], D->noise_var, (size_t)n * 8);
+    if ((rc = dev_alloc(m, &m->d_small, small.size()))) return bail(rc);
+    cudaMemcpy(m->d_small, small.data(), small.size() * 8, cudaMemcpyHostToDevice);
+    dm.beta = m->d_small + o_beta; dm.RM = m->d_small + o_RM; dm.tuuinv = m->d_small + o_tu;
+    dm.alpha = m->d_small + o_al; dm.KinvF = m->d_small + o_al + n;
+    dm.noise_var = D->noise_var ? m->d_small + o_nv : nullptr;
+    dm.Mcm = m->d_small + o_zM + n;
+    m->h_zM = (double*)std::malloc((size_t)n * (p + 1) * 8);
+    if (!m->h_zM) return bail(fail(DK_ERR_NOMEM, "host allocation failed"));
+    std::memcpy(m->h_zM, &small[o_zM], (size_t)n * (p + 1) * 8);
+
+    // host copy of T for the lazily built backward tiles
+    m->h_T = (double*)std::malloc((size_t)n * n * 8);
+    if (!m->h_T) return bail(fail(DK_ERR_NOMEM, "host allocation failed"));
+    std::memcpy(m->h_T, D->T, (size_t)n * n * 8);
+  } catch (const std::bad_alloc&) {
+    return bail(fail(DK_ERR_NOMEM, "host allocation failed while tiling the factor"));
+  }
+
+  // ---- per-CTA V panels: two resident CTAs per SM ----
+  m->grid = 2 * m->num_sms;
+  m->scratch_doubles_per_cta = (size_t)dm.n_pad * BN;
+  if ((rc = dev_alloc(m, &m->d_vscratch, (size_t)m->grid * m->scratch_doubles_per_cta))) return bail(rc);
+  if (cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess)
+    return bail(fail(DK_ERR_CUDA, "cudaStreamCreate failed"));
+  if (cudaDeviceSynchronize() != cudaSuccess)
+    return bail(fail(DK_ERR_CUDA, "model upload failed: %s", cudaGetErrorString(cudaGetLastError())));
+  *out = m;
+  return DK_OK;
+}
+
+void dk_model_destroy(dk_model* m) {
+  if (!m) return;
+  DeviceGuard guard(m->device);
+  cudaDeviceSynchronize();
+  cudaFree(m->d_tiles_fwd); cudaFree(m->d_tiles_bwd); cudaFree(m->d_Xrm); cudaFree(m->d_small);
+  cudaFree(m->d_vscratch); cudaFree(m->d_wscratch); cudaFree(m->d_io); cudaFree(m->d_red);
+  if (m->stream) cudaStreamDestroy(m->stream);
+  std::free(m->h_T);
+  std::free(m->h_zM);
+  delete m;
+}
+
+size_t dk_model_device_bytes(const dk_model* m) { return m ? m->device_bytes : 0; }
+long long dk_model_launches(const dk_model* m) { return m ? m->launches : 0; }
+
+// ------------------------------------------------------------------------------------------
+// device-pointer entry points
+// ------------------------------------------------------------------------------------------
+int dk_predict_dev(dk_model* m, const double* d_x, int64_t N, int type, double* d_mean, double* d_sd, void* stream) {
+  int rc = check_call(m, d_x, N);
+  if (rc) return rc;
+  if (!d_mean) return fail(DK_ERR_ARG, "d_mean is NULL");
+  DeviceGuard guard(m->device);
+  CritParams P{MODE_PREDICT, type, 1, 0, 0.0, 0.0};
+  return launch_predict(m, P, d_x, N, nullptr, d_mean, d_sd, (cudaStream_t)stream);
+}
+
+int dk_ei_dev(dk_model* m, const double* d_x, int64_t N, double plugin, int type, int minimization, int proxy,
+              double* d_ei, double* d_mean, double* d_sd, void* stream) {
+  int rc = check_call(m, d_x, N);
+  if (rc) return rc;
+  if (!d_ei) return fail(DK_ERR_ARG, "d_ei is NULL");
+  DeviceGuard guard(m->device);
+  CritParams P{MODE_EI, type, minimization, proxy, plugin, 0.0};
+  return launch_predict(m, P, d_x, N, d_ei, d_mean, d_sd, (cudaStream_t)stream);
+}
+
+int dk_quantile_dev(dk_model* m, const double* d_x, int64_t N, double qnorm_beta, int type, double* d_q,
+                    double* d_grad, void* stream) {
+  int rc = check_call(m, d_x, N);
+  if (rc) return rc;
+  if (!d_q && !d_grad) return fail(DK_ERR_ARG, "both outputs are NULL");
+  DeviceGuard guard(m->device);
+  CritParams P{MODE_QUANTILE, type, 1, 0, 0.0, qnorm_beta};
+  if (d_grad) return launch_grad(m, P, d_x, N, d_grad, d_q, (cudaStream_t)stream);
+  return launch_predict(m, P, d_x, N, d_q, nullptr, nullptr, (cudaStream_t)stream);
+}
+
+int dk_ei_grad_dev(dk_model* m, const double* d_x, int64_t N, double plugin, int type, int minimization, int proxy,
+                   double* d_grad, double* d_ei, void* stream) {
+  int rc = check_call(m, d_x, N);
+  if (rc) return rc;
+  if (!d_grad) return fail(DK_ERR_ARG, "d_grad is NULL");
+  DeviceGuard guard(m->device);
+  CritParams P{MODE_EI, type, minimization, proxy, plugin, 0.0};
+  return launch_grad(m, P, d_x, N, d_grad, d_ei, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------
+// host-pointer entry points: H2D, launch, D2H on the handle's stream, then synchronise.
+// ------------------------------------------------------------------------------------------
+namespace {
+struct HostCall {
+  dk_model* m;
+  double* d_x;
+  double* d_out;  // scratch for outputs after x
+  int init(dk_model* mm, const double* x, int64_t N, size_t out_doubles) {
+    m = mm;
+    const size_t xin = (size_t)N * m->d;
+    int rc = ensure_io(m, xin + out_doubles + 16);
+    if (rc) return rc;
+    d_x = m->d_io;
+    d_out = m->d_io + ((xin + 1) & ~(size_t)1);
+    if (N > 0) DK_CUDA_TRY(cudaMemcpyAsync(d_x, x, xin * 8, cudaMemcpyHostToDevice, m->stream));
+    return DK_OK;
+  }
+  int fetch(double* host, const double* dev, size_t count) {
+    if (host && count) DK_CUDA_TRY(cudaMemcpyAsync(host, dev, count * 8, cudaMemcpyDeviceToHost, m->stream));
+    return DK_OK;
+  }
+  int finish() {
+    DK_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    return DK_OK;
+  }
+};
+}  // namespace
+
+int dk_predict(dk_model* m, const double* x, int64_t N, int type, double* out_mean, double* out_sd) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (!out_mean) return fail(DK_ERR_ARG, "out_mean is NULL");
+  DeviceGuard guard(m->device);
+  HostCall h;
+  if ((rc = h.init(m, x, N, 2 * (size_t)N))) return rc;
+  if ((rc = dk_predict_dev(m, h.d_x, N, type, h.d_out, out_sd ? h.d_out + N : nullptr, m->stream))) return rc;
+  if ((rc = h.fetch(out_mean, h.d_out, N))) return rc;
+  if ((rc = h.fetch(out_sd, h.d_out + N, N))) return rc;
+  return h.finish();
+}
+
+int dk_ei(dk_model* m, const double* x, int64_t N, double plugin, int type, int minimization, int proxy,
+          double* out_ei, double* out_mean, double* out_sd) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (!out_ei) return fail(DK_ERR_ARG, "out_ei is NULL");
+  DeviceGuard guard(m->device);
+  HostCall h;
+  if ((rc = h.init(m, x, N, 3 * (size_t)N))) return rc;
+  double* d_ei = h.d_out;
+  double* d_mean = out_mean ? h.d_out + N : nullptr;
+  double* d_sd = out_sd ? h.d_out + 2 * N : nullptr;
+  if ((rc = dk_ei_dev(m, h.d_x, N, plugin, type, minimization, proxy, d_ei, d_mean, d_sd, m->stream))) return rc;
+  if ((rc = h.fetch(out_ei, d_ei, N))) return rc;
+  if ((rc = h.fetch(out_mean, d_mean, N))) return rc;
+  if ((rc = h.fetch(out_sd, d_sd, N))) return rc;
+  return h.finish();
+}
+
+int dk_ei_grad(dk_model* m, const double* x, int64_t N, double plugin, int type, int minimization, int proxy,
+               double* out_grad, double* out_ei) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (!out_grad) return fail(DK_ERR_ARG, "out_grad is NULL");
+  DeviceGuard guard(m->device);
+  HostCall h;
+  if ((rc = h.init(m, x, N, (size_t)N * (m->d + 1)))) return rc;
+  double* d_grad = h.d_out;
+  double* d_ei = h.d_out + (size_t)N * m->d;
+  if ((rc = dk_ei_grad_dev(m, h.d_x, N, plugin, type, minimization, proxy, d_grad, d_ei, m->stream))) return rc;
+  if ((rc = h.fetch(out_grad, d_grad, (size_t)N * m->d))) return rc;
+  if ((rc = h.fetch(out_ei, d_ei, N))) return rc;
+  return h.finish();
+}
+
+int dk_quantile(dk_model* m, const double* x, int64_t N, double qnorm_beta, int type, double* out_q, double* out_grad) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (!out_q) return fail(DK_ERR_ARG, "out_q is NULL");
+  DeviceGuard guard(m->device);
+  HostCall h;
+  if ((rc = h.init(m, x, N, (size_t)N * (m->d + 1)))) return rc;
+  double* d_q = h.d_out;
+  double* d_grad = out_grad ? h.d_out + N + (N & 1) : nullptr;
+  if ((rc = dk_quantile_dev(m, h.d_x, N, qnorm_beta, type, d_q, d_grad, m->stream))) return rc;
+  if ((rc = h.fetch(out_q, d_q, N))) return rc;
+  if ((rc = h.fetch(out_grad, d_grad, (size_t)N * m->d))) return rc;
+  return h.finish();
+}
+
+int dk_screen_ei(dk_model* m, const double* x, int x_on_device, int64_t N, double plugin, int type, int minimization,
+                 int proxy, int k, int64_t* out_idx, double* out_val, void* stream) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (k < 1 || k > DK_TOPK_MAX) return fail(DK_ERR_ARG, "k=%d outside 1..%d", k, DK_TOPK_MAX);
+  if (!out_idx || !out_val) return fail(DK_ERR_ARG, "output pointer is NULL");
+  DeviceGuard guard(m->device);
+  cudaStream_t st = x_on_device ? (cudaStream_t)stream : m->stream;
+  const size_t xin = x_on_device ? 0 : (size_t)N * m->d;
+  if ((rc = ensure_io(m, xin + (size_t)N + 16))) return rc;
+  const double* d_x = x;
+  if (!x_on_device) {
+    if (N > 0) DK_CUDA_TRY(cudaMemcpyAsync(m->d_io, x, xin * 8, cudaMemcpyHostToDevice, st));
+    d_x = m->d_io;
+  }
+  double* d_ei = m->d_io + ((xin + 1) & ~(size_t)1);
+  CritParams P{MODE_EI, type, minimization, proxy, plugin, 0.0};
+  if ((rc = launch_predict(m, P, d_x, N, d_ei, nullptr, nullptr, st))) return rc;
+  if ((rc = ensure_red(m, topk_workspace_bytes(k)))) return rc;
+  if ((rc = launch_topk(d_ei, N, k, m->d_red, st))) return rc;
+  m->launches += 2;
+  std::vector<TopkEntry> host(k);
+  DK_CUDA_TRY(cudaMemcpyAsync(host.data(), topk_result_ptr(m->d_red), sizeof(TopkEntry) * k, cudaMemcpyDeviceToHost, st));
+  DK_CUDA_TRY(cudaStreamSynchronize(st));
+  for (int i = 0; i < k; i++) {
+    out_idx[i] = host[i].idx;
+    out_val[i] = host[i].val;
+  }
+  return DK_OK;
+}
+
+/* Debug aid (not part of the drop-in surface): the same criterion through the plain
+ * one-thread-per-candidate substitution kernel; tests use it to localise tiling bugs. */
+int dk_debug_plain(dk_model* m, const double* x, int64_t N, int mode, double plugin, double qnorm_beta, int type,
+                   int minimization, int proxy, double* out_main, double* out_mean, double* out_sd) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  DeviceGuard guard(m->device);
+  const int n = m->n, p = m->p;
+  double *d_T = nullptr, *d_zM = nullptr, *d_v = nullptr, *d_xo = nullptr;
+  DK_CUDA_TRY(cudaMalloc(&d_T, (size_t)n * n * 8));
+  DK_CUDA_TRY(cudaMalloc(&d_zM, (size_t)n * (p + 1) * 8));
+  DK_CUDA_TRY(cudaMalloc(&d_v, (size_t)n * N * 8));
+  DK_CUDA_TRY(cudaMalloc(&d_xo, (size_t)N * (m->d + 3) * 8));
+  DK_CUDA_TRY(cudaMemcpy(d_T, m->h_T, (size_t)n * n * 8, cudaMemcpyHostToDevice));
+  DK_CUDA_TRY(cudaMemcpy(d_zM, m->h_zM, (size_t)n * (p + 1) * 8, cudaMemcpyHostToDevice));
+  DK_CUDA_TRY(cudaMemcpy(d_xo, x, (size_t)N * m->d * 8, cudaMemcpyHostToDevice));
+  double* d_main = d_xo + (size_t)N * m->d;
+  CritParams P{mode, type, minimization, proxy, plugin, qnorm_beta};
+  k_predict_plain<<<(unsigned)((N + 127) / 128), 128>>>(m->dm, P, d_xo, N, d_T, d_zM, d_v, d_main, d_main + N, d_main + 2 * N);
+  m->launches++;
+  DK_CUDA_TRY(cudaGetLastError());
+  DK_CUDA_TRY(cudaDeviceSynchronize());
+  if (out_main) DK_CUDA_TRY(cudaMemcpy(out_main, d_main, N * 8, cudaMemcpyDeviceToHost));
+  if (out_mean) DK_CUDA_TRY(cudaMemcpy(out_mean, d_main + N, N * 8, cudaMemcpyDeviceToHost));
+  if (out_sd) DK_CUDA_TRY(cudaMemcpy(out_sd, d_main + 2 * N, N * 8, cudaMemcpyDeviceToHost));
+  cudaFree(d_T); cudaFree(d_zM); cudaFree(d_v); cudaFree(d_xo);
+  return DK_OK;
+}
+
+}  // extern "C"

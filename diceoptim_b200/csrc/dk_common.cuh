@@ -1,0 +1,125 @@
+// dk_common.cuh — shared definitions of the dk_b200 engine (host + device).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+#include "dk_b200.h"
+
+namespace dk {
+
+// ---------------------------------------------------------------------------------------
+// Tile geometry of the blocked triangular solve (DESIGN.md "kernels").
+//   block row  : BM = 128 rows of the augmented factor  L_aug = [[T', 0], [ [z M]', I ]]
+//   candidates : BN = 64 columns per CTA tile
+//   k-chunk    : KC = 16 (four DMMA m8n8k4 steps per pipeline stage)
+// A and B tiles are stored in DMMA *fragment order* (a_tile_index / b_tile_index) both in
+// HBM and in shared memory, so a stage is a straight 16-byte copy and every fragment read
+// is one conflict-free LDS.128.
+// ---------------------------------------------------------------------------------------
+constexpr int BM = 128;
+constexpr int BN = 64;
+constexpr int KC = 16;
+constexpr int NT = 256;          // threads per CTA: 8 warps as 4 (rows) x 2 (cols), warp tile 32 x 32
+constexpr int STAGES = 3;
+constexpr int A_TILE = BM * KC;  // doubles
+constexpr int B_TILE = KC * BN;  // doubles
+constexpr int CB_STRIDE = 72;    // row stride (doubles) of the covariance staging tile
+constexpr int CHUNKS_PER_BLOCK = BM / KC;  // 8
+
+// Shared-memory map (bytes).  Region 0 is time-multiplexed inside one block row:
+//   cov-gen : [Cbuf 128 x 72 doubles = 73728][Xs 128 x d doubles <= 24576]
+//   GEMM    : [3 stages x (A 16384 + B 8192) = 73728][unused]
+//   diag    : [R 8 chunks x 8192 = 65536][Abuf 2 x 16384 = 32768]
+constexpr int SM_REGION0 = 98304;
+constexpr int SM_XS_OFF = CB_STRIDE * BM * 8;             // 73728
+constexpr int SM_ABUF_OFF = CHUNKS_PER_BLOCK * B_TILE * 8;  // 65536
+constexpr int SM_CAND_OFF = SM_REGION0;                   // xs[d][64]
+constexpr int SM_CAND_BYTES = DK_MAX_D * BN * 8;          // 12288
+constexpr int SM_S2_OFF = SM_CAND_OFF + SM_CAND_BYTES;    // s2acc[4][64]
+constexpr int SM_S2_BYTES = 4 * BN * 8;                   // 2048
+constexpr int SM_TOTAL = SM_S2_OFF + SM_S2_BYTES;         // 112640 (two CTAs per SM fit in 227 KB)
+
+__host__ __device__ __forceinline__ int a_tile_index(int r, int k) {  // r < 128, k < 16
+  const int g = r >> 3, mp = g >> 1, e = g & 1, rl = r & 7, k4 = k >> 2, kl = k & 3;
+  return (((mp * 4 + k4) * 32) + (rl * 4 + kl)) * 2 + e;
+}
+__host__ __device__ __forceinline__ int b_tile_index(int k, int n) {  // k < 16, n < 64
+  const int k4 = k >> 2, kl = k & 3, g = n >> 3, np = g >> 1, e = g & 1, nl = n & 7;
+  return (((k4 * 4 + np) * 32) + (nl * 4 + kl)) * 2 + e;
+}
+// first tile of block row I in a tile array: rows I' < I hold 8 I' off-diagonal tiles + 8 inverse tiles
+__host__ __device__ __forceinline__ size_t tile_base(int I) { return (size_t)4 * I * (I + 1); }
+
+// Model constants handed to kernels by value (constant bank).
+struct DevModel {
+  int n, d, p, n_aug, nblk, n_pad;
+  int nblk_b;               // block rows of the backward (flipped T) system: ceil(n / 128)
+  int kernel, trend, nugget_flag;
+  double sd2, nugget, total_sd2;
+  const double* tiles_fwd;  // forward tiles: -L_aug off-diagonal, block inverses on the diagonal
+  const double* tiles_bwd;  // backward (flipped T) tiles, same format; NULL until a gradient call
+  const double* Xrm;        // [n_pad][d] row-major design (pad rows zero)
+  const double* beta;       // p
+  const double* RM;         // chol(M'M) upper, p x p column-major
+  const double* tuuinv;     // (M'M)^-1, p x p
+  const double* alpha;      // T^-1 z, n
+  const double* KinvF;      // T^-1 M, n x p column-major
+  const double* Mcm;        // model@M, n x p column-major
+  const double* noise_var;  // n or NULL
+  double w[DK_MAX_D];       // per-dimension scale of |h|: 1/theta (gauss, exp, powexp), sqrt3/theta, sqrt5/theta
+  double shape[DK_MAX_D];   // powexp exponents
+  double theta[DK_MAX_D];
+};
+
+enum Mode { MODE_PREDICT = 0, MODE_EI = 1, MODE_QUANTILE = 2 };
+
+struct CritParams {
+  int mode, type, minimization, proxy;
+  double plugin, qnorm_beta;
+};
+
+// ---------------------------------------------------------------------------------------
+// error channel
+// ---------------------------------------------------------------------------------------
+std::string& last_error();
+int fail(int code, const char* fmt, ...);
+
+#define DK_CUDA_TRY(expr)                                                                         \
+  do {                                                                                            \
+    cudaError_t e__ = (expr);                                                                     \
+    if (e__ != cudaSuccess)                                                                       \
+      return dk::fail(DK_ERR_CUDA, "%s: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+
+}  // namespace dk
+
+// The opaque handle.
+struct dk_model {
+  int device = 0;
+  int num_sms = 0;
+  dk::DevModel dm{};
+  // device allocations owned by the handle
+  double* d_tiles_fwd = nullptr;
+  double* d_tiles_bwd = nullptr;
+  double* d_Xrm = nullptr;
+  double* d_small = nullptr;     // beta | RM | tuuinv | alpha | KinvF | noise_var
+  double* d_vscratch = nullptr;  // per-CTA V panels (forward solve), grid x n_pad x 64 doubles
+  double* d_wscratch = nullptr;  // per-CTA W panels (backward solve)
+  size_t scratch_doubles_per_cta = 0;
+  int grid = 0;
+  // grow-only staging for the host entry points
+  double* d_io = nullptr;
+  size_t io_doubles = 0;
+  void* d_red = nullptr;         // argmax partials
+  size_t red_bytes = 0;
+  cudaStream_t stream = nullptr;
+  size_t device_bytes = 0;
+  // host copies kept for lazily built pieces
+  int n = 0, d = 0, p = 0;
+  double* h_T = nullptr;         // n x n column-major copy (for the backward tiles)
+  double* h_zM = nullptr;        // [z | M], n x (p+1) column-major
+  long long launches = 0;        // kernels launched through this handle
+};

@@ -1,0 +1,174 @@
+// dk_grad.cuh — batched EI.grad / kriging.quantile.grad in adjoint form.
+//
+// The reference solves d extra triangular systems per point, W = backsolve(t(T), dc)
+// (R/EI.grad.R:161, R/kriging.quantile.grad.R:120), but W only ever appears as W'z, v'W and W'M:
+//     W'z           = dc' alpha                  alpha = T^-1 z          (per model)
+//     (v + M r)'W   = dc' T^-1 (v + M r)         ONE back substitution   (per candidate)
+// with r = tuuinv (F.newdata - v'M)'.  So per candidate tile this kernel runs
+//   1. the forward pass of dk_kernels.cuh (V panel, mean, sd),
+//   2. a backward blocked solve  T wt = v + M r  with the flipped factor's tiles (same DMMA code),
+//   3. one reduction  grad_k = sum_i c_i dlogk_k(i) (cA alpha_i + cW wt_i) + trend terms,
+// where (cA, cW) fold the closed-form outer derivative:
+//   EI       : cA = -/+ Phi(xcr) (min / max), cW = -phi(xcr)/sd ; all zero when sd/sqrt(sd2) < 1e-6 (R/EI.grad.R:153)
+//   EI proxy : cA = -/+ 1, cW = 0
+//   quantile : cA = 1, cW = -qnorm(beta)/sd ; cW = 0 when sd < sqrt(sd2)/1e6 (R/kriging.quantile.grad.R:123)
+#pragma once
+#include "dk_kernels.cuh"
+
+namespace dk {
+
+constexpr int COEF_ROWS = 2 + DK_MAX_P;  // cA, cW, r[p]
+constexpr int COEF_DOUBLES = COEF_ROWS * BN;
+
+template <int KERNEL>
+__device__ __forceinline__ void grad_accumulate(const DevModel& M, const double* __restrict__ xs,
+                                                const double* __restrict__ wpanel, int c, int slice, double cA,
+                                                double cW, double (&g)[DK_MAX_D]) {
+  const int n = M.n, d = M.d;
+#pragma unroll 1
+  for (int i = slice; i < n; i += 4) {
+    const double* Xi = M.Xrm + (size_t)i * d;
+    // covariance c_i (same arithmetic as covgen_rows)
+    double s = 0.0, pr = 1.0;
+#pragma unroll 1
+    for (int k = 0; k < d; k++) {
+      const double a = fabs(__ldg(Xi + k) - xs[k * BN + c]) * M.w[k];
+      if (KERNEL == DK_GAUSS) s = fma(0.5 * a, a, s);
+      else if (KERNEL == DK_EXP) s += a;
+      else if (KERNEL == DK_MATERN3_2) { pr *= (1.0 + a); s += a; }
+      else if (KERNEL == DK_MATERN5_2) { pr *= fma(a, fma(a, 1.0 / 3.0, 1.0), 1.0); s += a; }
+      else s += pow(a, M.shape[k]);
+    }
+    const double omega = cA * __ldg(M.alpha + i) + cW * panel_at(wpanel, n - 1 - i, c);
+    const double cw = M.sd2 * pr * exp(-s) * omega;
+    // covVector.dx: c_i * d log k / d x_k
+#pragma unroll
+    for (int k = 0; k < DK_MAX_D; k++) {
+      if (k < d) {
+        const double diff = xs[k * BN + c] - __ldg(Xi + k);
+        const double wk = M.w[k];
+        const double a = fabs(diff) * wk;
+        const double sg = (diff > 0.0) ? 1.0 : ((diff < 0.0) ? -1.0 : 0.0);
+        double dl;
+        if (KERNEL == DK_GAUSS) dl = -diff * wk * wk;
+        else if (KERNEL == DK_EXP) dl = -sg * wk;
+        else if (KERNEL == DK_MATERN3_2) dl = -sg * wk * a / (1.0 + a);
+        else if (KERNEL == DK_MATERN5_2) dl = -sg * wk * (a * (1.0 / 3.0)) * (1.0 + a) / fma(a, fma(a, 1.0 / 3.0, 1.0), 1.0);
+        else dl = (a > 0.0) ? -sg * M.shape[k] * pow(a, M.shape[k] - 1.0) * wk : 0.0;
+        g[k] = fma(cw, dl, g[k]);
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(NT, 2)
+k_grad_fused(const DevModel M, const CritParams P, const double* __restrict__ x, int64_t N, int64_t ntiles,
+             double* __restrict__ vscratch, double* __restrict__ wscratch, size_t panel_doubles,
+             double* __restrict__ out_grad, double* __restrict__ out_main) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, wm = warp >> 1, wn = warp & 1;
+  const double* xs = reinterpret_cast<const double*>(smem + SM_CAND_OFF);
+  const double* s2acc = reinterpret_cast<const double*>(smem + SM_S2_OFF);
+  double* vpanel = vscratch + (size_t)blockIdx.x * panel_doubles;
+  double* wpanel = wscratch + (size_t)blockIdx.x * (panel_doubles + COEF_DOUBLES);
+  double* coef = wpanel + panel_doubles;  // [COEF_ROWS][64]
+  const int n = M.n, d = M.d, p = M.p;
+
+#pragma unroll 1
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t c0 = tile * BN;
+    forward_tile(M, x, N, c0, vpanel, smem, tid);
+
+    // ---- epilogue 1: value + outer-derivative coefficients per candidate ----
+    if (tid < BN) {
+      const int c = tid;
+      double mean, sd, u[DK_MAX_P];
+      cand_predict(M, P.type, vpanel, xs, s2acc, c, mean, sd, u);
+      if (out_main && c0 + c < N) out_main[c0 + c] = crit_value(P, mean, sd);
+      double cA, cW;
+      bool drop_r = false;
+      if (P.mode == MODE_QUANTILE) {
+        cA = 1.0;
+        if (sd < sqrt(M.sd2) / 1e6) { cW = 0.0; drop_r = true; }
+        else cW = -P.qnorm_beta / sd;
+      } else {  // EI
+        const double sgn = P.minimization ? 1.0 : -1.0;
+        if (sd / sqrt(M.sd2) < 1e-6) { cA = 0.0; cW = 0.0; drop_r = true; }
+        else if (P.proxy) { cA = -sgn; cW = 0.0; drop_r = true; }
+        else {
+          const double xcr = (P.plugin - sgn * mean) / sd;
+          cA = -sgn * normcdf(xcr);
+          cW = -dnorm_std(xcr) / sd;
+        }
+      }
+      coef[c] = cA;
+      coef[BN + c] = cW;
+      for (int j = 0; j < p; j++) {
+        double r = 0.0;
+        if (P.type == DK_UK && !drop_r)
+          for (int i = 0; i < p; i++) r = fma(__ldg(M.tuuinv + j + i * p), u[i], r);
+        coef[(2 + j) * BN + c] = r;
+      }
+    }
+    __syncthreads();
+
+    // ---- backward blocked solve with the flipped factor: wt' = flip(T)^-1 flip(v + M r) ----
+#pragma unroll 1
+    for (int I = 0; I < M.nblk_b; I++) {
+      double acc[4][4][2];
+#pragma unroll
+      for (int mi = 0; mi < 4; mi++) {
+        const int ip = I * BM + 32 * wm + 8 * mi + (lane >> 2);  // flipped row
+        const int i = n - 1 - ip;
+#pragma unroll
+        for (int ni = 0; ni < 4; ni++)
+#pragma unroll
+          for (int e = 0; e < 2; e++) {
+            const int c = 32 * wn + 8 * ni + 2 * (lane & 3) + e;
+            double v = 0.0;
+            if (ip < n) {
+              v = panel_at(vpanel, i, c);
+              if (P.type == DK_UK)
+                for (int j = 0; j < p; j++) v = fma(__ldg(M.Mcm + i + (size_t)j * n), __ldcg(coef + (2 + j) * BN + c), v);
+            }
+            acc[mi][ni][e] = v;
+          }
+      }
+      solve_block_row(acc, M.tiles_bwd, I, wpanel, smem, tid);
+      __syncthreads();
+    }
+
+    // ---- gradient reduction: 4 row slices x 64 candidates ----
+    {
+      const int c = tid & (BN - 1), slice = tid >> 6;
+      const double cA = __ldcg(coef + c), cW = __ldcg(coef + BN + c);
+      double g[DK_MAX_D];
+#pragma unroll
+      for (int k = 0; k < DK_MAX_D; k++) g[k] = 0.0;
+      switch (M.kernel) {
+        case DK_GAUSS: grad_accumulate<DK_GAUSS>(M, xs, wpanel, c, slice, cA, cW, g); break;
+        case DK_EXP: grad_accumulate<DK_EXP>(M, xs, wpanel, c, slice, cA, cW, g); break;
+        case DK_MATERN3_2: grad_accumulate<DK_MATERN3_2>(M, xs, wpanel, c, slice, cA, cW, g); break;
+        case DK_MATERN5_2: grad_accumulate<DK_MATERN5_2>(M, xs, wpanel, c, slice, cA, cW, g); break;
+        default: grad_accumulate<DK_POWEXP>(M, xs, wpanel, c, slice, cA, cW, g); break;
+      }
+      double* gbuf = reinterpret_cast<double*>(smem);  // [4][DK_MAX_D][64] in region 0
+#pragma unroll
+      for (int k = 0; k < DK_MAX_D; k++)
+        if (k < d) gbuf[(slice * DK_MAX_D + k) * BN + c] = g[k];
+      __syncthreads();
+      if (c0 + c < N) {
+        for (int k = slice; k < d; k += 4) {
+          double s = ((gbuf[(0 * DK_MAX_D + k) * BN + c] + gbuf[(1 * DK_MAX_D + k) * BN + c]) +
+                      gbuf[(2 * DK_MAX_D + k) * BN + c]) + gbuf[(3 * DK_MAX_D + k) * BN + c];
+          if (M.trend == DK_TREND_LINEAR)  // trend.deltax = rbind(0, I_d): beta_{1+k} and r_{1+k}
+            s += cA * __ldg(M.beta + 1 + k) - cW * __ldcg(coef + (2 + 1 + k) * BN + c);
+          out_grad[(c0 + c) + (int64_t)k * N] = s;
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace dk

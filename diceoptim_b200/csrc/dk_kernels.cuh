@@ -1,0 +1,457 @@
+// dk_kernels.cuh — device code of the fused kriging-prediction kernel for sm_100a.
+//
+// One CTA owns a tile of BN = 64 candidates and walks the block rows of the augmented
+// Cholesky factor top to bottom (left-looking blocked forward substitution):
+//
+//   for block row I:
+//     P1  c_I   = sd2 * prod_k k1d(|X_ik - x_jk|)                 fused covariance generation
+//                                                                 (replaces covMat1Mat2)
+//     P3  acc   = c_I - sum_{J<I} L_IJ V_J                        FP64 DMMA m8n8k4, A = pre-tiled -L from L2,
+//                                                                 B = this CTA's V panel (3-stage cp.async ring)
+//     P4  V_I   = inv(L_II) acc                                   block inverse applied as a lower-triangular GEMM
+//                                                                 (replaces backsolve(t(T), c))
+//     P5  s2   += colsum(V_I^2); V_I -> per-CTA panel in HBM/L2   (apply(Tinv.c, 2, crossprod))
+//   epilogue: rows n..n+p of the augmented system hold -z'v and -M'v  -> mean, sd, EI / quantile.
+//
+// The V panel is the kernel's scratch: n_pad x 64 doubles per CTA, written once and re-read
+// (n_pad / 256) times on average; at n = 2000 it is 1 MB per CTA and mostly L2 traffic.
+#pragma once
+#include "dk_common.cuh"
+
+namespace dk {
+
+__device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+      : "+d"(c[0]), "+d"(c[1])
+      : "d"(a), "d"(b));
+}
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// 16 DMMAs per k4 step on the warp's 32 x 32 tile; As/Bs are fragment-ordered tiles in smem.
+__device__ __forceinline__ void mma_stage(double (&acc)[4][4][2], const double* __restrict__ As,
+                                          const double* __restrict__ Bs, int wm, int wn, int lane) {
+#pragma unroll
+  for (int k4 = 0; k4 < 4; k4++) {
+    const double2 a01 = *reinterpret_cast<const double2*>(As + (((2 * wm) * 4 + k4) * 32 + lane) * 2);
+    const double2 a23 = *reinterpret_cast<const double2*>(As + (((2 * wm + 1) * 4 + k4) * 32 + lane) * 2);
+    const double2 b01 = *reinterpret_cast<const double2*>(Bs + ((k4 * 4 + 2 * wn) * 32 + lane) * 2);
+    const double2 b23 = *reinterpret_cast<const double2*>(Bs + ((k4 * 4 + 2 * wn + 1) * 32 + lane) * 2);
+    const double a[4] = {a01.x, a01.y, a23.x, a23.y};
+    const double b[4] = {b01.x, b01.y, b23.x, b23.y};
+#pragma unroll
+    for (int mi = 0; mi < 4; mi++)
+#pragma unroll
+      for (int ni = 0; ni < 4; ni++) dmma884(acc[mi][ni], a[mi], b[ni]);
+  }
+}
+
+__device__ __forceinline__ void load_tile_async(double* dst, const double* __restrict__ src, int ndoubles, int tid) {
+  // straight copy, 16 B per cp.async
+  for (int i = tid * 2; i < ndoubles; i += NT * 2) cp_async16(dst + i, src + i);
+}
+
+// ---------------------------------------------------------------------------------------
+// P1: covariance block c[r][j] for the 128 design rows of block I and the tile's 64 candidates
+// into Cbuf (row stride CB_STRIDE).  Warp w owns rows 16w..16w+15; lane owns columns lane, lane+32.
+// 1-D kernels as DiceKriging codes them; matern kernels in product form
+// prod(1 + a + a^2/3) * exp(-sum a), algebraically the reference's exp(-sum(a - log(1+a+a^2/3))).
+// ---------------------------------------------------------------------------------------
+template <int KERNEL>
+__device__ __forceinline__ void covgen_rows(const DevModel& M, const double* __restrict__ Xs,
+                                            const double* __restrict__ xs, double* __restrict__ Cbuf,
+                                            int row0_global, int warp, int lane) {
+  const int d = M.d;
+#pragma unroll 1
+  for (int rr = 0; rr < 16; rr += 4) {
+    double s[4][2], pr[4][2], hs[4][2];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      s[j][0] = s[j][1] = 0.0;
+      pr[j][0] = pr[j][1] = 1.0;
+      hs[j][0] = hs[j][1] = 0.0;
+    }
+    const double* Xr = Xs + (16 * warp + rr) * d;
+#pragma unroll 1
+    for (int k = 0; k < d; k++) {
+      const double c0 = xs[k * BN + lane], c1 = xs[k * BN + lane + 32];
+      const double wk = M.w[k];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const double xr = Xr[j * d + k];
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+          const double h = fabs(xr - (e ? c1 : c0));
+          const double a = h * wk;
+          if (M.nugget_flag) hs[j][e] += h;
+          if (KERNEL == DK_GAUSS) {
+            s[j][e] = fma(0.5 * a, a, s[j][e]);
+          } else if (KERNEL == DK_EXP) {
+            s[j][e] += a;
+          } else if (KERNEL == DK_MATERN3_2) {
+            pr[j][e] *= (1.0 + a);
+            s[j][e] += a;
+          } else if (KERNEL == DK_MATERN5_2) {
+            pr[j][e] *= fma(a, fma(a, 1.0 / 3.0, 1.0), 1.0);
+            s[j][e] += a;
+          } else {  // powexp
+            s[j][e] += pow(a, M.shape[k]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int r = 16 * warp + rr + j;
+      const bool live = (row0_global + r) < M.n;
+#pragma unroll
+      for (int e = 0; e < 2; e++) {
+        double c = M.sd2 * pr[j][e] * exp(-s[j][e]);
+        if (M.nugget_flag && hs[j][e] < 1e-15) c += M.nugget;  // covMat1Mat2(nugget.flag=TRUE) white-noise term
+        Cbuf[r * CB_STRIDE + lane + 32 * e] = live ? c : 0.0;
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ void covgen_block(const DevModel& M, const double* Xs, const double* xs, double* Cbuf,
+                                             int row0_global, int warp, int lane) {
+  switch (M.kernel) {
+    case DK_GAUSS: covgen_rows<DK_GAUSS>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
+    case DK_EXP: covgen_rows<DK_EXP>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
+    case DK_MATERN3_2: covgen_rows<DK_MATERN3_2>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
+    case DK_MATERN5_2: covgen_rows<DK_MATERN5_2>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
+    default: covgen_rows<DK_POWEXP>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// One block row of the blocked substitution given its right-hand side already in `acc`
+// (C-fragment layout).  On return acc holds V_I; the panel chunk for rows of block I has been
+// written to `panel` (fragment-ordered B tiles).  `tiles` is the tile array to use (forward or
+// backward factor).  Contains the __syncthreads the phase changes need; callers must sync once
+// more before touching region 0 again.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const double* __restrict__ tiles, int I,
+                                                double* __restrict__ panel, unsigned char* smem, int tid) {
+  const int warp = tid >> 5, lane = tid & 31, wm = warp >> 1, wn = warp & 1;
+  double* ring = reinterpret_cast<double*>(smem);
+  const double* Atiles = tiles + tile_base(I) * A_TILE;
+  const int nk = CHUNKS_PER_BLOCK * I;
+
+  // ---- P3: acc += (-L_IJ) V_J over all k-chunks left of the diagonal block -----------------
+#pragma unroll
+  for (int s = 0; s < STAGES - 1; s++) {
+    if (s < nk) {
+      double* slot = ring + s * (A_TILE + B_TILE);
+      load_tile_async(slot, Atiles + (size_t)s * A_TILE, A_TILE, tid);
+      load_tile_async(slot + A_TILE, panel + (size_t)s * B_TILE, B_TILE, tid);
+    }
+    cp_async_commit();
+  }
+#pragma unroll 1
+  for (int kc = 0; kc < nk; kc++) {
+    cp_async_wait<STAGES - 2>();
+    __syncthreads();
+    {
+      const int nx = kc + STAGES - 1;
+      if (nx < nk) {
+        double* slot = ring + (nx % STAGES) * (A_TILE + B_TILE);
+        load_tile_async(slot, Atiles + (size_t)nx * A_TILE, A_TILE, tid);
+        load_tile_async(slot + A_TILE, panel + (size_t)nx * B_TILE, B_TILE, tid);
+      }
+      cp_async_commit();
+    }
+    const double* slot = ring + (kc % STAGES) * (A_TILE + B_TILE);
+    mma_stage(acc, slot, slot + A_TILE, wm, wn, lane);
+  }
+  cp_async_wait<0>();
+  __syncthreads();  // every warp is done with the ring: region 0 can change role
+
+  // ---- P4: V_I = inv(L_II) * acc, the right-hand side goes through smem as B fragments ------
+  double* Rbuf = reinterpret_cast<double*>(smem);
+  double* Abuf = reinterpret_cast<double*>(smem + SM_ABUF_OFF);
+  const double* Dtiles = Atiles + (size_t)nk * A_TILE;
+  load_tile_async(Abuf, Dtiles, A_TILE, tid);
+  cp_async_commit();
+#pragma unroll
+  for (int mi = 0; mi < 4; mi++) {
+    const int chunk = 2 * wm + (mi >> 1);
+    const int k = 8 * (mi & 1) + (lane >> 2);
+#pragma unroll
+    for (int ni = 0; ni < 4; ni++)
+#pragma unroll
+      for (int e = 0; e < 2; e++) {
+        const int nn = 32 * wn + 8 * ni + 2 * (lane & 3) + e;
+        Rbuf[chunk * B_TILE + b_tile_index(k, nn)] = acc[mi][ni][e];
+        acc[mi][ni][e] = 0.0;
+      }
+  }
+#pragma unroll 1
+  for (int j = 0; j < CHUNKS_PER_BLOCK; j++) {
+    cp_async_wait<0>();
+    __syncthreads();
+    if (j + 1 < CHUNKS_PER_BLOCK) {
+      load_tile_async(Abuf + ((j + 1) & 1) * A_TILE, Dtiles + (size_t)(j + 1) * A_TILE, A_TILE, tid);
+      cp_async_commit();
+    }
+    if (j < 2 * wm + 2)  // inverse is lower triangular: chunks right of this warp's rows are zero
+      mma_stage(acc, Abuf + (j & 1) * A_TILE, Rbuf + j * B_TILE, wm, wn, lane);
+  }
+
+  // ---- P5: publish V_I to the panel (fragment-ordered B tiles) -----------------------------
+#pragma unroll
+  for (int mi = 0; mi < 4; mi++) {
+    const int chunk = CHUNKS_PER_BLOCK * I + 2 * wm + (mi >> 1);
+    const int k = 8 * (mi & 1) + (lane >> 2);
+#pragma unroll
+    for (int ni = 0; ni < 4; ni++)
+#pragma unroll
+      for (int e = 0; e < 2; e++) {
+        const int nn = 32 * wn + 8 * ni + 2 * (lane & 3) + e;
+        panel[(size_t)chunk * B_TILE + b_tile_index(k, nn)] = acc[mi][ni][e];
+      }
+  }
+}
+
+__device__ __forceinline__ double panel_at(const double* panel, int row, int col) {
+  return __ldcg(panel + (size_t)(row >> 4) * B_TILE + b_tile_index(row & 15, col));
+}
+
+__device__ __forceinline__ double dnorm_std(double x) { return 0.3989422804014326779 * exp(-0.5 * x * x); }
+
+// Per-candidate predict.km epilogue: mean and sd from the solved panel.  The panel rows
+// n .. n+p hold -z'v and -M'v (augmented system).  u[j] = (F.newdata - t(Tinv.c) %*% M)_j is returned
+// for the gradient kernels.
+__device__ __forceinline__ void cand_predict(const DevModel& M, int type, const double* panel, const double* xs,
+                                             const double* s2acc, int c, double& mean_out, double& sd_out,
+                                             double* u) {
+  const int p = M.p, n = M.n;
+  double S[DK_MAX_P];
+  double mean = 0.0;
+  for (int j = 0; j < p; j++) {
+    const double fj = (j == 0) ? 1.0 : xs[(j - 1) * BN + c];  // model.matrix: ~1 -> 1 ; ~. -> (1, x)
+    mean = fma(fj, __ldg(M.beta + j), mean);
+    u[j] = fj + panel_at(panel, n + 1 + j, c);
+  }
+  mean += -panel_at(panel, n, c);  // + Tinv.c' z
+  double s2 = M.total_sd2 - (((s2acc[c] + s2acc[BN + c]) + s2acc[2 * BN + c]) + s2acc[3 * BN + c]);
+  if (type == DK_UK) {
+    // s2.predict.2 = colSums(backsolve(t(T.M), t(F.newdata - t(Tinv.c) %*% M))^2)
+    double s22 = 0.0;
+    for (int j = 0; j < p; j++) {
+      double t = u[j];
+      for (int i = 0; i < j; i++) t -= __ldg(M.RM + i + j * p) * S[i];
+      S[j] = t / __ldg(M.RM + j + j * p);
+      s22 = fma(S[j], S[j], s22);
+    }
+    s2 += s22;
+  }
+  s2 = fmax(s2, 0.0);
+  mean_out = mean;
+  sd_out = sqrt(s2);
+}
+
+// EI (R/EI.R:118-132), kriging.quantile (R/kriging.quantile.R:102-105) or the bare mean.
+__device__ __forceinline__ double crit_value(const CritParams& P, double mean, double sd) {
+  if (P.mode == MODE_PREDICT) return mean;
+  if (P.mode == MODE_QUANTILE) return mean + P.qnorm_beta * sd;
+  const double km = P.minimization ? mean : -mean;
+  const double diff = P.plugin - km;
+  if (P.proxy) return diff;
+  const double xcr = diff / sd;
+  return diff * normcdf(xcr) + sd * dnorm_std(xcr);
+}
+
+__device__ __noinline__ void crit_epilogue(const DevModel& M, const CritParams& P, const double* panel,
+                                           const double* xs, const double* s2acc, int c, int64_t gidx,
+                                           double* out_main, double* out_mean, double* out_sd) {
+  double mean, sd, u[DK_MAX_P];
+  cand_predict(M, P.type, panel, xs, s2acc, c, mean, sd, u);
+  if (out_mean) out_mean[gidx] = mean;
+  if (out_sd) out_sd[gidx] = sd;
+  if (out_main) out_main[gidx] = crit_value(P, mean, sd);
+}
+
+// ---------------------------------------------------------------------------------------
+// Forward pass of one candidate tile: stage the candidates, then for every block row
+// cov-gen -> solve -> s2.  On return (after a __syncthreads) the panel holds V (and the
+// augmented rows), s2acc the per-warp-row partial sums of v^2, xs the candidate tile.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void forward_tile(const DevModel& M, const double* __restrict__ x, int64_t N, int64_t c0,
+                                             double* __restrict__ panel, unsigned char* smem, int tid) {
+  const int warp = tid >> 5, lane = tid & 31, wm = warp >> 1, wn = warp & 1;
+  double* Cbuf = reinterpret_cast<double*>(smem);
+  double* Xs = reinterpret_cast<double*>(smem + SM_XS_OFF);
+  double* xs = reinterpret_cast<double*>(smem + SM_CAND_OFF);
+  double* s2acc = reinterpret_cast<double*>(smem + SM_S2_OFF);
+  const int d = M.d;
+  // candidate tile: xs[k][j], coalesced along j (R's column-major N x d is already SoA)
+  for (int i = tid; i < d * BN; i += NT) {
+    const int k = i / BN, j = i % BN;
+    const int64_t g = c0 + j;
+    xs[i] = (g < N) ? x[g + (int64_t)k * N] : x[(N - 1) + (int64_t)k * N];
+  }
+  if (tid < 4 * BN) s2acc[tid] = 0.0;
+
+#pragma unroll 1
+  for (int I = 0; I < M.nblk; I++) {
+    // ---- P1: design rows of this block -> smem, then covariance block -> Cbuf ----
+    {
+      const double* src = M.Xrm + (size_t)I * BM * d;
+      for (int i = tid; i < BM * d; i += NT) Xs[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    covgen_block(M, Xs, xs, Cbuf, I * BM, warp, lane);
+    __syncthreads();
+    // ---- P2: Cbuf -> accumulator fragments ----
+    double acc[4][4][2];
+#pragma unroll
+    for (int mi = 0; mi < 4; mi++)
+#pragma unroll
+      for (int ni = 0; ni < 4; ni++) {
+        const double2 v = *reinterpret_cast<const double2*>(
+            Cbuf + (32 * wm + 8 * mi + (lane >> 2)) * CB_STRIDE + 32 * wn + 8 * ni + 2 * (lane & 3));
+        acc[mi][ni][0] = v.x;
+        acc[mi][ni][1] = v.y;
+      }
+    __syncthreads();
+    // ---- P3..P5 ----
+    solve_block_row(acc, M.tiles_fwd, I, panel, smem, tid);
+    // ---- s2 += sum over this block's real rows of v^2 (fixed order: rows, then lanes, then warps) ----
+    {
+      double part[4][2];
+#pragma unroll
+      for (int ni = 0; ni < 4; ni++) part[ni][0] = part[ni][1] = 0.0;
+#pragma unroll
+      for (int mi = 0; mi < 4; mi++) {
+        const bool live = (I * BM + 32 * wm + 8 * mi + (lane >> 2)) < M.n;
+#pragma unroll
+        for (int ni = 0; ni < 4; ni++)
+#pragma unroll
+          for (int e = 0; e < 2; e++) {
+            const double v = live ? acc[mi][ni][e] : 0.0;
+            part[ni][e] = fma(v, v, part[ni][e]);
+          }
+      }
+#pragma unroll
+      for (int ni = 0; ni < 4; ni++)
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+          double v = part[ni][e];
+          v += __shfl_xor_sync(0xffffffffu, v, 4);
+          v += __shfl_xor_sync(0xffffffffu, v, 8);
+          v += __shfl_xor_sync(0xffffffffu, v, 16);
+          if (lane < 4) s2acc[wm * BN + 32 * wn + 8 * ni + 2 * lane + e] += v;
+        }
+    }
+    __syncthreads();  // panel writes + s2acc visible; region 0 free for the next block row
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// The fused forward kernel: persistent CTAs, two per SM, each looping over candidate tiles.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(NT, 2)
+k_predict_fused(const DevModel M, const CritParams P, const double* __restrict__ x, int64_t N, int64_t ntiles,
+                double* __restrict__ vscratch, size_t panel_doubles, double* __restrict__ out_main,
+                double* __restrict__ out_mean, double* __restrict__ out_sd) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int tid = threadIdx.x;
+  const double* xs = reinterpret_cast<const double*>(smem + SM_CAND_OFF);
+  const double* s2acc = reinterpret_cast<const double*>(smem + SM_S2_OFF);
+  double* panel = vscratch + (size_t)blockIdx.x * panel_doubles;
+#pragma unroll 1
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t c0 = tile * BN;
+    forward_tile(M, x, N, c0, panel, smem, tid);
+    if (tid < BN && c0 + tid < N)
+      crit_epilogue(M, P, panel, xs, s2acc, tid, c0 + tid, out_main, out_mean, out_sd);
+    __syncthreads();  // xs / s2acc / panel are reused by the next tile
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// Plain one-thread-per-candidate forward substitution (no tiles, no tensor pipe).  Debug aid
+// only: tests use it to tell a tiling bug from an epilogue bug.  v lives in `vcol` (n x N, column j
+// strided by N so that consecutive threads touch consecutive addresses).
+// ---------------------------------------------------------------------------------------
+__global__ void k_predict_plain(const DevModel M, const CritParams P, const double* __restrict__ x, int64_t N,
+                                const double* __restrict__ Tcm, const double* __restrict__ zM, double* __restrict__ vcol,
+                                double* __restrict__ out_main, double* __restrict__ out_mean,
+                                double* __restrict__ out_sd) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= N) return;
+  const int n = M.n, d = M.d, p = M.p;
+  double s2 = 0.0, zv = 0.0, Mv[DK_MAX_P];
+  for (int q = 0; q < p; q++) Mv[q] = 0.0;
+  for (int i = 0; i < n; i++) {
+    double s = 0.0, pr = 1.0, hs = 0.0;
+    for (int k = 0; k < d; k++) {
+      const double h = fabs(M.Xrm[(size_t)i * d + k] - x[j + (int64_t)k * N]);
+      const double a = h * M.w[k];
+      hs += h;
+      switch (M.kernel) {
+        case DK_GAUSS: s = fma(0.5 * a, a, s); break;
+        case DK_EXP: s += a; break;
+        case DK_MATERN3_2: pr *= (1.0 + a); s += a; break;
+        case DK_MATERN5_2: pr *= fma(a, fma(a, 1.0 / 3.0, 1.0), 1.0); s += a; break;
+        default: s += pow(a, M.shape[k]); break;
+      }
+    }
+    double c = M.sd2 * pr * exp(-s);
+    if (M.nugget_flag && hs < 1e-15) c += M.nugget;
+    // row i of T' = column i of T (upper): T[r + i n], r < i
+    double acc = c;
+    for (int r = 0; r < i; r++) acc = fma(-Tcm[r + (size_t)i * n], vcol[j + (int64_t)r * N], acc);
+    const double v = acc / Tcm[i + (size_t)i * n];
+    vcol[j + (int64_t)i * N] = v;
+    s2 = fma(v, v, s2);
+    zv = fma(v, zM[i], zv);
+    for (int q = 0; q < p; q++) Mv[q] = fma(v, zM[(size_t)(q + 1) * n + i], Mv[q]);
+  }
+  double f[DK_MAX_P], S[DK_MAX_P];
+  f[0] = 1.0;
+  if (M.trend == DK_TREND_LINEAR)
+    for (int k = 0; k < d; k++) f[1 + k] = x[j + (int64_t)k * N];
+  double mean = 0.0;
+  for (int q = 0; q < p; q++) mean = fma(f[q], M.beta[q], mean);
+  mean += zv;
+  double var = M.total_sd2 - s2;
+  if (P.type == DK_UK) {
+    double s22 = 0.0;
+    for (int q = 0; q < p; q++) {
+      double u = f[q] - Mv[q];
+      for (int i = 0; i < q; i++) u -= M.RM[i + q * p] * S[i];
+      S[q] = u / M.RM[q + q * p];
+      s22 = fma(S[q], S[q], s22);
+    }
+    var += s22;
+  }
+  var = fmax(var, 0.0);
+  const double sd = sqrt(var);
+  if (out_mean) out_mean[j] = mean;
+  if (out_sd) out_sd[j] = sd;
+  double res;
+  if (P.mode == MODE_PREDICT) res = mean;
+  else if (P.mode == MODE_QUANTILE) res = mean + P.qnorm_beta * sd;
+  else {
+    const double km = P.minimization ? mean : -mean;
+    const double diff = P.plugin - km;
+    if (P.proxy) res = diff;
+    else {
+      const double xcr = diff / sd;
+      res = diff * normcdf(xcr) + sd * dnorm_std(xcr);
+    }
+  }
+  if (out_main) out_main[j] = res;
+}
+
+}  // namespace dk

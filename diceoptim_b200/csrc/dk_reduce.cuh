@@ -1,0 +1,101 @@
+// dk_reduce.cuh — device which.max / top-k over a criterion vector (R/max_crit.R:107 semantics:
+// first maximal index, NaN skipped).  Selection is by the strict total order
+// (value descending, index ascending), so the result does not depend on block scheduling.
+// Pass t finds the best entry strictly after result[t-1] in that order; k passes give the k best.
+#pragma once
+#include "dk_common.cuh"
+
+#define DK_TOPK_MAX 64
+
+namespace dk {
+
+struct TopkEntry {
+  double val;
+  long long idx;  // -1 = empty
+};
+
+constexpr int RED_BLOCKS = 296;
+constexpr int RED_THREADS = 256;
+
+__host__ __device__ inline size_t topk_workspace_bytes(int) {
+  return sizeof(TopkEntry) * DK_TOPK_MAX + 64 + sizeof(TopkEntry) * RED_BLOCKS;
+}
+inline TopkEntry* topk_result_ptr(void* ws) { return reinterpret_cast<TopkEntry*>(ws); }
+
+__device__ __forceinline__ bool topk_better(const TopkEntry& a, const TopkEntry& b) {
+  if (a.idx < 0) return false;
+  if (b.idx < 0) return true;
+  return a.val > b.val || (a.val == b.val && a.idx < b.idx);
+}
+
+__global__ void __launch_bounds__(RED_THREADS)
+k_topk_pass(const double* __restrict__ v, int64_t N, int t, unsigned char* __restrict__ ws) {
+  TopkEntry* result = reinterpret_cast<TopkEntry*>(ws);
+  unsigned* counter = reinterpret_cast<unsigned*>(ws + sizeof(TopkEntry) * DK_TOPK_MAX);
+  TopkEntry* partial = reinterpret_cast<TopkEntry*>(ws + sizeof(TopkEntry) * DK_TOPK_MAX + 64);
+  __shared__ TopkEntry sh[RED_THREADS / 32];
+  __shared__ bool is_last;
+
+  TopkEntry prev{0.0, -1};
+  const bool have_prev = t > 0;
+  if (have_prev) prev = result[t - 1];
+  TopkEntry best{0.0, -1};
+  if (!have_prev || prev.idx >= 0) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x) {
+      const double x = v[i];
+      if (x != x) continue;  // NaN skipped, like which.max
+      if (have_prev && !(x < prev.val || (x == prev.val && i > prev.idx))) continue;
+      const TopkEntry cand{x, (long long)i};
+      if (topk_better(cand, best)) best = cand;
+    }
+  }
+  auto warp_reduce = [](TopkEntry b) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      TopkEntry o;
+      o.val = __shfl_xor_sync(0xffffffffu, b.val, off);
+      o.idx = __shfl_xor_sync(0xffffffffu, b.idx, off);
+      if (topk_better(o, b)) b = o;
+    }
+    return b;
+  };
+  best = warp_reduce(best);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) sh[warp] = best;
+  __syncthreads();
+  if (warp == 0) {
+    TopkEntry b = lane < RED_THREADS / 32 ? sh[lane] : TopkEntry{0.0, -1};
+    b = warp_reduce(b);
+    if (lane == 0) {
+      partial[blockIdx.x] = b;
+      __threadfence();
+      const unsigned ticket = atomicAdd(counter, 1u);
+      is_last = (ticket == gridDim.x - 1);
+    }
+  }
+  __syncthreads();
+  if (is_last && warp == 0) {
+    __threadfence();
+    TopkEntry b{0.0, -1};
+    for (int i = lane; i < (int)gridDim.x; i += 32) {
+      const TopkEntry o{__ldcg(&partial[i].val), __ldcg(&partial[i].idx)};
+      if (topk_better(o, b)) b = o;
+    }
+    b = warp_reduce(b);
+    if (lane == 0) {
+      result[t] = b;
+      *counter = 0u;  // ready for the next pass
+    }
+  }
+}
+
+inline int launch_topk(const double* d_v, int64_t N, int k, void* ws, cudaStream_t st) {
+  DK_CUDA_TRY(cudaMemsetAsync(reinterpret_cast<unsigned char*>(ws) + sizeof(TopkEntry) * DK_TOPK_MAX, 0, 64, st));
+  for (int t = 0; t < k; t++) {
+    k_topk_pass<<<RED_BLOCKS, RED_THREADS, 0, st>>>(d_v, N, t, reinterpret_cast<unsigned char*>(ws));
+    DK_CUDA_TRY(cudaGetLastError());
+  }
+  return DK_OK;
+}
+
+}  // namespace dk

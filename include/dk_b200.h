@@ -1,0 +1,126 @@
+/*
+ * dk_b200.h — C ABI of the B200-native batched acquisition engine for DiceOptim.
+ *
+ * This is the R-free layer (1) of SURVEY.md 8(b): plain pointers and sizes, int status
+ * return (0 = ok), message via dk_last_error().  The R `.Call` shim (r-package/src/dk_rcall.c,
+ * registered next to the reference's own table, /root/reference/src/packagename_init.c:12-21)
+ * is a mechanical wrapper over these entry points; INTEGRATION.md shows the binding.
+ *
+ * Conventions (R's): all matrices are COLUMN-MAJOR doubles.  Candidates `x` are N x d
+ * (coordinate k of candidate j at x[j + k*N]); gradients are N x d likewise.
+ * Host entry points take HOST pointers and do the host<->device copies themselves;
+ * the *_dev entry points take DEVICE pointers on the model's device and enqueue on `stream`
+ * (a cudaStream_t passed as void*; NULL = the default stream) without synchronising.
+ * One model handle is bound to one CUDA device; calls on one handle must not overlap
+ * (R is single-threaded; the handle owns per-call scratch).
+ */
+#ifndef DK_B200_H
+#define DK_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* covariance@name of a DiceKriging covTensorProduct */
+enum { DK_GAUSS = 0, DK_EXP = 1, DK_MATERN3_2 = 2, DK_MATERN5_2 = 3, DK_POWEXP = 4 };
+/* trend.formula: ~1 or ~. */
+enum { DK_TREND_CONST = 0, DK_TREND_LINEAR = 1 };
+/* predict type */
+enum { DK_SK = 0, DK_UK = 1 };
+/* criteria for dk_screen */
+enum { DK_CRIT_EI = 0, DK_CRIT_QUANTILE = 1, DK_CRIT_AKG = 2 };
+
+enum {
+  DK_OK = 0,
+  DK_ERR_ARG = 1,        /* bad dimension / NULL / unsupported kernel, trend, q */
+  DK_ERR_CUDA = 2,       /* CUDA runtime error (message has the string) */
+  DK_ERR_NOMEM = 3,      /* host or device allocation failed */
+  DK_ERR_UNSUPPORTED = 4 /* no usable sm_100 device */
+};
+
+#define DK_MAX_D 24   /* input dimension limit of the fused kernels */
+#define DK_MAX_P 25   /* trend columns (1 for ~1, d+1 for ~.) */
+#define DK_MAX_Q 4    /* qEI batch size served by the deterministic CDF kernels */
+
+typedef struct dk_model dk_model;
+
+/* The km S4 slots the hot path reads — replaces the reads at
+ * /root/reference/R/EI.grad.R:118-122, R/AKG.R:110-113,124, R/qEI.grad.R:78-83,
+ * R/kriging.quantile.grad.R:92-97, R/EI.R:84,86,109. */
+typedef struct {
+  int n, d, p;
+  int kernel;              /* DK_GAUSS ... DK_POWEXP  (covariance@name) */
+  int trend;               /* DK_TREND_CONST | DK_TREND_LINEAR (trend.formula) */
+  double sd2;              /* covariance@sd2 */
+  const double* theta;     /* covariance@range.val, d */
+  const double* shape;     /* covariance@shape.val, d (powexp) or NULL */
+  double nugget;           /* covariance@nugget */
+  int nugget_flag;         /* covariance@nugget.flag */
+  const double* noise_var; /* model@noise.var, n, or NULL */
+  const double* T;         /* model@T, n x n, upper Cholesky factor (only j<=i of column i read) */
+  const double* z;         /* model@z, n */
+  const double* M;         /* model@M, n x p */
+  const double* X;         /* model@X, n x d */
+  const double* y;         /* model@y, n */
+  const double* F;         /* model@F, n x p */
+  const double* beta;      /* model@trend.coef, p */
+  int device;              /* CUDA device ordinal the handle lives on */
+} dk_model_desc;
+
+/* Thread-local message of the last failing call. */
+const char* dk_last_error(void);
+/* Library / build identification string ("dk_b200 <ver> sm_100a"). */
+const char* dk_version(void);
+
+/* Upload the model, pre-tile the Cholesky factor for the DMMA solve, precompute the
+ * candidate-independent arrays (alpha = T^-1 z, T^-1 M, (M'M)^-1, chol(M'M), block inverses). */
+int dk_model_create(const dk_model_desc* desc, dk_model** out);
+void dk_model_destroy(dk_model* m);
+/* Device-memory bytes held by the handle (tiles + scratch). */
+size_t dk_model_device_bytes(const dk_model* m);
+/* Number of kernels launched through the handle so far (bench.py's gpu_launches). */
+long long dk_model_launches(const dk_model* m);
+
+/* predict.km(light.return=TRUE): mean and sd — replaces the DiceKriging call at
+ * /root/reference/R/EI.R:112-116 and R/sampleFromEI.R:109.  out_sd may be NULL. */
+int dk_predict(dk_model* m, const double* x, int64_t N, int type, double* out_mean, double* out_sd);
+int dk_predict_dev(dk_model* m, const double* d_x, int64_t N, int type, double* d_mean, double* d_sd,
+                   void* stream);
+
+/* EI(x, model, plugin, type, minimization, proxy) over an N x d matrix — replaces
+ * /root/reference/R/EI.R:80-145.  out_mean / out_sd (the envir values kriging.mean before
+ * the sign flip, kriging.sd) may be NULL. */
+int dk_ei(dk_model* m, const double* x, int64_t N, double plugin, int type, int minimization, int proxy,
+          double* out_ei, double* out_mean, double* out_sd);
+int dk_ei_dev(dk_model* m, const double* d_x, int64_t N, double plugin, int type, int minimization,
+              int proxy, double* d_ei, double* d_mean, double* d_sd, void* stream);
+
+/* EI.grad for every row of x (the reference evaluates one row per call) — replaces
+ * /root/reference/R/EI.grad.R:97-186.  out_grad is N x d; out_ei may be NULL. */
+int dk_ei_grad(dk_model* m, const double* x, int64_t N, double plugin, int type, int minimization,
+               int proxy, double* out_grad, double* out_ei);
+int dk_ei_grad_dev(dk_model* m, const double* d_x, int64_t N, double plugin, int type, int minimization,
+                   int proxy, double* d_grad, double* d_ei, void* stream);
+
+/* kriging.quantile / kriging.quantile.grad — replaces /root/reference/R/kriging.quantile.R:92-115
+ * and R/kriging.quantile.grad.R:83-138.  qnorm_beta = qnorm(beta) is computed by the caller
+ * (R's qnorm).  out_grad (N x d) may be NULL. */
+int dk_quantile(dk_model* m, const double* x, int64_t N, double qnorm_beta, int type, double* out_q,
+                double* out_grad);
+int dk_quantile_dev(dk_model* m, const double* d_x, int64_t N, double qnorm_beta, int type, double* d_q,
+                    double* d_grad, void* stream);
+
+/* The batched screen of /root/reference/R/max_crit.R:104-110: EI over N candidates and
+ * which.max (first maximal index, NaN skipped).  Returns the k best (value desc, index asc);
+ * out_idx are 0-based, -1 when fewer than k comparable values exist.  d_x is a DEVICE or HOST
+ * pointer according to x_on_device. */
+int dk_screen_ei(dk_model* m, const double* x, int x_on_device, int64_t N, double plugin, int type,
+                 int minimization, int proxy, int k, int64_t* out_idx, double* out_val, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DK_B200_H */

@@ -1,0 +1,231 @@
+"""Restatement of DiceOptim's acquisition criteria (the hot path), following
+/root/reference/R/*.R line by line, including guards and quirks.  numpy float64.
+
+pnorm/dnorm/qnorm are R's nmath (Cody 1969 / AS241): scipy.special.ndtr / ndtri agree with them
+to a few ulp (cross-checked against mpmath in tests/test_oracle_basic.py).
+"""
+from __future__ import annotations
+
+import numpy as np
+from scipy.linalg import solve_triangular
+from scipy.special import ndtr, ndtri
+
+from . import dicekriging as dk
+
+_INV_SQRT_2PI = 0.3989422804014326779399460599343818684758586311649
+
+
+def pnorm(x):
+    return ndtr(np.asarray(x, float))
+
+
+def dnorm(x):
+    x = np.asarray(x, float)
+    return _INV_SQRT_2PI * np.exp(-0.5 * x * x)
+
+
+def qnorm(p):
+    return ndtri(p)
+
+
+def _default_plugin(model, minimization):
+    # R/EI.R:82-88
+    return float(np.min(model.y)) if minimization else float(-np.max(model.y))
+
+
+def EI(x, model, plugin=None, type="UK", minimization=True, envir=None, proxy=False):
+    """R/EI.R:80-145.  x: vector (d) or N x d matrix; returns N values (IEEE semantics at sd=0)."""
+    if plugin is None:
+        plugin = _default_plugin(model, minimization)
+    m = plugin
+    x = np.atleast_2d(np.asarray(x, float))
+    if x.shape[1] != model.d:
+        raise ValueError("x does not have the right size")
+    predx = dk.predict_km(model, x, type=type, light_return=envir is None)
+    mean = predx["mean"]
+    if not minimization:
+        mean = -mean
+    sd = predx["sd"]
+    if proxy:
+        xcr = prob = dens = None
+        res = m - mean
+    else:
+        with np.errstate(divide="ignore", invalid="ignore"):
+            xcr = (m - mean) / sd
+            prob = pnorm(xcr)
+            dens = dnorm(xcr)
+            res = (m - mean) * prob + sd * dens
+    if envir is not None:
+        envir.update({"xcr": xcr, "xcr.prob": prob, "xcr.dens": dens, "kriging.sd": sd,
+                      "c": predx["c"], "Tinv.c": predx["Tinv.c"]})
+    return res
+
+
+def _mean_sd2_grad(x, model, type, v, c, sd_guard_zero):
+    """Shared W algebra of R/EI.grad.R:157-175 and R/kriging.quantile.grad.R:116-131."""
+    cov = model.covariance
+    T, z, u = model.T, model.z, model.M
+    Fn = dk.model_matrix(model.trend, x[None, :])
+    dc = dk.cov_vector_dx(cov, x, model.X, c)
+    fdx = dk.trend_deltax(model.trend, model.d)
+    W = solve_triangular(T, dc, trans="T", lower=False)
+    mean_grad = W.T @ z + (model.trend_coef @ fdx)
+    if sd_guard_zero:
+        return mean_grad, None
+    if type == "UK":
+        tuuinv = np.linalg.inv(u.T @ u)
+        sd2_grad = (-2.0 * v @ W + 2.0 * (Fn - v @ u) @ tuuinv @ (fdx - (W.T @ u).T)).ravel()
+    else:
+        sd2_grad = (-2.0 * v @ W).ravel()
+    return mean_grad, sd2_grad
+
+
+def EI_grad(x, model, plugin=None, type="UK", minimization=True, envir=None, proxy=False):
+    """R/EI.grad.R:97-186 at ONE point x (length d)."""
+    if plugin is None:
+        plugin = _default_plugin(model, minimization)
+    m = plugin
+    x = np.asarray(x, float).ravel()
+    d = x.size
+    if d != model.d:
+        raise ValueError("x does not have the right size")
+    predx = dk.predict_km(model, x[None, :], type=type)
+    mean = predx["mean"][0]
+    if not minimization:
+        mean = -mean
+    sd = predx["sd"][0]
+    v = predx["Tinv.c"][:, 0]; c = predx["c"][:, 0]
+    with np.errstate(divide="ignore", invalid="ignore"):
+        xcr = (m - mean) / sd
+    prob = pnorm(xcr); dens = dnorm(xcr)
+    if sd / np.sqrt(model.covariance.sd2) < 1e-6:          # R/EI.grad.R:153
+        return np.zeros(d)
+    mean_grad, sd2_grad = _mean_sd2_grad(x, model, type, v, c, sd_guard_zero=proxy)
+    if not minimization:
+        mean_grad = -mean_grad
+    if proxy:
+        return -mean_grad
+    sd_grad = sd2_grad / (2.0 * sd)
+    return -mean_grad * prob + sd_grad * dens
+
+
+def kriging_quantile(x, model, beta=0.1, type="UK", envir=None):
+    """R/kriging.quantile.R:92-115 (vectorised over rows like predict)."""
+    x = np.atleast_2d(np.asarray(x, float))
+    predx = dk.predict_km(model, x, type=type)
+    return predx["mean"] + qnorm(beta) * predx["sd"]
+
+
+def kriging_quantile_grad(x, model, beta=0.1, type="UK", envir=None):
+    """R/kriging.quantile.grad.R:83-138 at one point."""
+    x = np.asarray(x, float).ravel()
+    predx = dk.predict_km(model, x[None, :], type=type)
+    sk = predx["sd"][0]
+    v = predx["Tinv.c"][:, 0]; c = predx["c"][:, 0]
+    guard = sk < np.sqrt(model.covariance.sd2) / 1e6      # :123
+    mk_grad, sk2_grad = _mean_sd2_grad(x, model, type, v, c, sd_guard_zero=guard)
+    sk_grad = 0.0 if guard else sk2_grad / (2.0 * sk)
+    return mk_grad + qnorm(beta) * sk_grad
+
+
+def AKG(x, model, new_noise_var=0.0, type="UK", envir=None):
+    """R/AKG.R:93-229 at ONE point (approximate knowledge gradient, written for maximisation)."""
+    x = np.asarray(x, float).ravel()
+    if x.size != model.d:
+        raise ValueError("x does not have the right size")
+    tau2_new = new_noise_var
+    predx = dk.predict_km(model, x[None, :], type=type)
+    mk_x = predx["mean"][0]; sk_x = predx["sd"][0]
+    c_x = predx["c"][:, 0]; V_x = predx["Tinv.c"][:, 0]
+    U = model.M
+    F_x = dk.model_matrix(model.trend, x[None, :])
+    sd2 = model.covariance.sd2
+    if sk_x < np.sqrt(sd2) / 1e6 or sd2 < 1e-20:           # :115
+        return 0.0
+    predX = dk.predict_km(model, model.X, type=type)       # :121 (candidate independent)
+    mk_X = predX["mean"]; V_X = predX["Tinv.c"]
+    F_X = model.F
+    m_min = min(np.min(mk_X), mk_x)
+    if type == "UK":
+        tuuinv = np.linalg.inv(U.T @ U)
+        mu_x = ((F_X - V_X.T @ U) @ tuuinv @ (F_x - V_x[None, :] @ U).T).ravel()
+    else:
+        mu_x = 0.0
+    cn = c_x - V_X.T @ V_x + mu_x
+    cn = np.append(cn, sk_x ** 2)
+    A = np.append(mk_X, mk_x)
+    B = cn / np.sqrt(tau2_new + sk_x ** 2)
+    A = -A
+    return _akg_envelope(A, B, model.n) - (-m_min)
+
+
+def _akg_envelope(A, B, nobs):
+    """R/AKG.R:147-205: order(B, A), drop equal slopes, upper-envelope scan, Phi/phi sum."""
+    Isort = np.lexsort((A, B))                               # order(x=B, y=A)
+    b = B[Isort]; a = A[Isort]
+    keep = np.ones(b.size, bool)
+    for i in range(nobs):                                    # :153-157 (1-based i -> b[i+1]==b[i])
+        if b[i + 1] == b[i]:
+            keep[i] = False
+    b = b[keep]; a = a[keep]
+    nobs = a.size - 1
+    C = np.zeros(nobs + 2); C[0] = -1e36; C[-1] = 1e36
+    A1 = [0]
+    for k in range(2, nobs + 2):                             # R: k in 2:(nobs+1), 1-based
+        nondom = 1
+        if k == nobs + 1:
+            nondom = 1
+        elif a[k] >= a[k - 1] and b[k - 1] == b[k]:          # a[k+1]>=a[k] && b[k]==b[k+1]
+            nondom = 0
+        if nondom == 1:
+            loopdone = 0; count = 0
+            while loopdone == 0 and count < 1000:
+                count += 1
+                u = A1[-1] + 1                                # 1-based index into a/b
+                C[u] = (a[u - 1] - a[k - 1]) / (b[k - 1] - b[u - 1])   # C[u+1] 1-based
+                if len(A1) > 1 and C[u] <= C[A1[-2] + 1]:      # C[A1[len-1]+2] 1-based
+                    A1.pop()
+                else:
+                    A1.append(k - 1)
+                    loopdone = 1
+    A1 = np.asarray(A1)
+    at = a[A1]; bt = b[A1]
+    ct = C[np.concatenate(([0], A1 + 1))]
+    maxNew = 0.0
+    for k in range(at.size):
+        maxNew += at[k] * (pnorm(ct[k + 1]) - pnorm(ct[k])) + bt[k] * (dnorm(ct[k]) - dnorm(ct[k + 1]))
+    return float(maxNew)
+
+
+def which_max(v):
+    """R's which.max: first maximal index, NaN skipped; -1 if nothing comparable (R: integer(0))."""
+    v = np.asarray(v, float)
+    ok = ~np.isnan(v)
+    if not ok.any():
+        return -1
+    return int(np.flatnonzero(ok & (v == np.max(v[ok])))[0])
+
+
+def max_crit_screen(x, model, type="UK", minimization=True, proxy=False):
+    """The batched screen of R/max_crit.R:104-110: EI over the N x d matrix, which.max, value, row."""
+    ei = EI(x, model, plugin=None, type=type, minimization=minimization, envir=None, proxy=proxy)
+    I = which_max(ei)
+    return I, ei[I], np.atleast_2d(x)[I]
+
+
+def sample_from_EI_weights(x, model, minimization=True, T=None):
+    """The EI weights of R/sampleFromEI.R:109-132 (before the weighted sample())."""
+    x = np.atleast_2d(np.asarray(x, float))
+    pred = dk.predict_km(model, x, type="UK", light_return=True)
+    mn, sn = pred["mean"], pred["sd"]
+    if T is None:
+        T = np.min(model.y) if minimization else np.max(model.y)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        uu = (mn - T) / sn
+        if minimization:
+            uu = -uu
+        ei = sn * (uu * pnorm(uu) + dnorm(uu))
+    nan = np.isnan(ei)
+    ei[nan] = (T - mn)[nan] if minimization else (mn - T)[nan]
+    ei = ei * (ei > 0)
+    return ei

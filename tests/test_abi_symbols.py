@@ -1,0 +1,34 @@
+"""CPU: the C-ABI library loads and exports every symbol include/dk_b200.h declares (no compute)."""
+import ctypes
+import os
+import re
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "dk_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(dk_[a-z_0-9]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    import __graft_entry__ as g
+    g.build()
+    from diceoptim_b200 import _lib
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    names = _declared()
+    assert len(names) >= 12
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in dk_b200.h but not exported"
+    # and the binding table covers the header
+    assert set(names) <= set(_lib.SIGNATURES)
+
+
+def test_version_and_argument_errors_without_gpu():
+    from diceoptim_b200 import _lib
+    lib = _lib.load()
+    assert b"sm_100a" in lib.dk_version()
+    assert lib.dk_model_create(None, None) != 0
+    assert b"NULL" in lib.dk_last_error()
+    assert lib.dk_ei(None, None, 0, 0.0, 1, 1, 0, None, None, None) != 0

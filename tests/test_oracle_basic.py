@@ -1,0 +1,68 @@
+"""CPU tests of the oracle itself: the strongest pinning available without an R install
+(the reference ships no golden vectors; its self-validating examples are
+finite-difference and Monte-Carlo cross-checks, mirrored here)."""
+import mpmath
+import numpy as np
+import pytest
+
+from oracle import dicekriging as dk, diceoptim as do, testfuns
+from conftest import small_model, to_oracle
+
+
+def test_test_functions_match_reference_constants():
+    # R/hartman4.R:31, R/branin2.R:32-34, R/rosenbrock4.R:32-34
+    assert abs(testfuns.hartman4([0.1873, 0.1906, 0.5566, 0.2647])[0] - (-3.135474)) < 1e-6
+    assert abs(testfuns.rosenbrock4([0.4] * 4)[0] - (-1.019701)) < 1e-6
+    v = testfuns.branin2([[0.1239, 0.8183], [0.5428, 0.1517], [0.9617, 0.1650]])
+    assert np.all(np.abs(v - (-1.047410)) < 2e-5)
+
+
+def test_pnorm_dnorm_qnorm_against_mpmath():
+    mpmath.mp.dps = 40
+    for x in [-38.0, -20.0, -8.3, -3.0, -0.5, 0.0, 0.7, 2.5, 6.0, 8.2]:
+        ref = float(mpmath.ncdf(x))
+        assert do.pnorm(x) == pytest.approx(ref, rel=5e-14, abs=1e-300)
+        assert do.dnorm(x) == pytest.approx(float(mpmath.npdf(x)), rel=5e-13, abs=1e-300)
+    for p in [1e-10, 0.01, 0.1, 0.5, 0.9, 0.999]:
+        assert float(mpmath.ncdf(do.qnorm(p))) == pytest.approx(p, rel=1e-12)
+
+
+@pytest.mark.parametrize("name", dk.KERNELS)
+@pytest.mark.parametrize("trend", ["const", "linear"])
+def test_interpolation_and_gradients_by_finite_differences(name, trend):
+    m = to_oracle(small_model(name, trend, n=25, d=2, seed=3))
+    p = dk.predict_km(m, m.X[:5])
+    assert np.allclose(p["mean"], m.y[:5], atol=1e-8)
+    assert np.all(p["sd"] < 1e-5)
+    rng = np.random.default_rng(5)
+    for typ in ("UK", "SK"):
+        x = rng.random(2)
+        h = 1e-6
+        g = do.EI_grad(x, m, type=typ)
+        fd = np.array([(do.EI(x + h * e, m, type=typ)[0] - do.EI(x - h * e, m, type=typ)[0]) / (2 * h) for e in np.eye(2)])
+        assert np.allclose(g, fd, rtol=2e-5, atol=1e-9)
+        gq = do.kriging_quantile_grad(x, m, type=typ)
+        fdq = np.array([(do.kriging_quantile(x + h * e, m, type=typ)[0] - do.kriging_quantile(x - h * e, m, type=typ)[0]) / (2 * h)
+                        for e in np.eye(2)])
+        assert np.allclose(gq, fdq, rtol=2e-5, atol=1e-9)
+
+
+def test_ei_edge_semantics():
+    m = to_oracle(small_model(n=20, d=2))
+    ei = do.EI(m.X[:3], m)                       # at design points sd -> 0
+    assert np.all((ei >= 0) | np.isnan(ei))
+    x = np.random.default_rng(0).random((7, 2))
+    assert np.allclose(do.EI(x, m, proxy=True), np.min(m.y) - dk.predict_km(m, x)["mean"])
+    assert np.allclose(do.EI(x, m, minimization=False, plugin=-np.max(m.y)), do.EI(x, m, minimization=False))
+    assert do.which_max([np.nan, 1.0, 3.0, 3.0, np.nan]) == 2
+    assert do.which_max([np.nan, np.nan]) == -1
+
+
+def test_akg_runs_and_is_nonnegative():
+    from diceoptim_b200 import synth
+    X = synth.lhs(12, 2, 421)
+    rng = np.random.default_rng(421)
+    y = synth.branin2(X) + np.sqrt(0.2) * rng.standard_normal(12)
+    m = to_oracle(synth.make_km(X, y, "matern5_2", [0.4, 0.5], float(np.var(y)), noise_var=0.2))
+    vals = [do.AKG(x, m, new_noise_var=0.2) for x in rng.random((10, 2))]
+    assert all(np.isfinite(v) and v >= -1e-12 for v in vals)
