@@ -178,8 +178,10 @@ int launch_predict(dk_model* m, const CritParams& P, const double* d_x, int64_t 
   if (N == 0) return DK_OK;
   const int64_t ntiles = (N + BN - 1) / BN;
   const int grid = (int)std::min<int64_t>(ntiles, m->grid);
+  if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
   k_predict_fused<<<grid, NT, SM_TOTAL, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->scratch_doubles_per_cta,
                                                d_main, d_mean, d_sd);
+  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
   m->launches++;
   DK_CUDA_TRY(cudaGetLastError());
   return DK_OK;
@@ -192,8 +194,10 @@ int launch_grad(dk_model* m, const CritParams& P, const double* d_x, int64_t N, 
   if (rc) return rc;
   const int64_t ntiles = (N + BN - 1) / BN;
   const int grid = (int)std::min<int64_t>(ntiles, m->grid);
+  if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
   k_grad_fused<<<grid, NT, SM_TOTAL, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->d_wscratch,
                                             m->scratch_doubles_per_cta, d_grad, d_main);
+  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
   m->launches++;
   DK_CUDA_TRY(cudaGetLastError());
   return DK_OK;
@@ -379,6 +383,8 @@ void dk_model_destroy(dk_model* m) {
   cudaFree(m->d_tiles_fwd); cudaFree(m->d_tiles_bwd); cudaFree(m->d_Xrm); cudaFree(m->d_small);
   cudaFree(m->d_vscratch); cudaFree(m->d_wscratch); cudaFree(m->d_io); cudaFree(m->d_red);
   if (m->stream) cudaStreamDestroy(m->stream);
+  if (m->ev0) cudaEventDestroy(m->ev0);
+  if (m->ev1) cudaEventDestroy(m->ev1);
   std::free(m->h_T);
   std::free(m->h_zM);
   delete m;
@@ -386,6 +392,27 @@ void dk_model_destroy(dk_model* m) {
 
 size_t dk_model_device_bytes(const dk_model* m) { return m ? m->device_bytes : 0; }
 long long dk_model_launches(const dk_model* m) { return m ? m->launches : 0; }
+
+int dk_model_set_timing(dk_model* m, int on) {
+  if (!m) return fail(DK_ERR_ARG, "model handle is NULL");
+  DeviceGuard guard(m->device);
+  if (on && !m->ev0) {
+    DK_CUDA_TRY(cudaEventCreate(&m->ev0));
+    DK_CUDA_TRY(cudaEventCreate(&m->ev1));
+  }
+  m->timing = on ? 1 : 0;
+  m->ev_valid = false;
+  return DK_OK;
+}
+
+double dk_model_last_kernel_ms(dk_model* m) {
+  if (!m || !m->ev_valid) return -1.0;
+  DeviceGuard guard(m->device);
+  if (cudaEventSynchronize(m->ev1) != cudaSuccess) return -1.0;
+  float ms = -1.0f;
+  if (cudaEventElapsedTime(&ms, m->ev0, m->ev1) != cudaSuccess) return -1.0;
+  return (double)ms;
+}
 
 // ------------------------------------------------------------------------------------------
 // device-pointer entry points
@@ -528,7 +555,7 @@ int dk_screen_ei(dk_model* m, const double* x, int x_on_device, int64_t N, doubl
   if (k < 1 || k > DK_TOPK_MAX) return fail(DK_ERR_ARG, "k=%d outside 1..%d", k, DK_TOPK_MAX);
   if (!out_idx || !out_val) return fail(DK_ERR_ARG, "output pointer is NULL");
   DeviceGuard guard(m->device);
-  cudaStream_t st = x_on_device ? (cudaStream_t)stream : m->stream;
+  cudaStream_t st = stream ? (cudaStream_t)stream : (x_on_device ? (cudaStream_t) nullptr : m->stream);
   const size_t xin = x_on_device ? 0 : (size_t)N * m->d;
   if ((rc = ensure_io(m, xin + (size_t)N + 16))) return rc;
   const double* d_x = x;

@@ -122,4 +122,7 @@ struct dk_model {
   double* h_T = nullptr;         // n x n column-major copy (for the backward tiles)
   double* h_zM = nullptr;        // [z | M], n x (p+1) column-major
   long long launches = 0;        // kernels launched through this handle
+  int timing = 0;                // bracket the solve kernel with events
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  bool ev_valid = false;
 };

@@ -83,6 +83,10 @@ void dk_model_destroy(dk_model* m);
 size_t dk_model_device_bytes(const dk_model* m);
 /* Number of kernels launched through the handle so far (bench.py's gpu_launches). */
 long long dk_model_launches(const dk_model* m);
+/* Bracket the dominant (solve) kernel of every call with CUDA events on its launch stream (on = 0/1);
+ * dk_model_last_kernel_ms returns the device time of the most recent completed one, < 0 if none. */
+int dk_model_set_timing(dk_model* m, int on);
+double dk_model_last_kernel_ms(dk_model* m);
 
 /* predict.km(light.return=TRUE): mean and sd — replaces the DiceKriging call at
  * /root/reference/R/EI.R:112-116 and R/sampleFromEI.R:109.  out_sd may be NULL. */
