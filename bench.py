@@ -257,7 +257,8 @@ def main():
     achieved = flops_per_candidate(n, p) * N / (k_ms * 1e-3) * 1e-12
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get("k_predict_fused_bytes_per_launch")
+        # ncu capture (profiles/ncu_k_predict_fused_r01.md) gives DRAM bytes per candidate; one launch screens N of them
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json")))["k_predict_fused_bytes_per_candidate"] * N
     except Exception:
         pass
 
