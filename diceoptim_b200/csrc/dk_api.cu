@@ -609,3 +609,68 @@ int dk_debug_plain(dk_model* m, const double* x, int64_t N, int mode, double plu
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// Allocation-free EI entry point.
+//
+// Some hosts of this library may not allocate device memory once they are running: a serving
+// loop whose memory budget was fixed at start-up, code that runs under another framework's
+// memory pool (a raw cudaMalloc there synchronises the whole device and can fail although the
+// pool has room), or a step replayed at a steady cadence where an allocation stall is not
+// acceptable.  dk_ei_dev() is fine for them except for one thing: its V panels (the solve's
+// scratch) were cudaMalloc'ed by dk_model_create().  dk_ei_dev_noalloc() runs the same fused
+// kernel with the panels placed in the fixed array below instead, so a handle is not even
+// needed to own scratch and nothing is allocated or freed during the call.
+//
+// The array lives in every CUDA context that loads this library, from load until exit.  All
+// calls (all handles, all streams) on one device share it and it keeps whatever the previous
+// call left: the kernel writes every panel element of a tile before reading it, so nothing has
+// to be cleared, but two calls that overlap on the GPU would overwrite each other's panels.
+// ------------------------------------------------------------------------------------------
+#define DK_NOALLOC_SCRATCH_DOUBLES ((size_t)DK_NOALLOC_SCRATCH_BYTES / 8)
+static __device__ __align__(256) double g_noalloc_scratch[DK_NOALLOC_SCRATCH_DOUBLES];
+
+namespace {
+// g_noalloc_scratch is only a host-side stand-in for the symbol here; the kernel needs the device
+// address, looked up once per device (with that device current) and kept.
+double* g_noalloc_ptr[64] = {};
+
+int noalloc_scratch_address(int device, double** out) {
+  if (device < 0 || device >= 64) return dk::fail(DK_ERR_ARG, "device %d out of range for the fixed scratch table", device);
+  if (!g_noalloc_ptr[device]) {
+    double* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p)
+      return dk::fail(DK_ERR_CUDA, "cudaGetSymbolAddress(fixed scratch) on device %d: %s", device, cudaGetErrorString(e));
+    g_noalloc_ptr[device] = p;
+  }
+  *out = g_noalloc_ptr[device];
+  return DK_OK;
+}
+}  // namespace
+
+extern "C" int dk_ei_dev_noalloc(dk_model* m, const double* d_x, int64_t N, double plugin, int type, int minimization,
+                                 int proxy, double* d_ei, double* d_mean, double* d_sd, void* stream) {
+  int rc = check_call(m, d_x, N);
+  if (rc) return rc;
+  if (!d_ei) return fail(DK_ERR_ARG, "d_ei is NULL");
+  const size_t panel = m->scratch_doubles_per_cta;  // n_pad x 64 doubles: one CTA's V panel
+  if (panel > DK_NOALLOC_SCRATCH_DOUBLES)
+    return fail(DK_ERR_ARG,
+                "dk_ei_dev_noalloc: this model needs %zu bytes of scratch per CTA (n + p + 1 = %d rows padded to %d), "
+                "more than the fixed %zu-byte array; use dk_ei_dev",
+                panel * 8, m->dm.n_aug, m->dm.n_pad, (size_t)DK_NOALLOC_SCRATCH_BYTES);
+  DeviceGuard guard(m->device);
+  double* scratch = nullptr;
+  if ((rc = noalloc_scratch_address(m->device, &scratch))) return rc;
+  if (N == 0) return DK_OK;
+  const int64_t ntiles = (N + BN - 1) / BN;
+  const int64_t fit = (int64_t)(DK_NOALLOC_SCRATCH_DOUBLES / panel);  // CTAs whose panels fit the array
+  const int grid = (int)std::min<int64_t>(std::min<int64_t>(ntiles, m->grid), fit);
+  CritParams P{MODE_EI, type, minimization, proxy, plugin, 0.0};
+  k_predict_fused<<<grid, NT, SM_TOTAL, (cudaStream_t)stream>>>(m->dm, P, d_x, N, ntiles, scratch, panel, d_ei, d_mean,
+                                                                 d_sd);
+  m->launches++;
+  DK_CUDA_TRY(cudaGetLastError());
+  return DK_OK;
+}

@@ -124,6 +124,24 @@ int dk_quantile_dev(dk_model* m, const double* d_x, int64_t N, double qnorm_beta
 int dk_screen_ei(dk_model* m, const double* x, int x_on_device, int64_t N, double plugin, int type,
                  int minimization, int proxy, int k, int64_t* out_idx, double* out_val, void* stream);
 
+/* EI over device-resident candidates WITHOUT any device allocation (no counterpart in the reference:
+ * it exists for hosts that must not allocate once running, e.g. a serving loop with a memory budget fixed
+ * at start-up, or code living under another framework's memory pool where a raw cudaMalloc stalls the
+ * device and may fail).  Same arguments and results as dk_ei_dev; the solve's scratch (the per-CTA V
+ * panels) sits in a fixed DK_NOALLOC_SCRATCH_BYTES array inside the library instead of the handle's
+ * allocation.  Limits and rules:
+ *  - the model must satisfy  128*ceil((n+p+1)/128) * 64 * 8 <= DK_NOALLOC_SCRATCH_BYTES, else DK_ERR_ARG;
+ *    only as many CTAs run as have a panel in the array (n = 2000: 64 of 296), so large models run slower
+ *    here than through dk_ei_dev;
+ *  - every context that loads the library holds the array until it exits;
+ *  - the first call on a device looks up the array's device address; make that first call before any
+ *    stream capture begins;
+ *  - all calls on a device share the array: calls that overlap on the GPU (two streams, two handles) race.
+ *    Nothing needs clearing between calls (every panel element is written before it is read). */
+#define DK_NOALLOC_SCRATCH_BYTES (64u << 20)
+int dk_ei_dev_noalloc(dk_model* m, const double* d_x, int64_t N, double plugin, int type, int minimization,
+                      int proxy, double* d_ei, double* d_mean, double* d_sd, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
