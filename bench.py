@@ -191,24 +191,12 @@ def main():
     torch.cuda.set_stream(stream)
     sptr = C.c_void_p(stream.cuda_stream)
     idx = np.empty(1, dtype=np.int64); val = np.empty(1)
-    gather = [torch.empty(2, dtype=torch.float64, device="cuda") for _ in range(world)] if world > 1 else None
-    mine = torch.empty(2, dtype=torch.float64, device="cuda")
+    from diceoptim_b200 import parallel
 
     def global_argmax():
-        # (value, global index) pairs of all ranks; first maximum wins, lower rank on ties
-        if world == 1:
-            return int(idx[0]), float(val[0])
-        mine[0] = float(val[0]); mine[1] = float(rank * N + int(idx[0]))
-        dist.all_gather(gather, mine)
-        allv = torch.stack(gather).cpu().numpy()
-        best = None
-        for r in range(world):
-            v, gi = allv[r]
-            if gi - r * N < 0 or np.isnan(v):
-                continue
-            if best is None or v > best[1]:
-                best = (int(gi), float(v))
-        return best if best else (-1, float("nan"))
+        # all-gather of one (value, global index) pair per rank; first maximum wins
+        v, gi = parallel.global_argmax(float(val[0]), int(idx[0]), rank * N, device="cuda")
+        return gi, v
 
     def step(on_device):
         ptr = C.c_void_p(x_dev.data_ptr()) if on_device else C.c_void_p(x_host.data_ptr())
