@@ -173,3 +173,26 @@ def max_crit(model: KM, type="UK", lower=None, upper=None, minimization=True, co
         if best is None or value > best[1]:
             best = (np.asarray(par, float), float(value))
     return {"par": best[0], "value": best[1]}
+
+
+def qEI(x, model: KM, plugin=None, type="UK", minimization=True, fastCompute=True, eps=1e-5, envir=None, device=0):
+    """Multipoint expected improvement, R/qEI.R:119-194.  ``x`` is one batch (q x d) -> a scalar, or a
+    stack of batches (B x q x d) -> B values.  The engine evaluates the exact second term for both
+    values of ``fastCompute`` (the reference's fast path is a finite difference of it); ``eps`` is unused."""
+    x = np.asarray(x, dtype=np.float64)
+    single = x.ndim <= 2
+    if x.ndim <= 1:
+        x = x.reshape(-1, model.d)          # R: matrix(x, ncol = d)
+    if x.ndim == 2:
+        x = x[None]
+    B, q, d = x.shape
+    if d != model.d:
+        raise ValueError("x does not have the right size")
+    if plugin is None:                       # R/qEI.R:129-130 (max(y), not -max(y), when maximising)
+        plugin = float(np.min(model.y)) if minimization else float(np.max(model.y))
+    rows = np.asfortranarray(x.reshape(B * q, d))
+    out = np.empty(B)
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_qei(h.ptr, _vp(rows), B, q, float(plugin), _type_id(type), int(bool(minimization)),
+                                  _vp(out)), "dk_qei")
+    return float(out[0]) if single else out

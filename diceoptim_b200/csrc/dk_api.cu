@@ -382,6 +382,7 @@ void dk_model_destroy(dk_model* m) {
   cudaDeviceSynchronize();
   cudaFree(m->d_tiles_fwd); cudaFree(m->d_tiles_bwd); cudaFree(m->d_Xrm); cudaFree(m->d_small);
   cudaFree(m->d_vscratch); cudaFree(m->d_wscratch); cudaFree(m->d_io); cudaFree(m->d_red);
+  cudaFree(m->d_aux); cudaFree(m->d_mom);
   if (m->stream) cudaStreamDestroy(m->stream);
   if (m->ev0) cudaEventDestroy(m->ev0);
   if (m->ev1) cudaEventDestroy(m->ev1);
@@ -672,5 +673,91 @@ extern "C" int dk_ei_dev_noalloc(dk_model* m, const double* d_x, int64_t N, doub
                                                                  d_sd);
   m->launches++;
   DK_CUDA_TRY(cudaGetLastError());
+  return DK_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// qEI (R/qEI.R:119-261): batches of q <= DK_MAX_Q points
+// ------------------------------------------------------------------------------------------
+#include "dk_qei.cuh"
+
+namespace {
+bool g_qei_attr_done[64] = {};
+
+int ensure_qei(dk_model* m, int64_t B) {
+  if (m->device < 64 && !g_qei_attr_done[m->device]) {
+    DK_CUDA_TRY(cudaFuncSetAttribute(k_qei_moments, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+    g_qei_attr_done[m->device] = true;
+  }
+  if (!m->d_aux) {
+    int rc = dev_alloc(m, &m->d_aux, (size_t)m->grid * QEI_AUX_DOUBLES);
+    if (rc) return rc;
+  }
+  const size_t need = (size_t)std::max<int64_t>(B, 1) * MOM_STRIDE;
+  if (m->mom_doubles < need) {
+    if (m->d_mom) { cudaFree(m->d_mom); m->device_bytes -= m->mom_doubles * 8; m->d_mom = nullptr; m->mom_doubles = 0; }
+    int rc = dev_alloc(m, &m->d_mom, need);
+    if (rc) return rc;
+    m->mom_doubles = need;
+  }
+  return DK_OK;
+}
+
+}  // namespace
+
+extern "C" int dk_qei_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type, int minimization,
+                          double* d_out, void* stream) {
+  int rc = check_call(m, d_x, B);
+  if (rc) return rc;
+  if (q < 1 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI batch size q=%d outside 1..%d (deterministic CDFs are implemented up to dimension %d)", q, DK_MAX_Q, DK_MAX_Q);
+  if (!d_out) return fail(DK_ERR_ARG, "d_out is NULL");
+  if (B == 0) return DK_OK;
+  DeviceGuard guard(m->device);
+  if ((rc = ensure_qei(m, B))) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t ntiles = (B + QB - 1) / QB;
+  const int grid = (int)std::min<int64_t>(ntiles, m->grid);
+  if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
+  k_qei_moments<<<grid, NT, SM_TOTAL, st>>>(m->dm, type, q, d_x, B, ntiles, m->d_vscratch, m->scratch_doubles_per_cta,
+                                             m->d_aux, m->d_mom);
+  DK_CUDA_TRY(cudaGetLastError());
+  const int64_t threads = B * 4;
+  k_qei_cdf<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(m->d_mom, B, q, plugin, minimization, d_out);
+  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
+  m->launches += 2;
+  DK_CUDA_TRY(cudaGetLastError());
+  return DK_OK;
+}
+
+extern "C" int dk_qei(dk_model* m, const double* x, int64_t B, int q, double plugin, int type, int minimization,
+                      double* out) {
+  int rc = check_call(m, x, B);
+  if (rc) return rc;
+  if (q < 1 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI batch size q=%d outside 1..%d", q, DK_MAX_Q);
+  if (!out) return fail(DK_ERR_ARG, "out is NULL");
+  DeviceGuard guard(m->device);
+  HostCall h;
+  if ((rc = h.init(m, x, B * q, (size_t)B))) return rc;
+  if ((rc = dk_qei_dev(m, h.d_x, B, q, plugin, type, minimization, h.d_out, m->stream))) return rc;
+  if ((rc = h.fetch(out, h.d_out, B))) return rc;
+  return h.finish();
+}
+
+/* Test hook: pmnorm(h_b, varcov = S_b) for B independent q-variate problems (q <= 4), host pointers,
+ * device 0.  h is B x q row-major, S is B x q x q row-major. */
+extern "C" int dk_mvn_cdf(int q, int64_t B, const double* h, const double* S, double* out) {
+  if (q < 1 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "dimension q=%d outside 1..%d", q, DK_MAX_Q);
+  if (!h || !S || !out || B < 0) return fail(DK_ERR_ARG, "dk_mvn_cdf: bad argument");
+  if (B == 0) return DK_OK;
+  double *d_h = nullptr, *d_S = nullptr, *d_o = nullptr;
+  DK_CUDA_TRY(cudaMalloc(&d_h, B * q * 8));
+  DK_CUDA_TRY(cudaMalloc(&d_S, B * q * q * 8));
+  DK_CUDA_TRY(cudaMalloc(&d_o, B * 8));
+  DK_CUDA_TRY(cudaMemcpy(d_h, h, B * q * 8, cudaMemcpyHostToDevice));
+  DK_CUDA_TRY(cudaMemcpy(d_S, S, B * q * q * 8, cudaMemcpyHostToDevice));
+  k_mvn_cdf_test<<<(unsigned)((B + 63) / 64), 64>>>(q, B, d_h, d_S, d_o);
+  DK_CUDA_TRY(cudaGetLastError());
+  DK_CUDA_TRY(cudaMemcpy(out, d_o, B * 8, cudaMemcpyDeviceToHost));
+  cudaFree(d_h); cudaFree(d_S); cudaFree(d_o);
   return DK_OK;
 }

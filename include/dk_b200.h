@@ -124,6 +124,20 @@ int dk_quantile_dev(dk_model* m, const double* d_x, int64_t N, double qnorm_beta
 int dk_screen_ei(dk_model* m, const double* x, int x_on_device, int64_t N, double plugin, int type,
                  int minimization, int proxy, int k, int64_t* out_idx, double* out_val, void* stream);
 
+/* qEI(x, model, plugin, type, minimization) for B batches of q points — replaces
+ * /root/reference/R/qEI.R:119-261 (incl. covZk / get_cik / get_sigmaik and the duplicate test of
+ * R/qEI.R:124-128).  x is (B*q) x d column-major; rows b*q .. b*q+q-1 form batch b.  1 <= q <= DK_MAX_Q.
+ * plugin must be given (R default: min(y), or max(y) when !minimization, R/qEI.R:129-130).
+ * The q-variate normal CDFs (mnormt::pmnorm in the reference) are deterministic Genz bivariate /
+ * Plackett trivariate and quadrivariate rules; the exact second term is returned for fastCompute
+ * TRUE and FALSE alike. */
+int dk_qei(dk_model* m, const double* x, int64_t B, int q, double plugin, int type, int minimization, double* out);
+int dk_qei_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type, int minimization,
+               double* d_out, void* stream);
+/* pmnorm(h_b, varcov = S_b) for B independent q-variate problems (q <= DK_MAX_Q): the device CDFs behind
+ * dk_qei, exposed for parity tests against mnormt-class references.  h: B x q, S: B x q x q, row-major, host. */
+int dk_mvn_cdf(int q, int64_t B, const double* h, const double* S, double* out);
+
 /* EI over device-resident candidates WITHOUT any device allocation (no counterpart in the reference:
  * it exists for hosts that must not allocate once running, e.g. a serving loop with a memory budget fixed
  * at start-up, or code living under another framework's memory pool where a raw cudaMalloc stalls the

@@ -229,3 +229,119 @@ def sample_from_EI_weights(x, model, minimization=True, T=None):
     ei[nan] = (T - mn)[nan] if minimization else (mn - T)[nan]
     ei = ei * (ei > 0)
     return ei
+
+
+# ----------------------------------------------------------------------------------------
+# qEI (R/qEI.R:119-261)
+# ----------------------------------------------------------------------------------------
+def covZk(sigma, index):
+    """R/qEI.R:240-261: covariance of Z^(k) = (Y_k - Y_1, ..., -Y_k, ..., Y_k - Y_q)."""
+    q = sigma.shape[0]
+    res = sigma.copy()
+    for i in range(q):
+        if i != index:
+            res[index, i] = res[i, index] = sigma[index, index] - sigma[index, i]
+    for i in range(q):
+        for j in range(i, q):
+            if i != index and j != index:
+                res[i, j] = res[j, i] = sigma[i, j] + sigma[index, index] - sigma[index, i] - sigma[index, j]
+    return res
+
+
+def get_sigmaik(sigma, i):
+    """R/qEI.R:196-214."""
+    q = sigma.shape[0]
+    res = sigma - np.outer(sigma[:, i], sigma[:, i]) / sigma[i, i]
+    keep = [u for u in range(q) if u != i]
+    return res[np.ix_(keep, keep)]
+
+
+def get_cik(b, m, sigma, i):
+    """R/qEI.R:217-227."""
+    sigmai = sigma[i, :] / sigma[i, i]
+    res = (b - m) - (b[i] - m[i]) * sigmai
+    return np.delete(res, i)
+
+
+def r_round8(x):
+    """round(x, digits = 8) as used by the duplicate test R/qEI.R:126 (ties are immaterial here)."""
+    return np.round(np.asarray(x, float) * 1e8) / 1e8
+
+
+def qEI_dedup(x, model):
+    """R/qEI.R:124-128: rows of x that survive unique(round(rbind(X, x), 8)), in order."""
+    xr = r_round8(x)
+    seen = {tuple(r) for r in r_round8(model.X)}
+    keep = []
+    for j, row in enumerate(map(tuple, xr)):
+        if row not in seen:
+            seen.add(row)
+            keep.append(j)
+    return keep
+
+
+def qEI(x, model, plugin=None, type="UK", minimization=True, fastCompute=True, eps=1e-5, envir=None,
+        adaptive=False):
+    """R/qEI.R:119-194.  fastCompute=TRUE is the reference's finite-difference form of the second term,
+    fastCompute=FALSE the exact Chevalier-Ginsbourger double sum; both use oracle.mvnorm.pmnorm."""
+    from . import mvnorm as mv
+    d = model.d
+    x = np.asarray(x, float).reshape(-1, d)
+    keep = qEI_dedup(x, model)
+    if len(keep) == 0:
+        return 0.0
+    x = r_round8(x[keep])                                   # the reference continues with the ROUNDED rows
+    if plugin is None:
+        plugin = float(np.min(model.y)) if minimization else float(np.max(model.y))   # :129-130 (max, not -max)
+    if x.shape[0] == 1:
+        return float(EI(x, model, plugin=plugin, type=type, envir=envir)[0])          # :132-134 (minimization default)
+    krig = dk.predict_km(model, x, type=type, se_compute=False, cov_compute=True)
+    sigma, mu = krig["cov"], krig["mean"]
+    q = mu.size
+    pk = np.zeros(q); first = np.zeros(q); second = np.zeros(q)
+    sym = np.zeros((q, q)); nonsym = np.zeros((q, q))
+    for k in range(q):
+        Sk = covZk(sigma, k)
+        mu_k = mu - mu[k]; mu_k[k] = -mu[k]
+        if minimization:
+            mu_k = -mu_k
+        b_k = np.zeros(q); b_k[k] = -plugin
+        if minimization:
+            b_k = -b_k
+        pk[k] = mv.pmnorm(b_k - mu_k, varcov=Sk, adaptive=adaptive)
+        first[k] = (mu[k] - plugin) * pk[k]
+        if minimization:
+            first[k] = -first[k]
+        if fastCompute:
+            second[k] = (mv.pmnorm(b_k + eps * Sk[:, k] - mu_k, varcov=Sk, adaptive=adaptive) - pk[k]) / eps
+        else:
+            for i in range(q):
+                nonsym[k, i] = Sk[i, k]
+                if i >= k:
+                    phi_ik = dnorm((b_k[i] - mu_k[i]) / np.sqrt(Sk[i, i])) / np.sqrt(Sk[i, i])
+                    cik = get_cik(b_k, mu_k, Sk, i)
+                    sik = get_sigmaik(Sk, i)
+                    sym[k, i] = phi_ik * mv.pmnorm(cik, varcov=sik, adaptive=adaptive)
+    if not fastCompute:
+        sym = sym + sym.T
+        sym[np.diag_indices(q)] *= 0.5
+        second = np.sum(sym * nonsym)
+    if envir is not None:
+        envir.update({"pk": pk, "kriging.mean": mu, "kriging.cov": sigma})
+        if not fastCompute:
+            envir["symetric_term"] = sym
+    return float(np.sum(first) + np.sum(second))
+
+
+def qEI_monte_carlo(x, model, plugin=None, type="UK", minimization=True, nsim=300000, seed=0):
+    """The Monte-Carlo cross-check of the reference's example (R/qEI.R:89-104): mean of the
+    improvement of the batch minimum over draws of the conditional Gaussian vector."""
+    x = np.asarray(x, float).reshape(-1, model.d)
+    if plugin is None:
+        plugin = float(np.min(model.y)) if minimization else float(np.max(model.y))
+    krig = dk.predict_km(model, x, type=type, se_compute=False, cov_compute=True)
+    rng = np.random.default_rng(seed)
+    L = np.linalg.cholesky(krig["cov"] + 1e-14 * np.eye(x.shape[0]))
+    Y = krig["mean"][None, :] + rng.standard_normal((nsim, x.shape[0])) @ L.T
+    imp = np.maximum(plugin - Y.min(1), 0.0) if minimization else np.maximum(Y.max(1) - plugin, 0.0)
+    return float(imp.mean()), float(imp.std() / np.sqrt(nsim))

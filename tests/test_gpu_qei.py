@@ -1,0 +1,109 @@
+"""GPU parity of qEI (R/qEI.R) and of the device normal CDFs against the oracle, which runs the SAME
+deterministic rules (oracle/mvnorm.py).  Tolerances: CDFs 1e-12 absolute; qEI 1e-9 relative with an
+absolute floor of 1e-12 x the response scale (the two terms of the formula cancel for poor batches)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import small_model, to_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand_cov(rng, q):
+    A = rng.standard_normal((q, q + 1)); A[:, 0] *= rng.choice([0.3, 2.0, 6.0])
+    S = A @ A.T
+    return S * rng.uniform(0.2, 3.0)
+
+
+@pytest.mark.parametrize("q", [1, 2, 3, 4])
+def test_device_mvn_cdf_matches_oracle_rules(gpu_lib, q):
+    from oracle import mvnorm as mv
+    rng = np.random.default_rng(40 + q)
+    B = 150
+    S = np.stack([_rand_cov(rng, q) for _ in range(B)])
+    h = rng.standard_normal((B, q)) * 1.5 * np.sqrt(np.einsum("bii->bi", S))
+    out = np.empty(B)
+    rc = gpu_lib.dk_mvn_cdf(q, B, C.c_void_p(np.ascontiguousarray(h).ctypes.data),
+                            C.c_void_p(np.ascontiguousarray(S).ctypes.data), C.c_void_p(out.ctypes.data))
+    assert rc == 0, gpu_lib.dk_last_error()
+    ref = np.array([mv.pmnorm(h[b], varcov=S[b]) for b in range(B)])
+    assert np.max(np.abs(out - ref)) < 1e-12
+
+
+def _check_qei(km, xb, **kw):
+    from diceoptim_b200 import qEI
+    from oracle import diceoptim as do
+    ko = to_oracle(km)
+    got = qEI(xb, km, **kw)
+    ref = np.array([do.qEI(xb[b], ko, fastCompute=False, **kw) for b in range(xb.shape[0])])
+    scale = np.max(np.abs(km.y)) + np.sqrt(km.covariance.sd2)
+    assert np.all(np.abs(got - ref) <= 1e-9 * np.abs(ref) + 1e-12 * scale), np.max(np.abs(got - ref))
+    return got, ref
+
+
+@pytest.mark.parametrize("q", [2, 3, 4])
+@pytest.mark.parametrize("trend,type", [("const", "UK"), ("const", "SK"), ("linear", "UK")])
+def test_qei_matches_oracle(gpu_lib, q, trend, type):
+    km = small_model("matern5_2", trend, n=140, d=3, seed=50 + q)
+    rng = np.random.default_rng(q)
+    xb = rng.random((40, q, 3))
+    plugin = float(np.median(km.y))                 # a reachable target: EI terms of order 0.1
+    got, ref = _check_qei(km, xb, plugin=plugin, type=type)
+    assert np.all(ref > 0)
+    _check_qei(km, xb[:10], type=type)             # default plugin = min(y)
+    _check_qei(km, xb[:10], plugin=plugin, type=type, minimization=False)
+    km.release()
+
+
+def test_qei_single_batch_and_other_kernels(gpu_lib):
+    from diceoptim_b200 import qEI
+    from oracle import diceoptim as do
+    for name in ("gauss", "exp", "matern3_2", "powexp"):
+        km = small_model(name, "const", n=60, d=2, seed=3, noise_var=0.01 if name == "gauss" else None)
+        x = np.random.default_rng(1).random((3, 2))
+        got = qEI(x, km, plugin=float(np.median(km.y)))
+        assert isinstance(got, float)
+        ref = do.qEI(x, to_oracle(km), plugin=float(np.median(km.y)), fastCompute=False)
+        assert abs(got - ref) <= 1e-9 * abs(ref) + 1e-12
+        km.release()
+
+
+def test_qei_duplicates_follow_reference_unique_rule(gpu_lib):
+    """R/qEI.R:124-134: points equal (to 8 digits) to a design row or to an earlier batch point are dropped;
+    nothing left -> 0; one left -> EI."""
+    from diceoptim_b200 import qEI
+    from oracle import diceoptim as do
+    km = small_model("matern5_2", "const", n=50, d=2, seed=9)
+    ko = to_oracle(km)
+    rng = np.random.default_rng(4)
+    plugin = float(np.median(km.y))
+    fresh = rng.random((4, 2))
+    cases = [
+        np.vstack([km.X[3], fresh[0], fresh[1], fresh[2]]),            # one design row  -> q' = 3
+        np.vstack([fresh[0], fresh[0] + 1e-10, fresh[1], fresh[2]]),   # in-batch duplicate after rounding
+        np.vstack([km.X[0], km.X[1], km.X[2], fresh[3]]),              # q' = 1 -> EI
+        np.vstack([km.X[0], km.X[1], km.X[2], km.X[3]]),               # all duplicates -> 0
+    ]
+    xb = np.stack(cases)
+    got = qEI(xb, km, plugin=plugin)
+    ref = np.array([do.qEI(c, ko, plugin=plugin, fastCompute=False) for c in cases])
+    assert got[3] == 0.0 and ref[3] == 0.0
+    assert np.all(np.abs(got - ref) <= 1e-9 * np.abs(ref) + 1e-12)
+    with pytest.raises(Exception):
+        qEI(rng.random((5, 2)), km)                                      # q = 5 > DK_MAX_Q: refused loudly
+    km.release()
+
+
+def test_qei_against_monte_carlo(gpu_lib):
+    """The reference's own cross-check (R/qEI.R:89-104): qEI vs the mean improvement over draws."""
+    from diceoptim_b200 import qEI
+    from oracle import diceoptim as do
+    km = small_model("matern5_2", "const", n=80, d=3, seed=13)
+    x = np.random.default_rng(2).random((4, 3))
+    plugin = float(np.median(km.y))
+    got = qEI(x, km, plugin=plugin)
+    mc, se = do.qEI_monte_carlo(x, to_oracle(km), plugin=plugin, nsim=400000)
+    assert abs(got - mc) < 5 * se + 1e-6
+    km.release()
