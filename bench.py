@@ -283,6 +283,40 @@ def main():
         gfl = (2 * n * n + 2 * n * d + 4 * n) * Ng / (gms * 1e-3) * 1e-12
         line["extra"] = {"ei_grad_candidates_per_s": Ng / (gms * 1e-3), "ei_grad_batch": Ng,
                          "ei_grad_tflops_algorithmic": gfl, "ei_grad_frac_of_peak": gfl / peak}
+        # qEI (q = 4) on BASELINE config 3: rosenbrock4 km, n = 500, 10^5 batches; device-resident batches
+        km3 = synth.config_model("cfg3_rosenbrock4_n500")
+        h3 = km3.handle(local)
+        Bq, q = 100_000, 4
+        xq = torch.rand((km3.d, Bq * q), dtype=torch.float64, device="cuda")
+        oq = torch.empty(Bq, dtype=torch.float64, device="cuda")
+        pl3 = float(np.median(km3.y))
+        def qstep():
+            _lib.check(lib.dk_qei_dev(h3.ptr, C.c_void_p(xq.data_ptr()), Bq, q, pl3, 1, 1, C.c_void_p(oq.data_ptr()), sptr),
+                       "dk_qei_dev")
+        qstep(); torch.cuda.synchronize()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record(stream); qstep(); qstep(); qstep(); e1.record(stream); torch.cuda.synchronize()
+        qms = e0.elapsed_time(e1) / 3
+        line["extra"].update({"qei_q4_evals_per_s": Bq / (qms * 1e-3), "qei_batches": Bq, "qei_model": "cfg3 n=500 d=4 matern5_2",
+                              "qei_ms": qms, "qei_nan": int(torch.isnan(oq).sum().item())})
+        km3.release()
+        # AKG + kriging.quantile on BASELINE config 5: d = 20, n = 5000, noise.var = 0.1
+        km5 = synth.config_model("cfg5_noisy20_n5000")
+        h5 = km5.handle(local)
+        lib.dk_model_set_timing(h5.ptr, 1)
+        Na = 1 << 16
+        xa = torch.rand((km5.d, Na), dtype=torch.float64, device="cuda")
+        oa = torch.empty(Na, dtype=torch.float64, device="cuda")
+        for name, call in (("akg", lambda: lib.dk_akg_dev(h5.ptr, C.c_void_p(xa.data_ptr()), Na, 0.1, 1, C.c_void_p(oa.data_ptr()), sptr)),
+                           ("quantile", lambda: lib.dk_quantile_dev(h5.ptr, C.c_void_p(xa.data_ptr()), Na, -1.2815515655446004, 1,
+                                                                    C.c_void_p(oa.data_ptr()), None, sptr))):
+            _lib.check(call(), name); torch.cuda.synchronize()
+            _lib.check(call(), name); torch.cuda.synchronize()
+            ms5 = lib.dk_model_last_kernel_ms(h5.ptr)
+            fl5 = (2 if name == "akg" else 1) * km5.n ** 2 * Na / (ms5 * 1e-3) * 1e-12
+            line["extra"].update({f"{name}_n5000_candidates_per_s": Na / (ms5 * 1e-3), f"{name}_n5000_tflops_algorithmic": fl5,
+                                  f"{name}_n5000_finite": bool(torch.isfinite(oa).all().item())})
+        km5.release()
 
     if rank == 0:
         # CPU baseline: the oracle port on a bounded sample of the same workload, host cores

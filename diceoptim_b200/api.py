@@ -196,3 +196,16 @@ def qEI(x, model: KM, plugin=None, type="UK", minimization=True, fastCompute=Tru
     _lib.check(_lib.load().dk_qei(h.ptr, _vp(rows), B, q, float(plugin), _type_id(type), int(bool(minimization)),
                                   _vp(out)), "dk_qei")
     return float(out[0]) if single else out
+
+
+def AKG(x, model: KM, new_noise_var=0.0, type="UK", envir=None, device=0):
+    """Approximate knowledge gradient, R/AKG.R:93-229.  A length-d ``x`` gives a scalar (the reference's
+    contract); an N x d matrix gives N values from one launch (the noisy DOE scans of
+    R/noisy.optimizer.R:456-457 become one call)."""
+    single = np.asarray(x).ndim <= 1
+    x = _as_candidates(x, model.d)
+    N = x.shape[0]
+    out = np.empty(N)
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_akg(h.ptr, _vp(x), N, float(new_noise_var), _type_id(type), _vp(out)), "dk_akg")
+    return float(out[0]) if single else out

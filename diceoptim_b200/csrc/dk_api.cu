@@ -355,6 +355,16 @@ int dk_model_create(const dk_model_desc* D, dk_model** out) {
     m->h_zM = (double*)std::malloc((size_t)n * (p + 1) * 8);
     if (!m->h_zM) return bail(fail(DK_ERR_NOMEM, "host allocation failed"));
     std::memcpy(m->h_zM, &small[o_zM], (size_t)n * (p + 1) * 8);
+    if (D->y) {
+      m->h_y = (double*)std::malloc((size_t)n * 8);
+      if (!m->h_y) return bail(fail(DK_ERR_NOMEM, "host allocation failed"));
+      std::memcpy(m->h_y, D->y, (size_t)n * 8);
+    }
+    if (D->noise_var) {
+      m->h_nv = (double*)std::malloc((size_t)n * 8);
+      if (!m->h_nv) return bail(fail(DK_ERR_NOMEM, "host allocation failed"));
+      std::memcpy(m->h_nv, D->noise_var, (size_t)n * 8);
+    }
 
     // host copy of T for the lazily built backward tiles
     m->h_T = (double*)std::malloc((size_t)n * n * 8);
@@ -388,6 +398,9 @@ void dk_model_destroy(dk_model* m) {
   if (m->ev1) cudaEventDestroy(m->ev1);
   std::free(m->h_T);
   std::free(m->h_zM);
+  std::free(m->h_y);
+  std::free(m->h_nv);
+  cudaFree(m->d_akg_const); cudaFree(m->d_akg_perm); cudaFree(m->d_akg_scratch);
   delete m;
 }
 
@@ -760,4 +773,84 @@ extern "C" int dk_mvn_cdf(int q, int64_t B, const double* h, const double* S, do
   DK_CUDA_TRY(cudaMemcpy(out, d_o, B * 8, cudaMemcpyDeviceToHost));
   cudaFree(d_h); cudaFree(d_S); cudaFree(d_o);
   return DK_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// AKG (R/AKG.R:93-229)
+// ------------------------------------------------------------------------------------------
+#include "dk_akg.cuh"
+
+namespace {
+bool g_akg_attr_done[64] = {};
+
+int ensure_akg(dk_model* m) {
+  if (m->device < 64 && !g_akg_attr_done[m->device]) {
+    DK_CUDA_TRY(cudaFuncSetAttribute(k_akg_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+    g_akg_attr_done[m->device] = true;
+  }
+  if (m->d_akg_const) return DK_OK;
+  const int n = m->n;
+  if (!m->h_y) return fail(DK_ERR_ARG, "AKG needs model@y (dk_model_desc.y was NULL)");
+  std::vector<double> alpha(n), cst(2 * (size_t)n), a(n);
+  DK_CUDA_TRY(cudaMemcpy(alpha.data(), m->dm.alpha, (size_t)n * 8, cudaMemcpyDeviceToHost));
+  // mk.X = y - delta .* alpha (predict.km at the design, hoisted out of R/AKG.R:121)
+  double min_mkX = INFINITY;
+  for (int i = 0; i < n; i++) {
+    const double delta = m->h_nv ? m->h_nv[i] : 0.0;
+    const double mkX = m->h_y[i] - delta * alpha[i];
+    a[i] = -mkX;
+    cst[n + i] = delta;
+    min_mkX = std::min(min_mkX, mkX);
+  }
+  std::vector<int> perm(n);
+  for (int i = 0; i < n; i++) perm[i] = i;
+  std::stable_sort(perm.begin(), perm.end(), [&](int u, int v) { return a[u] < a[v]; });
+  for (int j = 0; j < n; j++) cst[j] = a[perm[j]];
+  int rc = dev_alloc(m, &m->d_akg_const, cst.size());
+  if (rc) return rc;
+  if ((rc = dev_alloc(m, &m->d_akg_perm, (size_t)n))) return rc;
+  DK_CUDA_TRY(cudaMemcpy(m->d_akg_const, cst.data(), cst.size() * 8, cudaMemcpyHostToDevice));
+  DK_CUDA_TRY(cudaMemcpy(m->d_akg_perm, perm.data(), (size_t)n * 4, cudaMemcpyHostToDevice));
+  if ((rc = dev_alloc(m, &m->d_akg_scratch, (size_t)m->grid * akg_scratch_doubles(n)))) return rc;
+  m->dm.akg_a_sorted = m->d_akg_const;
+  m->dm.akg_delta = m->d_akg_const + n;
+  m->dm.akg_perm = m->d_akg_perm;
+  m->dm.akg_min_mkX = min_mkX;
+  return DK_OK;
+}
+}  // namespace
+
+extern "C" int dk_akg_dev(dk_model* m, const double* d_x, int64_t N, double new_noise_var, int type, double* d_out,
+                          void* stream) {
+  int rc = check_call(m, d_x, N);
+  if (rc) return rc;
+  if (!d_out) return fail(DK_ERR_ARG, "d_out is NULL");
+  if (m->n + 1 > AKG_MAX_SORT) return fail(DK_ERR_ARG, "AKG: n + 1 = %d exceeds the %d keys the in-kernel sort holds", m->n + 1, AKG_MAX_SORT);
+  if (!(new_noise_var >= 0)) return fail(DK_ERR_ARG, "new.noise.var must be >= 0");
+  if (N == 0) return DK_OK;
+  DeviceGuard guard(m->device);
+  if ((rc = ensure_bwd(m))) return rc;
+  if ((rc = ensure_akg(m))) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t ntiles = (N + BN - 1) / BN;
+  const int grid = (int)std::min<int64_t>(ntiles, m->grid);
+  if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
+  k_akg_fused<<<grid, NT, SM_TOTAL, st>>>(m->dm, type, new_noise_var, d_x, N, ntiles, m->d_vscratch, m->d_wscratch,
+                                           m->scratch_doubles_per_cta, m->d_akg_scratch, d_out);
+  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
+  m->launches++;
+  DK_CUDA_TRY(cudaGetLastError());
+  return DK_OK;
+}
+
+extern "C" int dk_akg(dk_model* m, const double* x, int64_t N, double new_noise_var, int type, double* out) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (!out) return fail(DK_ERR_ARG, "out is NULL");
+  DeviceGuard guard(m->device);
+  HostCall h;
+  if ((rc = h.init(m, x, N, (size_t)N))) return rc;
+  if ((rc = dk_akg_dev(m, h.d_x, N, new_noise_var, type, h.d_out, m->stream))) return rc;
+  if ((rc = h.fetch(out, h.d_out, N))) return rc;
+  return h.finish();
 }

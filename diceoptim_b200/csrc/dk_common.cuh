@@ -69,6 +69,11 @@ struct DevModel {
   const double* KinvF;      // T^-1 M, n x p column-major
   const double* Mcm;        // model@M, n x p column-major
   const double* noise_var;  // n or NULL
+  // AKG constants (built lazily): design lines sorted by a_i = -mk.X_i
+  const double* akg_a_sorted;  // n, ascending
+  const double* akg_delta;     // n: noise.var (0 for nugget / noise-free models)
+  const int* akg_perm;         // n: design row with the j-th smallest a
+  double akg_min_mkX;          // min_i mk.X_i
   double w[DK_MAX_D];       // per-dimension scale of |h|: 1/theta (gauss, exp, powexp), sqrt3/theta, sqrt5/theta
   double shape[DK_MAX_D];   // powexp exponents
   double theta[DK_MAX_D];
@@ -124,6 +129,11 @@ struct dk_model {
   int n = 0, d = 0, p = 0;
   double* h_T = nullptr;         // n x n column-major copy (for the backward tiles)
   double* h_zM = nullptr;        // [z | M], n x (p+1) column-major
+  double* h_y = nullptr;         // n
+  double* h_nv = nullptr;        // n noise.var or NULL
+  double* d_akg_const = nullptr; // a_sorted | delta
+  int* d_akg_perm = nullptr;
+  double* d_akg_scratch = nullptr;
   long long launches = 0;        // kernels launched through this handle
   int timing = 0;                // bracket the solve kernel with events
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;

@@ -124,6 +124,11 @@ int dk_quantile_dev(dk_model* m, const double* d_x, int64_t N, double qnorm_beta
 int dk_screen_ei(dk_model* m, const double* x, int x_on_device, int64_t N, double plugin, int type,
                  int minimization, int proxy, int k, int64_t* out_idx, double* out_val, void* stream);
 
+/* AKG(x, model, new.noise.var, type) for every row of x (the reference evaluates one row per call and
+ * re-predicts at the whole design each time) — replaces /root/reference/R/AKG.R:93-229.  Needs n + 1 <= 8192. */
+int dk_akg(dk_model* m, const double* x, int64_t N, double new_noise_var, int type, double* out);
+int dk_akg_dev(dk_model* m, const double* d_x, int64_t N, double new_noise_var, int type, double* d_out, void* stream);
+
 /* qEI(x, model, plugin, type, minimization) for B batches of q points — replaces
  * /root/reference/R/qEI.R:119-261 (incl. covZk / get_cik / get_sigmaik and the duplicate test of
  * R/qEI.R:124-128).  x is (B*q) x d column-major; rows b*q .. b*q+q-1 form batch b.  1 <= q <= DK_MAX_Q.

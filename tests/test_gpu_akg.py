@@ -1,0 +1,64 @@
+"""GPU parity of the batched AKG (R/AKG.R) against the oracle's line-by-line restatement.  The engine uses
+the exact identity cn = noise.var .* T^-1 (v + M r) where the reference subtracts two nearly equal vectors,
+so agreement is at the level of the reference's own rounding: 1e-8 relative + 1e-11 of the response scale."""
+import numpy as np
+import pytest
+
+from conftest import small_model, to_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(km, x, tau2, type="UK", rtol=1e-8):
+    from diceoptim_b200 import AKG
+    from oracle import diceoptim as do
+    ko = to_oracle(km)
+    got = AKG(x, km, new_noise_var=tau2, type=type)
+    ref = np.array([do.AKG(xi, ko, new_noise_var=tau2, type=type) for xi in x])
+    scale = np.max(np.abs(km.y)) + np.sqrt(km.covariance.sd2)
+    assert np.all(np.abs(got - ref) <= rtol * np.abs(ref) + 1e-11 * scale), (np.max(np.abs(got - ref)), ref[:5], got[:5])
+    return got, ref
+
+
+@pytest.mark.parametrize("trend,type", [("const", "UK"), ("const", "SK"), ("linear", "UK")])
+@pytest.mark.parametrize("n", [12, 150])
+def test_akg_noise_var_model(gpu_lib, trend, type, n):
+    rng = np.random.default_rng(n)
+    km = small_model("matern5_2", trend, n=n, d=2, seed=421, noise_var=0.02 + 0.03 * rng.random(n))
+    x = rng.random((90, 2))
+    got, ref = _check(km, x, tau2=0.02, type=type)
+    assert np.all(got >= -1e-12) and np.max(ref) > 1e-4
+    _check(km, x[:20], tau2=0.0, type=type)       # new.noise.var = 0 (default)
+    km.release()
+
+
+def test_akg_other_kernels_and_single_point(gpu_lib):
+    from diceoptim_b200 import AKG
+    rng = np.random.default_rng(3)
+    for name in ("gauss", "exp", "matern3_2", "powexp"):
+        km = small_model(name, "const", n=40, d=3, seed=7, noise_var=0.05)
+        x = rng.random((33, 3))
+        got, _ = _check(km, x, tau2=0.05)
+        assert isinstance(AKG(x[0], km, new_noise_var=0.05), float)
+        assert AKG(x[0], km, new_noise_var=0.05) == got[0]
+        km.release()
+
+
+def test_akg_nugget_and_noise_free_models_values_only(gpu_lib):
+    """With a homogeneous nugget (or no noise) the reference's cn is rounding noise around mu.x; the slopes'
+    order is not reproducible but the AKG value is."""
+    rng = np.random.default_rng(5)
+    x = rng.random((60, 2))
+    kn = small_model("matern5_2", "const", n=30, d=2, seed=2, nugget=0.05)
+    _check(kn, x, tau2=0.05, type="SK", rtol=1e-7)
+    _check(kn, x, tau2=0.05, type="UK", rtol=1e-7)
+    kd = small_model("matern5_2", "const", n=30, d=2, seed=2)
+    _check(kd, x, tau2=0.01, type="SK", rtol=1e-7)
+    kn.release(); kd.release()
+
+
+def test_akg_zero_at_design_points_and_size_limit(gpu_lib):
+    from diceoptim_b200 import AKG
+    km = small_model("matern5_2", "const", n=25, d=2, seed=1)          # noise-free: sk.x = 0 at the design
+    assert np.all(AKG(km.X[:5], km, new_noise_var=0.1) == 0.0)          # guard of R/AKG.R:115
+    km.release()
