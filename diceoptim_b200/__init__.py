@@ -7,7 +7,7 @@ DiceKriging; ``synth`` only builds km objects with FIXED hyper-parameters for te
 """
 from .km import KM, Covariance, DeviceModel  # noqa: F401
 from .api import (AKG, EI, EI_grad, kriging_quantile, kriging_quantile_grad, max_crit, predict, qEI,  # noqa: F401
-                  screen_EI)
+                  sampleFromEI, screen_EI)
 
 __all__ = ["AKG", "KM", "Covariance", "DeviceModel", "EI", "EI_grad", "kriging_quantile", "kriging_quantile_grad",
-           "max_crit", "predict", "qEI", "screen_EI"]
+           "max_crit", "predict", "qEI", "sampleFromEI", "screen_EI"]

@@ -52,6 +52,8 @@ SIGNATURES = {
     "dk_quantile": (_I, [_V, _V, _L, _D, _I, _V, _V]),
     "dk_quantile_dev": (_I, [_V, _V, _L, _D, _I, _V, _V, _V]),
     "dk_screen_ei": (_I, [_V, _V, _I, _L, _D, _I, _I, _I, _I, _V, _V, _V]),
+    "dk_sample_weights": (_I, [_V, _V, _L, _D, _I, _V]),
+    "dk_sample_weights_dev": (_I, [_V, _V, _L, _D, _I, _V, _V]),
     "dk_akg": (_I, [_V, _V, _L, _D, _I, _V]),
     "dk_akg_dev": (_I, [_V, _V, _L, _D, _I, _V, _V]),
     "dk_qei": (_I, [_V, _V, _L, _I, _D, _I, _I, _V]),

@@ -209,3 +209,36 @@ def AKG(x, model: KM, new_noise_var=0.0, type="UK", envir=None, device=0):
     h = model.handle(device)
     _lib.check(_lib.load().dk_akg(h.ptr, _vp(x), N, float(new_noise_var), _type_id(type), _vp(out)), "dk_akg")
     return float(out[0]) if single else out
+
+
+def randLHS(n, k, rng):
+    """R/sampleFromEI.R:143-149: random Latin hypercube (numpy RNG instead of R's runif)."""
+    perm = np.argsort(rng.random((n, k)), axis=0)
+    return (perm + rng.random((n, k))) / n
+
+
+def sampleFromEI(model: KM, minimization=True, n=1, initdistrib=None, lower=None, upper=None, T=None, seed=None,
+                 device=0):
+    """R/sampleFromEI.R:77-141: draw ``n`` points with probability proportional to EI among 1000 d LHS points
+    (or ``initdistrib``).  The prediction + weight screen runs on the GPU; the weighted draw without
+    replacement uses numpy's generator in place of R's sample()."""
+    d = model.d
+    lower = np.zeros(d) if lower is None else np.asarray(lower, float)
+    upper = np.ones(d) if upper is None else np.asarray(upper, float)
+    if lower.size != upper.size:
+        raise ValueError("Error in samplefromEI : lower and upper must have the same length")
+    rng = np.random.default_rng(seed)
+    pts = lower + randLHS(1000 * d, d, rng) * (upper - lower) if initdistrib is None else np.asarray(initdistrib, float)
+    pts = _as_candidates(pts, d)
+    N = pts.shape[0]
+    if T is None:
+        T = float(np.min(model.y)) if minimization else float(np.max(model.y))
+    ei = np.empty(N)
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_sample_weights(h.ptr, _vp(pts), N, float(T), int(bool(minimization)), _vp(ei)),
+               "dk_sample_weights")
+    if np.count_nonzero(ei) < n:                             # R/sampleFromEI.R:126-133
+        mx = ei.max()
+        ei = ei / mx + 1.0 / (1000 * d) if mx > 0 else np.ones(N)
+    idx = rng.choice(N, size=n, replace=False, p=ei / ei.sum())
+    return np.asarray(pts[idx]).reshape(n, d)

@@ -854,3 +854,28 @@ extern "C" int dk_akg(dk_model* m, const double* x, int64_t N, double new_noise_
   if ((rc = h.fetch(out, h.d_out, N))) return rc;
   return h.finish();
 }
+
+// ------------------------------------------------------------------------------------------
+// sampleFromEI's candidate screen (R/sampleFromEI.R:109-125): EI-proportional sampling weights
+// ------------------------------------------------------------------------------------------
+extern "C" int dk_sample_weights_dev(dk_model* m, const double* d_x, int64_t N, double T, int minimization, double* d_w,
+                                     void* stream) {
+  int rc = check_call(m, d_x, N);
+  if (rc) return rc;
+  if (!d_w) return fail(DK_ERR_ARG, "d_w is NULL");
+  DeviceGuard guard(m->device);
+  CritParams P{MODE_EI_WEIGHT, DK_UK, minimization, 0, T, 0.0};  // the reference hard-codes type = "UK" here
+  return launch_predict(m, P, d_x, N, d_w, nullptr, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int dk_sample_weights(dk_model* m, const double* x, int64_t N, double T, int minimization, double* out_w) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (!out_w) return fail(DK_ERR_ARG, "out_w is NULL");
+  DeviceGuard guard(m->device);
+  HostCall h;
+  if ((rc = h.init(m, x, N, (size_t)N))) return rc;
+  if ((rc = dk_sample_weights_dev(m, h.d_x, N, T, minimization, h.d_out, m->stream))) return rc;
+  if ((rc = h.fetch(out_w, h.d_out, N))) return rc;
+  return h.finish();
+}

@@ -79,7 +79,7 @@ struct DevModel {
   double theta[DK_MAX_D];
 };
 
-enum Mode { MODE_PREDICT = 0, MODE_EI = 1, MODE_QUANTILE = 2 };
+enum Mode { MODE_PREDICT = 0, MODE_EI = 1, MODE_QUANTILE = 2, MODE_EI_WEIGHT = 3 };
 
 struct CritParams {
   int mode, type, minimization, proxy;

@@ -263,6 +263,14 @@ __device__ __forceinline__ void cand_predict(const DevModel& M, int type, const 
 __device__ __forceinline__ double crit_value(const CritParams& P, double mean, double sd) {
   if (P.mode == MODE_PREDICT) return mean;
   if (P.mode == MODE_QUANTILE) return mean + P.qnorm_beta * sd;
+  if (P.mode == MODE_EI_WEIGHT) {
+    // sampleFromEI's sampling weight (R/sampleFromEI.R:119-125): sn (u Phi(u) + phi(u)), NaN -> +-(T - mn), clipped at 0
+    double uu = (mean - P.plugin) / sd;
+    if (P.minimization) uu = -uu;
+    double ei = sd * (uu * normcdf(uu) + dnorm_std(uu));
+    if (ei != ei) ei = P.minimization ? (P.plugin - mean) : (mean - P.plugin);
+    return ei > 0.0 ? ei : 0.0;
+  }
   const double km = P.minimization ? mean : -mean;
   const double diff = P.plugin - km;
   if (P.proxy) return diff;

@@ -124,6 +124,12 @@ int dk_quantile_dev(dk_model* m, const double* d_x, int64_t N, double qnorm_beta
 int dk_screen_ei(dk_model* m, const double* x, int x_on_device, int64_t N, double plugin, int type,
                  int minimization, int proxy, int k, int64_t* out_idx, double* out_val, void* stream);
 
+/* The candidate screen of sampleFromEI — replaces /root/reference/R/sampleFromEI.R:109-125: the
+ * EI-proportional sampling weight sn (u Phi(u) + phi(u)) of every row (type "UK" as in the reference,
+ * NaN -> +-(T - mn), clipped at 0).  The weighted draw itself (R's sample()) stays on the host. */
+int dk_sample_weights(dk_model* m, const double* x, int64_t N, double T, int minimization, double* out_w);
+int dk_sample_weights_dev(dk_model* m, const double* d_x, int64_t N, double T, int minimization, double* d_w, void* stream);
+
 /* AKG(x, model, new.noise.var, type) for every row of x (the reference evaluates one row per call and
  * re-predicts at the whole design each time) — replaces /root/reference/R/AKG.R:93-229.  Needs n + 1 <= 8192. */
 int dk_akg(dk_model* m, const double* x, int64_t N, double new_noise_var, int type, double* out);

@@ -187,3 +187,25 @@ def test_cfg4_shape_subsample(gpu_lib):
     got, ref = check_ei(km, x)
     assert int(np.nanargmax(got)) == int(np.nanargmax(ref))
     km.release()
+
+
+def test_sample_from_ei_weights_and_draw(gpu_lib):
+    """R/sampleFromEI.R:109-135: weights vs the oracle (incl. NaN -> T - mn at zero-sd points), draw shape."""
+    import ctypes as C
+    from diceoptim_b200 import sampleFromEI, _lib
+    from oracle import diceoptim as do
+    km = small_model("matern5_2", "const", n=60, d=3, seed=17)
+    pts = np.vstack([np.random.default_rng(8).random((500, 3)), km.X[:4]])
+    for minimization in (True, False):
+        T = float(np.median(km.y))
+        w = np.empty(pts.shape[0]); xf = np.asfortranarray(pts)
+        _lib.check(gpu_lib.dk_sample_weights(km.handle(0).ptr, C.c_void_p(xf.ctypes.data), pts.shape[0], T, int(minimization),
+                                             C.c_void_p(w.ctypes.data)), "dk_sample_weights")
+        with np.errstate(all="ignore"):
+            ref = do.sample_from_EI_weights(pts, to_oracle(km), minimization=minimization, T=T)
+        assert np.all(w >= 0) and not np.isnan(w).any()
+        assert np.all(np.abs(w - ref) <= 1e-9 * np.abs(ref) + 1e-12 * np.max(ref))
+    out = sampleFromEI(km, n=7, seed=3)
+    assert out.shape == (7, 3) and np.all((out >= 0) & (out <= 1))
+    assert sampleFromEI(km, n=1, seed=3, initdistrib=pts).shape == (1, 3)
+    km.release()
