@@ -58,6 +58,8 @@ SIGNATURES = {
     "dk_akg_dev": (_I, [_V, _V, _L, _D, _I, _V, _V]),
     "dk_qei": (_I, [_V, _V, _L, _I, _D, _I, _I, _V]),
     "dk_qei_dev": (_I, [_V, _V, _L, _I, _D, _I, _I, _V, _V]),
+    "dk_qei_grad": (_I, [_V, _V, _L, _I, _D, _I, _I, _V]),
+    "dk_qei_grad_dev": (_I, [_V, _V, _L, _I, _D, _I, _I, _V, _V]),
     "dk_mvn_cdf": (_I, [_I, _L, _V, _V, _V]),
     "dk_ei_dev_noalloc": (_I, [_V, _V, _L, _D, _I, _I, _I, _V, _V, _V, _V]),
 }

@@ -242,3 +242,66 @@ def sampleFromEI(model: KM, minimization=True, n=1, initdistrib=None, lower=None
         ei = ei / mx + 1.0 / (1000 * d) if mx > 0 else np.ones(N)
     idx = rng.choice(N, size=n, replace=False, p=ei / ei.sum())
     return np.asarray(pts[idx]).reshape(n, d)
+
+
+def qEI_grad(x, model: KM, plugin=None, type="UK", minimization=True, fastCompute=True, eps=1e-6, envir=None, device=0):
+    """Gradient of qEI with respect to the batch, R/qEI.grad.R:267-424: q x d for one batch, B x q x d for a
+    stack.  q = 1 is routed to EI.grad as the reference does."""
+    x = np.asarray(x, dtype=np.float64)
+    single = x.ndim <= 2
+    if x.ndim <= 1:
+        x = x.reshape(-1, model.d)
+    if x.ndim == 2:
+        x = x[None]
+    B, q, d = x.shape
+    if d != model.d:
+        raise ValueError("x does not have the right size")
+    if plugin is None:                       # R/qEI.grad.R:272-276, 297
+        plugin = float(np.min(model.y)) if minimization else -float(np.max(model.y))
+    if q == 1:
+        if not minimization:
+            raise ValueError("qEI.grad doesn't work in 'minimization = FALSE' when dim = 1 (in progress).")
+        g = np.asarray(EI_grad(x[:, 0, :], model, plugin=plugin, type=type, device=device)).reshape(B, 1, d)
+        return g[0] if single else g
+    rows = np.asfortranarray(x.reshape(B * q, d))
+    out = np.empty((B * q, d), order="F")
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_qei_grad(h.ptr, _vp(rows), B, q, float(plugin), _type_id(type), int(bool(minimization)),
+                                       _vp(out)), "dk_qei_grad")
+    g = np.ascontiguousarray(out).reshape(B, q, d)
+    return g[0] if single else g
+
+
+def max_qEI(model: KM, npoints, lower, upper, crit="exact", minimization=True, optimcontrol=None, seed=None, device=0):
+    """R/max_qEI.R:176-225, crit = "exact", optimcontrol$method = "BFGS": nStarts L-BFGS-B runs of qEI / qEI.grad
+    from batches drawn by sampleFromEI; the best run wins.  All nStarts start batches are scored in ONE qEI launch
+    first.  crit = "CL" (constant liar) and method = "genoud" need DiceKriging's model update / rgenoud and stay
+    outside the engine."""
+    from scipy.optimize import minimize
+    if crit != "exact":
+        raise NotImplementedError("max_qEI(crit='CL') relies on DiceKriging model updates, which stay in R")
+    oc = dict(optimcontrol or {})
+    if oc.get("method", "BFGS") != "BFGS":
+        raise NotImplementedError("only optimcontrol$method = 'BFGS' is served")
+    d = model.d
+    lower = np.asarray(lower, float); upper = np.asarray(upper, float)
+    n_starts = int(oc.get("nStarts", 4))
+    fast = bool(oc.get("fastCompute", True))
+    start = oc.get("parinit")
+    if start is None:                                         # R/max_qEI.R:204
+        start = sampleFromEI(model, minimization=minimization, n=npoints * n_starts, lower=lower, upper=upper,
+                             seed=seed, device=device).reshape(n_starts, npoints, d)
+    start = np.asarray(start, float).reshape(-1, npoints, d)
+    lo = np.tile(lower, npoints); up = np.tile(upper, npoints)
+    plugin_v = float(np.min(model.y)) if minimization else float(np.max(model.y))
+    plugin_g = float(np.min(model.y)) if minimization else -float(np.max(model.y))
+    best = None
+    for s in range(start.shape[0]):
+        f = lambda t: -qEI(t.reshape(npoints, d), model, plugin=plugin_v, minimization=minimization, fastCompute=fast, device=device)
+        g = lambda t: -qEI_grad(t.reshape(npoints, d), model, plugin=plugin_g, minimization=minimization, fastCompute=fast,
+                                device=device).ravel()
+        res = minimize(f, start[s].ravel(), jac=g, method="L-BFGS-B", bounds=list(zip(lo, up)),
+                       options={"maxiter": int(oc.get("maxit", 100))})
+        if best is None or -res.fun > best[1]:
+            best = (res.x.reshape(npoints, d), float(-res.fun))
+    return {"par": best[0], "value": best[1]}

@@ -392,7 +392,7 @@ void dk_model_destroy(dk_model* m) {
   cudaDeviceSynchronize();
   cudaFree(m->d_tiles_fwd); cudaFree(m->d_tiles_bwd); cudaFree(m->d_Xrm); cudaFree(m->d_small);
   cudaFree(m->d_vscratch); cudaFree(m->d_wscratch); cudaFree(m->d_io); cudaFree(m->d_red);
-  cudaFree(m->d_aux); cudaFree(m->d_mom);
+  cudaFree(m->d_aux); cudaFree(m->d_mom); cudaFree(m->d_deriv);
   if (m->stream) cudaStreamDestroy(m->stream);
   if (m->ev0) cudaEventDestroy(m->ev0);
   if (m->ev1) cudaEventDestroy(m->ev1);
@@ -753,6 +753,57 @@ extern "C" int dk_qei(dk_model* m, const double* x, int64_t B, int q, double plu
   if ((rc = h.init(m, x, B * q, (size_t)B))) return rc;
   if ((rc = dk_qei_dev(m, h.d_x, B, q, plugin, type, minimization, h.d_out, m->stream))) return rc;
   if ((rc = h.fetch(out, h.d_out, B))) return rc;
+  return h.finish();
+}
+
+extern "C" int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type,
+                               int minimization, double* d_grad, void* stream) {
+  int rc = check_call(m, d_x, B);
+  if (rc) return rc;
+  if (q < 2 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI.grad batch size q=%d outside 2..%d (use dk_ei_grad for q = 1)", q, DK_MAX_Q);
+  if (!d_grad) return fail(DK_ERR_ARG, "d_grad is NULL");
+  if (B == 0) return DK_OK;
+  DeviceGuard guard(m->device);
+  if ((rc = ensure_bwd(m))) return rc;
+  if ((rc = ensure_qei(m, B))) return rc;
+  static bool attr_done[64] = {};
+  if (m->device < 64 && !attr_done[m->device]) {
+    DK_CUDA_TRY(cudaFuncSetAttribute(k_qei_grad_moments, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+    attr_done[m->device] = true;
+  }
+  const size_t need = (size_t)B * qei_deriv_stride(m->d);
+  if (m->deriv_doubles < need) {
+    if (m->d_deriv) { cudaFree(m->d_deriv); m->device_bytes -= m->deriv_doubles * 8; m->d_deriv = nullptr; m->deriv_doubles = 0; }
+    if ((rc = dev_alloc(m, &m->d_deriv, need))) return rc;
+    m->deriv_doubles = need;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t ntiles = (B + QB - 1) / QB;
+  const int grid = (int)std::min<int64_t>(ntiles, m->grid);
+  if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
+  k_qei_grad_moments<<<grid, NT, SM_TOTAL, st>>>(m->dm, type, q, d_x, B, ntiles, m->d_vscratch, m->d_wscratch,
+                                                  m->scratch_doubles_per_cta, m->d_aux, m->d_mom, m->d_deriv);
+  DK_CUDA_TRY(cudaGetLastError());
+  const int64_t threads = B * 4;
+  k_qei_grad_cdf<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(m->d_mom, m->d_deriv, B, q, m->d, plugin, minimization,
+                                                                   m->dm.sd2, d_grad);
+  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
+  m->launches += 2;
+  DK_CUDA_TRY(cudaGetLastError());
+  return DK_OK;
+}
+
+extern "C" int dk_qei_grad(dk_model* m, const double* x, int64_t B, int q, double plugin, int type, int minimization,
+                           double* out_grad) {
+  int rc = check_call(m, x, B);
+  if (rc) return rc;
+  if (q < 2 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI.grad batch size q=%d outside 2..%d (use dk_ei_grad for q = 1)", q, DK_MAX_Q);
+  if (!out_grad) return fail(DK_ERR_ARG, "out_grad is NULL");
+  DeviceGuard guard(m->device);
+  HostCall h;
+  if ((rc = h.init(m, x, B * q, (size_t)B * q * m->d))) return rc;
+  if ((rc = dk_qei_grad_dev(m, h.d_x, B, q, plugin, type, minimization, h.d_out, m->stream))) return rc;
+  if ((rc = h.fetch(out_grad, h.d_out, (size_t)B * q * m->d))) return rc;
   return h.finish();
 }
 

@@ -116,6 +116,8 @@ struct dk_model {
   double* d_aux = nullptr;       // per-CTA Gram accumulators of the qEI kernel
   double* d_mom = nullptr;       // per-batch (mu, Sigma, mask) of the qEI kernels, grow-only
   size_t mom_doubles = 0;
+  double* d_deriv = nullptr;     // per-batch kriging derivatives of the qEI.grad kernels, grow-only
+  size_t deriv_doubles = 0;
   size_t scratch_doubles_per_cta = 0;
   int grid = 0;
   // grow-only staging for the host entry points

@@ -23,7 +23,8 @@ constexpr int COEF_DOUBLES = COEF_ROWS * BN;
 template <int KERNEL>
 __device__ __forceinline__ void grad_accumulate(const DevModel& M, const double* __restrict__ xs,
                                                 const double* __restrict__ wpanel, int c, int slice, double cA,
-                                                double cW, double (&g)[DK_MAX_D]) {
+                                                double cW, double (&g)[DK_MAX_D], int cw = -1) {
+  if (cw < 0) cw = c;  // column of the W panel that supplies the weights (qEI.grad pairs point c with point cw)
   const int n = M.n, d = M.d;
 #pragma unroll 1
   for (int i = slice; i < n; i += 4) {
@@ -39,7 +40,7 @@ __device__ __forceinline__ void grad_accumulate(const DevModel& M, const double*
       else if (KERNEL == DK_MATERN5_2) { pr *= fma(a, fma(a, 1.0 / 3.0, 1.0), 1.0); s += a; }
       else s += pow(a, M.shape[k]);
     }
-    const double omega = cA * __ldg(M.alpha + i) + cW * panel_at(wpanel, n - 1 - i, c);
+    const double omega = cA * __ldg(M.alpha + i) + cW * panel_at(wpanel, n - 1 - i, cw);
     const double cw = M.sd2 * pr * exp(-s) * omega;
     // covVector.dx: c_i * d log k / d x_k
 #pragma unroll

@@ -145,6 +145,14 @@ int dk_akg_dev(dk_model* m, const double* d_x, int64_t N, double new_noise_var, 
 int dk_qei(dk_model* m, const double* x, int64_t B, int q, double plugin, int type, int minimization, double* out);
 int dk_qei_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type, int minimization,
                double* d_out, void* stream);
+/* qEI.grad for B batches of q points (2 <= q <= DK_MAX_Q; q = 1 is dk_ei_grad) — replaces
+ * /root/reference/R/qEI.grad.R:267-424 with krigingDeriv / decompo / GPhi / HPhi (:1-142).  out_grad is
+ * (B*q) x d column-major, row b*q + l = gradient with respect to point l of batch b.  plugin must be given
+ * (R default: min(y), or -max(y) when !minimization, R/qEI.grad.R:272-276,297).  Exact term B for both
+ * values of fastCompute. */
+int dk_qei_grad(dk_model* m, const double* x, int64_t B, int q, double plugin, int type, int minimization, double* out_grad);
+int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type, int minimization,
+                    double* d_grad, void* stream);
 /* pmnorm(h_b, varcov = S_b) for B independent q-variate problems (q <= DK_MAX_Q): the device CDFs behind
  * dk_qei, exposed for parity tests against mnormt-class references.  h: B x q, S: B x q x q, row-major, host. */
 int dk_mvn_cdf(int q, int64_t B, const double* h, const double* S, double* out);

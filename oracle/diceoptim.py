@@ -345,3 +345,162 @@ def qEI_monte_carlo(x, model, plugin=None, type="UK", minimization=True, nsim=30
     Y = krig["mean"][None, :] + rng.standard_normal((nsim, x.shape[0])) @ L.T
     imp = np.maximum(plugin - Y.min(1), 0.0) if minimization else np.maximum(Y.max(1) - plugin, 0.0)
     return float(imp.mean()), float(imp.std() / np.sqrt(nsim))
+
+
+# ----------------------------------------------------------------------------------------
+# qEI.grad (R/qEI.grad.R:1-142, 267-424)
+# ----------------------------------------------------------------------------------------
+def _decompo(x, mu, Sigma, k, adaptive=False):
+    """R/qEI.grad.R:1-26: density of the components k times the CDF of the rest given them."""
+    from . import mvnorm as mv
+    x = np.asarray(x, float).ravel(); mu = np.asarray(mu, float).ravel()
+    k = list(np.atleast_1d(k))
+    q = x.size
+    if len(k) == q:
+        return mv.dmnorm(x, mu, Sigma)
+    rest = [u for u in range(q) if u not in k]
+    x1 = x[k]; x2 = x[rest]; mu1 = mu[k]
+    S22 = Sigma[np.ix_(rest, rest)]; S21 = Sigma[np.ix_(rest, k)]; S11 = Sigma[np.ix_(k, k)]
+    S11inv = np.linalg.inv(S11)
+    varcov = S22 - S21 @ S11inv @ S21.T
+    varcov = 0.5 * (varcov + varcov.T)
+    dg = np.diag(varcov).copy()
+    if dg.min() <= 0:
+        varcov[np.diag_indices_from(varcov)] = dg * (dg >= 0) + 1e-9
+    moy = mu[rest] + S21 @ S11inv @ (x1 - mu1)
+    return mv.dmnorm(x1, mu1, S11) * mv.pmnorm(x2, mean=moy, varcov=varcov, adaptive=adaptive)
+
+
+def GPhi(x, mu, Sigma, adaptive=False):
+    """R/qEI.grad.R:29-36: gradient of the q-variate normal CDF."""
+    q = np.asarray(x).size
+    return np.array([_decompo(x, mu, Sigma, [i], adaptive) for i in range(q)])
+
+
+def HPhi(x, mu, Sigma, gradient=None, adaptive=False):
+    """R/qEI.grad.R:39-60: Hessian of the q-variate normal CDF."""
+    x = np.asarray(x, float).ravel(); mu = np.asarray(mu, float).ravel()
+    Sigma = np.atleast_2d(np.asarray(Sigma, float))
+    q = x.size
+    if q == 1:
+        s = np.sqrt(Sigma[0, 0])
+        return np.array([[-(x[0] - mu[0]) / Sigma[0, 0] * dnorm((x[0] - mu[0]) / s) / s]])
+    res = np.zeros((q, q))
+    for i in range(q - 1):
+        for j in range(i + 1, q):
+            res[i, j] = _decompo(x, mu, Sigma, [i, j], adaptive)
+    res = res + res.T
+    if gradient is None:
+        gradient = GPhi(x, mu, Sigma, adaptive)
+    res = res - np.diag(((x - mu) * np.asarray(gradient).ravel() + np.diag(Sigma @ res)) / np.diag(Sigma))
+    return res
+
+
+def kriging_deriv(x, model, type="UK"):
+    """R/qEI.grad.R:62-142 (krigingDeriv): derivatives of the conditional mean and covariance of a batch.
+    mean_jacob[l, j, k] = d m_k / d x_lj ; cov_jacob[l, j, k, i] = d Sigma_ki / d x_lj."""
+    x = np.asarray(x, float)
+    q, d = x.shape
+    T, z, u, cov = model.T, model.z, model.M, model.covariance
+    Fn = dk.model_matrix(model.trend, x)
+    pred = dk.predict_km(model, x, type=type, se_compute=False, cov_compute=True)
+    mean, kcov, v, c = pred["mean"], pred["cov"], pred["Tinv.c"], pred["c"]
+    if np.prod(np.diag(kcov) / cov.sd2 < 1e-8):              # :107 (all of them tiny)
+        return None
+    mj = np.zeros((q, d, q)); cj = np.zeros((q, d, q, q))
+    tuuinv = np.linalg.inv(u.T @ u)
+    covM = dk.cov_matrix(cov, x)
+    fdx = dk.trend_deltax(model.trend, d)
+    for k in range(q):
+        dc = dk.cov_vector_dx(cov, x[k], model.X, c[:, k])
+        W = solve_triangular(T, dc, trans="T", lower=False)
+        mj[k, :, k] = z @ W + model.trend_coef @ fdx
+        for l in range(q):
+            kg = dk.cov_vector_dx(cov, x[k], x[l][None, :], np.array([covM[k, l]])).ravel()
+            cj[k, :, k, l] = kg - v[:, l] @ W
+            if type == "UK":
+                cj[k, :, k, l] += ((fdx.T - W.T @ u) @ tuuinv @ (Fn[l] - v[:, l] @ u)).ravel()
+    for l in range(q):
+        for j in range(d):
+            cj[l, j] = cj[l, j] + cj[l, j].T
+    return mean, mj, kcov, cj
+
+
+def qEI_grad(x, model, plugin=None, type="UK", minimization=True, fastCompute=True, eps=1e-6, envir=None,
+             adaptive=False):
+    """R/qEI.grad.R:267-424.  Returns the q x d gradient matrix."""
+    from . import mvnorm as mv
+    if not minimization and plugin is None:
+        plugin = -float(np.max(model.y))
+    d = model.d
+    x = np.asarray(x, float).reshape(-1, d)
+    q = x.shape[0]
+    xb = np.vstack([model.X, x])
+    if len({tuple(r) for r in r_round8(xb)}) != xb.shape[0]:   # :293-295 any duplicate -> zero matrix
+        return np.zeros((q, d))
+    if plugin is None:
+        plugin = float(np.min(model.y))
+    if q == 1:
+        if not minimization:
+            raise ValueError("qEI.grad doesn't work in 'minimization = FALSE' when dim = 1 (in progress).")
+        return EI_grad(x[0], model, plugin=plugin, type=type)[None, :]
+    kd = kriging_deriv(x, model, type=type)
+    if kd is None:
+        return np.zeros((q, d))
+    kmean, mj, kcov, cj = kd
+    if not minimization:
+        kmean = -kmean; mj = -mj
+    G = np.zeros((q, d))
+    b = np.zeros(q)
+    L = -np.eye(q)
+    for k in range(q):
+        bk = b.copy(); bk[k] = plugin
+        Lk = L.copy(); Lk[:, k] = 1.0
+        mk = Lk @ kmean
+        Sigk = Lk @ kcov @ Lk.T
+        Sigk = 0.5 * (Sigk + Sigk.T)
+        pk = mv.pmnorm(bk, mean=mk, varcov=Sigk, adaptive=adaptive)
+        G[k] -= mj[k, :, k] * pk                                            # term A1
+        gradpk = GPhi(bk - mk, b, Sigk, adaptive)
+        hesspk = HPhi(bk, mk, Sigk, gradpk, adaptive)
+        Sdx = np.einsum("ab,ljbc,dc->ljad", Lk, cj, Lk)                      # Lk %*% cov.jacob[l,j,,] %*% t(Lk)
+        mdx = np.einsum("ab,ljb->lja", Lk, mj)
+        Dpk = 0.5 * np.einsum("ab,ljab->lj", hesspk, Sdx) - np.einsum("a,lja->lj", gradpk, mdx)
+        G += (plugin - kmean[k]) * Dpk                                      # term A2
+        if fastCompute:
+            gradpk1 = GPhi(bk - mk + Sigk[:, k] * eps, b, Sigk, adaptive)
+            hesspk1 = HPhi(bk + Sigk[:, k] * eps, mk, Sigk, gradpk1, adaptive)
+            f1 = (-np.einsum("lja,a->lj", mdx, gradpk1) + eps * np.einsum("lja,a->lj", Sdx[:, :, :, k], gradpk1)
+                  + 0.5 * np.einsum("ljab,ab->lj", Sdx, hesspk1))
+            f = -np.einsum("lja,a->lj", mdx, gradpk) + 0.5 * np.einsum("ljab,ab->lj", Sdx, hesspk)
+            G += (f1 - f) / eps
+        else:
+            B = np.zeros((q, d))
+            for i in range(q):
+                oth = [u for u in range(q) if u != i]
+                S_ik, S_ii, mk_i, bk_i = Sigk[i, k], Sigk[i, i], mk[i], bk[i]
+                S_mi = Sigk[oth, i]
+                ck_pi = bk[oth] - mk[oth] - (bk_i - mk_i) / S_ii * S_mi
+                A = Sigk[np.ix_(oth, oth)] - np.outer(S_mi, S_mi) / S_ii
+                S_pi = 0.5 * (A + A.T)
+                phi_ik = dnorm((bk_i - mk_i) / np.sqrt(S_ii)) / np.sqrt(S_ii)
+                dphi_dS = ((bk_i - mk_i) ** 2 / (2 * S_ii ** 2) - 0.5 / S_ii) * phi_ik
+                dphi_dm = (bk_i - mk_i) / S_ii * phi_ik
+                Phi_ik = mv.pmnorm(ck_pi, varcov=S_pi, adaptive=adaptive)
+                G_ik = GPhi(ck_pi, np.zeros(q - 1), S_pi, adaptive)
+                H_ik = HPhi(ck_pi, np.zeros(q - 1), S_pi, G_ik, adaptive)
+                for l in range(q):
+                    for j in range(d):
+                        sdx = Sdx[l, j]
+                        B1 = sdx[i, k] * phi_ik * Phi_ik
+                        B2 = S_ik * (mdx[l, j, i] * dphi_dm + dphi_dS * sdx[i, i]) * Phi_ik
+                        dck = (-mdx[l, j, oth] + (mdx[l, j, i] * S_ii + (bk_i - mk_i) * sdx[i, i]) / S_ii ** 2 * S_mi
+                               - (bk_i - mk_i) / S_ii * sdx[oth, i])
+                        cross = np.outer(sdx[oth, i], S_mi)
+                        dS = sdx[np.ix_(oth, oth)] + sdx[i, i] / S_ii ** 2 * np.outer(S_mi, S_mi) - (cross + cross.T) / S_ii
+                        B3 = S_ik * phi_ik * (G_ik @ dck + 0.5 * np.sum(H_ik * dS))
+                        B[l, j] += B1 + B2 + B3
+            G += B
+    if np.isnan(G.sum()):
+        return np.zeros((q, d))
+    return G

@@ -49,3 +49,22 @@ def test_qei_exact_vs_fast_and_monte_carlo():
     # q = 2 closed form cross-check: qEI of two far-apart independent-ish points is below the sum of EIs
     x = rng.random((2, 3))
     assert do.qEI(x, km, plugin=plugin, fastCompute=False) <= do.EI(x, km, plugin=plugin).sum() + 1e-12
+
+
+def test_qei_grad_oracle_vs_finite_differences():
+    """The reference's own check (R/qEI.grad.R:232-241): analytic gradient vs finite differences of qEI."""
+    km = to_oracle(small_model("matern5_2", "linear", n=25, d=2, seed=15, noise_var=0.02))
+    rng = np.random.default_rng(1)
+    plugin = float(np.median(km.y))
+    for q in (2, 3):
+        x = rng.random((q, 2))
+        g = do.qEI_grad(x, km, plugin=plugin, fastCompute=False)
+        h = 1e-5
+        fd = np.zeros_like(g)
+        for l in range(q):
+            for j in range(2):
+                xp = x.copy(); xp[l, j] += h; xm = x.copy(); xm[l, j] -= h
+                fd[l, j] = (do.qEI(xp, km, plugin=plugin, fastCompute=False) - do.qEI(xm, km, plugin=plugin, fastCompute=False)) / (2 * h)
+        assert np.max(np.abs(g - fd)) <= 1e-6 * np.max(np.abs(g))
+        gf = do.qEI_grad(x, km, plugin=plugin, fastCompute=True)
+        assert np.max(np.abs(g - gf)) <= 1e-6 * np.max(np.abs(g))
