@@ -1,0 +1,148 @@
+/* dk_rcall.c — the R `.Call` shim over include/dk_b200.h (layer (2) of SURVEY.md 8(b)).
+ *
+ * Mechanical wrappers: unwrap REAL()/INTEGER() pointers (R matrices are column-major already, no
+ * copies), allocate results with allocVector, hold the model as an external pointer whose finalizer
+ * calls dk_model_destroy.  Errors are raised with Rf_error AFTER unprotecting, so the callers' try()
+ * chains (e.g. /root/reference/R/fastEGO.nsteps.R:137) keep working.
+ *
+ * R and its headers are not installed in the build image: this file is compiled only where
+ * DK_HAVE_R is defined (R CMD SHLIB adds it through Makevars) and is not exercised by tests/.
+ */
+#ifdef DK_HAVE_R
+#include <R.h>
+#include <Rinternals.h>
+#include <R_ext/Rdynload.h>
+#include <string.h>
+
+#include "dk_b200.h"
+
+static void dkR_finalize(SEXP ptr) {
+  dk_model* m = (dk_model*)R_ExternalPtrAddr(ptr);
+  if (m) dk_model_destroy(m);
+  R_ClearExternalPtr(ptr);
+}
+static dk_model* handle_of(SEXP h) {
+  dk_model* m = (dk_model*)R_ExternalPtrAddr(h);
+  if (!m) Rf_error("dk_b200: model handle is NULL (released or restored from a saved workspace)");
+  return m;
+}
+static SEXP el(SEXP list, const char* name) {
+  SEXP names = Rf_getAttrib(list, R_NamesSymbol);
+  for (R_xlen_t i = 0; i < Rf_xlength(list); i++)
+    if (strcmp(CHAR(STRING_ELT(names, i)), name) == 0) return VECTOR_ELT(list, i);
+  return R_NilValue;
+}
+static const double* opt_real(SEXP x) { return (x == R_NilValue || Rf_xlength(x) == 0) ? NULL : REAL(x); }
+
+/* slots: list(T, z, M, X, y, F, trend.coef, range.val, shape.val, noise.var, n, d, p, kernel, trend, sd2, nugget, nugget.flag) */
+SEXP dkR_model_create(SEXP slots, SEXP device) {
+  dk_model_desc D;
+  memset(&D, 0, sizeof D);
+  D.n = Rf_asInteger(el(slots, "n")); D.d = Rf_asInteger(el(slots, "d")); D.p = Rf_asInteger(el(slots, "p"));
+  D.kernel = Rf_asInteger(el(slots, "kernel")); D.trend = Rf_asInteger(el(slots, "trend"));
+  D.sd2 = Rf_asReal(el(slots, "sd2")); D.nugget = Rf_asReal(el(slots, "nugget"));
+  D.nugget_flag = Rf_asLogical(el(slots, "nugget.flag"));
+  D.theta = REAL(el(slots, "range.val")); D.shape = opt_real(el(slots, "shape.val"));
+  D.noise_var = opt_real(el(slots, "noise.var"));
+  D.T = REAL(el(slots, "T")); D.z = REAL(el(slots, "z")); D.M = REAL(el(slots, "M")); D.X = REAL(el(slots, "X"));
+  D.y = REAL(el(slots, "y")); D.F = REAL(el(slots, "F")); D.beta = REAL(el(slots, "trend.coef"));
+  D.device = Rf_asInteger(device);
+  dk_model* m = NULL;
+  if (dk_model_create(&D, &m)) Rf_error("dk_model_create: %s", dk_last_error());
+  SEXP ptr = PROTECT(R_MakeExternalPtr(m, R_NilValue, R_NilValue));
+  R_RegisterCFinalizerEx(ptr, dkR_finalize, TRUE);
+  UNPROTECT(1);
+  return ptr;
+}
+
+SEXP dkR_ei(SEXP h, SEXP x, SEXP plugin, SEXP type, SEXP minimization, SEXP proxy, SEXP want_envir) {
+  dk_model* m = handle_of(h);
+  R_xlen_t N = Rf_nrows(x);
+  int env = Rf_asLogical(want_envir);
+  SEXP out = PROTECT(Rf_allocVector(VECSXP, 3));
+  SEXP ei = PROTECT(Rf_allocVector(REALSXP, N));
+  SEXP mean = PROTECT(Rf_allocVector(REALSXP, env ? N : 0));
+  SEXP sd = PROTECT(Rf_allocVector(REALSXP, env ? N : 0));
+  int rc = dk_ei(m, REAL(x), (int64_t)N, Rf_asReal(plugin), Rf_asInteger(type), Rf_asLogical(minimization),
+                 Rf_asLogical(proxy), REAL(ei), env ? REAL(mean) : NULL, env ? REAL(sd) : NULL);
+  SET_VECTOR_ELT(out, 0, ei); SET_VECTOR_ELT(out, 1, mean); SET_VECTOR_ELT(out, 2, sd);
+  UNPROTECT(4);
+  if (rc) Rf_error("dk_ei: %s", dk_last_error());
+  return out;
+}
+
+SEXP dkR_ei_grad(SEXP h, SEXP x, SEXP plugin, SEXP type, SEXP minimization, SEXP proxy) {
+  dk_model* m = handle_of(h);
+  R_xlen_t N = Rf_nrows(x), d = Rf_ncols(x);
+  SEXP g = PROTECT(Rf_allocMatrix(REALSXP, N, d));
+  int rc = dk_ei_grad(m, REAL(x), (int64_t)N, Rf_asReal(plugin), Rf_asInteger(type), Rf_asLogical(minimization),
+                      Rf_asLogical(proxy), REAL(g), NULL);
+  UNPROTECT(1);
+  if (rc) Rf_error("dk_ei_grad: %s", dk_last_error());
+  return g;
+}
+
+SEXP dkR_quantile(SEXP h, SEXP x, SEXP qnorm_beta, SEXP type, SEXP want_grad) {
+  dk_model* m = handle_of(h);
+  R_xlen_t N = Rf_nrows(x), d = Rf_ncols(x);
+  int wg = Rf_asLogical(want_grad);
+  SEXP out = PROTECT(Rf_allocVector(VECSXP, 2));
+  SEXP q = PROTECT(Rf_allocVector(REALSXP, N));
+  SEXP g = PROTECT(wg ? Rf_allocMatrix(REALSXP, N, d) : Rf_allocVector(REALSXP, 0));
+  int rc = dk_quantile(m, REAL(x), (int64_t)N, Rf_asReal(qnorm_beta), Rf_asInteger(type), REAL(q), wg ? REAL(g) : NULL);
+  SET_VECTOR_ELT(out, 0, q); SET_VECTOR_ELT(out, 1, g);
+  UNPROTECT(3);
+  if (rc) Rf_error("dk_quantile: %s", dk_last_error());
+  return out;
+}
+
+SEXP dkR_akg(SEXP h, SEXP x, SEXP new_noise_var, SEXP type) {
+  dk_model* m = handle_of(h);
+  R_xlen_t N = Rf_nrows(x);
+  SEXP out = PROTECT(Rf_allocVector(REALSXP, N));
+  int rc = dk_akg(m, REAL(x), (int64_t)N, Rf_asReal(new_noise_var), Rf_asInteger(type), REAL(out));
+  UNPROTECT(1);
+  if (rc) Rf_error("dk_akg: %s", dk_last_error());
+  return out;
+}
+
+/* x: (B*q) x d matrix, rows b*q .. b*q+q-1 = batch b */
+SEXP dkR_qei(SEXP h, SEXP x, SEXP q, SEXP plugin, SEXP type, SEXP minimization, SEXP want_grad) {
+  dk_model* m = handle_of(h);
+  int qq = Rf_asInteger(q), wg = Rf_asLogical(want_grad);
+  R_xlen_t rows = Rf_nrows(x), d = Rf_ncols(x), B = rows / qq;
+  SEXP out = PROTECT(wg ? Rf_allocMatrix(REALSXP, rows, d) : Rf_allocVector(REALSXP, B));
+  int rc = wg ? dk_qei_grad(m, REAL(x), (int64_t)B, qq, Rf_asReal(plugin), Rf_asInteger(type), Rf_asLogical(minimization), REAL(out))
+              : dk_qei(m, REAL(x), (int64_t)B, qq, Rf_asReal(plugin), Rf_asInteger(type), Rf_asLogical(minimization), REAL(out));
+  UNPROTECT(1);
+  if (rc) Rf_error("dk_qei: %s", dk_last_error());
+  return out;
+}
+
+SEXP dkR_screen_ei(SEXP h, SEXP x, SEXP plugin, SEXP type, SEXP minimization, SEXP proxy, SEXP k) {
+  dk_model* m = handle_of(h);
+  int kk = Rf_asInteger(k);
+  R_xlen_t N = Rf_nrows(x);
+  SEXP out = PROTECT(Rf_allocVector(VECSXP, 2));
+  SEXP idx = PROTECT(Rf_allocVector(REALSXP, kk));
+  SEXP val = PROTECT(Rf_allocVector(REALSXP, kk));
+  int64_t* tmp = (int64_t*)R_alloc(kk, sizeof(int64_t));
+  int rc = dk_screen_ei(m, REAL(x), 0, (int64_t)N, Rf_asReal(plugin), Rf_asInteger(type), Rf_asLogical(minimization),
+                        Rf_asLogical(proxy), kk, tmp, REAL(val), NULL);
+  for (int i = 0; i < kk; i++) REAL(idx)[i] = tmp[i] < 0 ? NA_REAL : (double)(tmp[i] + 1); /* 1-based like which.max */
+  SET_VECTOR_ELT(out, 0, idx); SET_VECTOR_ELT(out, 1, val);
+  UNPROTECT(3);
+  if (rc) Rf_error("dk_screen_ei: %s", dk_last_error());
+  return out;
+}
+
+SEXP dkR_sample_weights(SEXP h, SEXP x, SEXP T, SEXP minimization) {
+  dk_model* m = handle_of(h);
+  R_xlen_t N = Rf_nrows(x);
+  SEXP w = PROTECT(Rf_allocVector(REALSXP, N));
+  int rc = dk_sample_weights(m, REAL(x), (int64_t)N, Rf_asReal(T), Rf_asLogical(minimization), REAL(w));
+  UNPROTECT(1);
+  if (rc) Rf_error("dk_sample_weights: %s", dk_last_error());
+  return w;
+}
+#endif /* DK_HAVE_R */

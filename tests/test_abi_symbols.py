@@ -32,3 +32,15 @@ def test_version_and_argument_errors_without_gpu():
     assert lib.dk_model_create(None, None) != 0
     assert b"NULL" in lib.dk_last_error()
     assert lib.dk_ei(None, None, 0, 0.0, 1, 1, 0, None, None, None) != 0
+
+
+def test_r_call_shim_compiles_against_declarations():
+    """The .Call shim (r-package/src) type-checks against declarations of the R C API it uses
+    (tests/r_stub: declarations only, no R runtime here) and names only symbols the header declares."""
+    import subprocess
+    srcs = [os.path.join(ROOT, "r-package", "src", f) for f in ("dk_rcall.c", "packagename_init.c")]
+    cmd = ["gcc", "-fsyntax-only", "-Wall", "-Werror", "-DDK_HAVE_R", "-I" + os.path.join(ROOT, "tests", "r_stub"),
+           "-I" + os.path.join(ROOT, "include")] + srcs
+    subprocess.run(cmd, check=True)
+    used = set(re.findall(r"\b(dk_[a-z_0-9]+)\s*\(", open(srcs[0]).read()))
+    assert used <= set(_declared()) | {"dk_handle"}
