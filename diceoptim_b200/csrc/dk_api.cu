@@ -160,6 +160,7 @@ bool g_attr_done[64] = {};
 int set_kernel_attrs(int device) {
   if (device < 64 && g_attr_done[device]) return DK_OK;
   DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+  DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_fused_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + 64));
   DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
   if (device < 64) g_attr_done[device] = true;
   return DK_OK;
@@ -179,8 +180,14 @@ int launch_predict(dk_model* m, const CritParams& P, const double* d_x, int64_t 
   const int64_t ntiles = (N + BN - 1) / BN;
   const int grid = (int)std::min<int64_t>(ntiles, m->grid);
   if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
-  k_predict_fused<<<grid, NT, SM_TOTAL, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->scratch_doubles_per_cta,
-                                               d_main, d_mean, d_sd);
+  // default: bulk-copy + mbarrier pipeline (+8.6 % at cfg4); DK_PIPELINE=cpasync selects the cp.async / __syncthreads ring
+  static const bool use_tma = [] { const char* e = std::getenv("DK_PIPELINE"); return !(e && std::strcmp(e, "cpasync") == 0); }();
+  if (use_tma)
+    k_predict_fused_tma<<<grid, NT, SM_TOTAL + 64, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch,
+                                                          m->scratch_doubles_per_cta, d_main, d_mean, d_sd);
+  else
+    k_predict_fused<<<grid, NT, SM_TOTAL, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->scratch_doubles_per_cta,
+                                                 d_main, d_mean, d_sd);
   if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
   m->launches++;
   DK_CUDA_TRY(cudaGetLastError());

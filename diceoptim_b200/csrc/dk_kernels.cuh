@@ -132,6 +132,37 @@ __device__ __forceinline__ void covgen_block(const DevModel& M, const double* Xs
   }
 }
 
+// ---- mbarrier + bulk-copy (TMA 1-D) helpers for the warp-synchronous variant of the GEMM phase ----
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// one bulk asynchronous copy global -> shared, completion counted in bytes on `bar` (SASS: UBLKCP)
+__device__ __forceinline__ void bulk_load(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
 // ---------------------------------------------------------------------------------------
 // One block row of the blocked substitution given its right-hand side already in `acc`
 // (C-fragment layout).  On return acc holds V_I; the panel chunk for rows of block I has been
@@ -139,13 +170,46 @@ __device__ __forceinline__ void covgen_block(const DevModel& M, const double* Xs
 // backward factor).  Contains the __syncthreads the phase changes need; callers must sync once
 // more before touching region 0 again.
 // ---------------------------------------------------------------------------------------
+// TMA = true: the GEMM phase is fed by bulk asynchronous copies (one 16 KB A tile + one 8 KB B tile per stage,
+// issued by thread 0) and synchronised per stage by full/empty mbarriers instead of __syncthreads; `stage_base`
+// counts the stages this CTA has consumed so far (slot = index % STAGES, parity = (index / STAGES) & 1).
+template <bool TMA = false>
 __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const double* __restrict__ tiles, int I,
-                                                double* __restrict__ panel, unsigned char* smem, int tid) {
+                                                double* __restrict__ panel, unsigned char* smem, int tid,
+                                                unsigned* stage_base = nullptr) {
   const int warp = tid >> 5, lane = tid & 31, wm = warp >> 1, wn = warp & 1;
   double* ring = reinterpret_cast<double*>(smem);
   const double* Atiles = tiles + tile_base(I) * A_TILE;
   const int nk = CHUNKS_PER_BLOCK * I;
 
+  if constexpr (TMA) {
+    unsigned long long* full = reinterpret_cast<unsigned long long*>(smem + SM_TOTAL);
+    unsigned long long* empty = full + STAGES;
+    const unsigned base = *stage_base;
+    constexpr unsigned STAGE_BYTES = (A_TILE + B_TILE) * 8;
+    auto issue = [&](int idx) {  // thread 0 only
+      const unsigned gi = base + idx, slot = gi % STAGES, par = (gi / STAGES) & 1;
+      mbar_wait(&empty[slot], par ^ 1);  // every warp has released the slot's previous contents
+      double* dst = ring + slot * (A_TILE + B_TILE);
+      mbar_arrive_expect_tx(&full[slot], STAGE_BYTES);
+      bulk_load(dst, Atiles + (size_t)idx * A_TILE, A_TILE * 8, &full[slot]);
+      bulk_load(dst + A_TILE, panel + (size_t)idx * B_TILE, B_TILE * 8, &full[slot]);
+    };
+    if (tid == 0)
+      for (int s = 0; s < STAGES - 1 && s < nk; s++) issue(s);
+#pragma unroll 1
+    for (int kc = 0; kc < nk; kc++) {
+      if (tid == 0 && kc + STAGES - 1 < nk) issue(kc + STAGES - 1);
+      const unsigned gi = base + kc, slot = gi % STAGES, par = (gi / STAGES) & 1;
+      mbar_wait(&full[slot], par);
+      const double* s = ring + slot * (A_TILE + B_TILE);
+      mma_stage(acc, s, s + A_TILE, wm, wn, lane);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[slot]);
+    }
+    *stage_base = base + nk;
+    __syncthreads();  // every warp is done with the ring: region 0 can change role
+  } else {
   // ---- P3: acc += (-L_IJ) V_J over all k-chunks left of the diagonal block -----------------
 #pragma unroll
   for (int s = 0; s < STAGES - 1; s++) {
@@ -174,6 +238,7 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
   }
   cp_async_wait<0>();
   __syncthreads();  // every warp is done with the ring: region 0 can change role
+  }
 
   // ---- P4: V_I = inv(L_II) * acc, the right-hand side goes through smem as B fragments ------
   double* Rbuf = reinterpret_cast<double*>(smem);
@@ -219,6 +284,8 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
         panel[(size_t)chunk * B_TILE + b_tile_index(k, nn)] = acc[mi][ni][e];
       }
   }
+  // the panel is next read through the async proxy (bulk copies): order these generic-proxy stores before it
+  if constexpr (TMA) asm volatile("fence.proxy.async.global;" ::: "memory");
 }
 
 __device__ __forceinline__ double panel_at(const double* panel, int row, int col) {
@@ -293,8 +360,10 @@ __device__ __noinline__ void crit_epilogue(const DevModel& M, const CritParams& 
 // cov-gen -> solve -> s2.  On return (after a __syncthreads) the panel holds V (and the
 // augmented rows), s2acc the per-warp-row partial sums of v^2, xs the candidate tile.
 // ---------------------------------------------------------------------------------------
+template <bool TMA = false>
 __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __restrict__ x, int64_t N, int64_t c0,
-                                             double* __restrict__ panel, unsigned char* smem, int tid) {
+                                             double* __restrict__ panel, unsigned char* smem, int tid,
+                                             unsigned* stage_base = nullptr) {
   const int warp = tid >> 5, lane = tid & 31, wm = warp >> 1, wn = warp & 1;
   double* Cbuf = reinterpret_cast<double*>(smem);
   double* Xs = reinterpret_cast<double*>(smem + SM_XS_OFF);
@@ -332,7 +401,7 @@ __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __
       }
     __syncthreads();
     // ---- P3..P5 ----
-    solve_block_row(acc, M.tiles_fwd, I, panel, smem, tid);
+    solve_block_row<TMA>(acc, M.tiles_fwd, I, panel, smem, tid, stage_base);
     // ---- s2 += sum over this block's real rows of v^2 (fixed order: rows, then lanes, then warps) ----
     {
       double part[4][2];
@@ -367,6 +436,36 @@ __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __
 // ---------------------------------------------------------------------------------------
 // The fused forward kernel: persistent CTAs, two per SM, each looping over candidate tiles.
 // ---------------------------------------------------------------------------------------
+// Same kernel with the GEMM phase fed by bulk asynchronous copies + mbarriers (SM_TOTAL + 64 B of shared memory).
+__global__ void __launch_bounds__(NT, 2)
+k_predict_fused_tma(const DevModel M, const CritParams P, const double* __restrict__ x, int64_t N, int64_t ntiles,
+                    double* __restrict__ vscratch, size_t panel_doubles, double* __restrict__ out_main,
+                    double* __restrict__ out_mean, double* __restrict__ out_sd) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int tid = threadIdx.x;
+  const double* xs = reinterpret_cast<const double*>(smem + SM_CAND_OFF);
+  const double* s2acc = reinterpret_cast<const double*>(smem + SM_S2_OFF);
+  double* panel = vscratch + (size_t)blockIdx.x * panel_doubles;
+  unsigned long long* bars = reinterpret_cast<unsigned long long*>(smem + SM_TOTAL);
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; s++) {
+      mbar_init(&bars[s], 1);               // full: one arrive.expect_tx by the issuing thread
+      mbar_init(&bars[STAGES + s], NT / 32);  // empty: one arrive per consumer warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  unsigned stage_base = 0;
+#pragma unroll 1
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t c0 = tile * BN;
+    forward_tile<true>(M, x, N, c0, panel, smem, tid, &stage_base);
+    if (tid < BN && c0 + tid < N)
+      crit_epilogue(M, P, panel, xs, s2acc, tid, c0 + tid, out_main, out_mean, out_sd);
+    __syncthreads();
+  }
+}
+
 __global__ void __launch_bounds__(NT, 2)
 k_predict_fused(const DevModel M, const CritParams P, const double* __restrict__ x, int64_t N, int64_t ntiles,
                 double* __restrict__ vscratch, size_t panel_doubles, double* __restrict__ out_main,
