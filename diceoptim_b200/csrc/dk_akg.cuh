@@ -51,11 +51,13 @@ k_akg_fused(const DevModel M, int type, double tau2, const double* __restrict__ 
   double* kc = kb + (size_t)m0 * BN;                                      // stack cend
   int P2 = 1;
   while (P2 < m0) P2 <<= 1;
+  pipeline_init(smem, tid);
+  unsigned stage_base = 0;
 
 #pragma unroll 1
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t c0 = tile * BN;
-    forward_tile(M, x, N, c0, vpanel, smem, tid);
+    forward_tile<true>(M, x, N, c0, vpanel, smem, tid, &stage_base);
 
     if (tid < BN) {
       const int c = tid;
@@ -94,7 +96,7 @@ k_akg_fused(const DevModel M, int type, double tau2, const double* __restrict__ 
             acc[mi][ni][e] = v;
           }
       }
-      solve_block_row(acc, M.tiles_bwd, I, wpanel, smem, tid);
+      solve_block_row<true>(acc, M.tiles_bwd, I, wpanel, smem, tid, &stage_base);
       __syncthreads();
     }
 

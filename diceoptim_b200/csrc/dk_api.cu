@@ -160,8 +160,8 @@ bool g_attr_done[64] = {};
 int set_kernel_attrs(int device) {
   if (device < 64 && g_attr_done[device]) return DK_OK;
   DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
-  DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_fused_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + 64));
-  DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+  DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_fused_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
+  DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
   if (device < 64) g_attr_done[device] = true;
   return DK_OK;
 }
@@ -183,7 +183,7 @@ int launch_predict(dk_model* m, const CritParams& P, const double* d_x, int64_t 
   // default: bulk-copy + mbarrier pipeline (+8.6 % at cfg4); DK_PIPELINE=cpasync selects the cp.async / __syncthreads ring
   static const bool use_tma = [] { const char* e = std::getenv("DK_PIPELINE"); return !(e && std::strcmp(e, "cpasync") == 0); }();
   if (use_tma)
-    k_predict_fused_tma<<<grid, NT, SM_TOTAL + 64, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch,
+    k_predict_fused_tma<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch,
                                                           m->scratch_doubles_per_cta, d_main, d_mean, d_sd);
   else
     k_predict_fused<<<grid, NT, SM_TOTAL, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->scratch_doubles_per_cta,
@@ -202,7 +202,7 @@ int launch_grad(dk_model* m, const CritParams& P, const double* d_x, int64_t N, 
   const int64_t ntiles = (N + BN - 1) / BN;
   const int grid = (int)std::min<int64_t>(ntiles, m->grid);
   if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
-  k_grad_fused<<<grid, NT, SM_TOTAL, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->d_wscratch,
+  k_grad_fused<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->d_wscratch,
                                             m->scratch_doubles_per_cta, d_grad, d_main);
   if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
   m->launches++;
@@ -706,7 +706,7 @@ bool g_qei_attr_done[64] = {};
 
 int ensure_qei(dk_model* m, int64_t B) {
   if (m->device < 64 && !g_qei_attr_done[m->device]) {
-    DK_CUDA_TRY(cudaFuncSetAttribute(k_qei_moments, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+    DK_CUDA_TRY(cudaFuncSetAttribute(k_qei_moments, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
     g_qei_attr_done[m->device] = true;
   }
   if (!m->d_aux) {
@@ -738,7 +738,7 @@ extern "C" int dk_qei_dev(dk_model* m, const double* d_x, int64_t B, int q, doub
   const int64_t ntiles = (B + QB - 1) / QB;
   const int grid = (int)std::min<int64_t>(ntiles, m->grid);
   if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
-  k_qei_moments<<<grid, NT, SM_TOTAL, st>>>(m->dm, type, q, d_x, B, ntiles, m->d_vscratch, m->scratch_doubles_per_cta,
+  k_qei_moments<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, type, q, d_x, B, ntiles, m->d_vscratch, m->scratch_doubles_per_cta,
                                              m->d_aux, m->d_mom);
   DK_CUDA_TRY(cudaGetLastError());
   const int64_t threads = B * 4;
@@ -775,7 +775,7 @@ extern "C" int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q,
   if ((rc = ensure_qei(m, B))) return rc;
   static bool attr_done[64] = {};
   if (m->device < 64 && !attr_done[m->device]) {
-    DK_CUDA_TRY(cudaFuncSetAttribute(k_qei_grad_moments, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+    DK_CUDA_TRY(cudaFuncSetAttribute(k_qei_grad_moments, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
     attr_done[m->device] = true;
   }
   const size_t need = (size_t)B * qei_deriv_stride(m->d);
@@ -788,7 +788,7 @@ extern "C" int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q,
   const int64_t ntiles = (B + QB - 1) / QB;
   const int grid = (int)std::min<int64_t>(ntiles, m->grid);
   if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
-  k_qei_grad_moments<<<grid, NT, SM_TOTAL, st>>>(m->dm, type, q, d_x, B, ntiles, m->d_vscratch, m->d_wscratch,
+  k_qei_grad_moments<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, type, q, d_x, B, ntiles, m->d_vscratch, m->d_wscratch,
                                                   m->scratch_doubles_per_cta, m->d_aux, m->d_mom, m->d_deriv);
   DK_CUDA_TRY(cudaGetLastError());
   const int64_t threads = B * 4;
@@ -843,7 +843,7 @@ bool g_akg_attr_done[64] = {};
 
 int ensure_akg(dk_model* m) {
   if (m->device < 64 && !g_akg_attr_done[m->device]) {
-    DK_CUDA_TRY(cudaFuncSetAttribute(k_akg_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+    DK_CUDA_TRY(cudaFuncSetAttribute(k_akg_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
     g_akg_attr_done[m->device] = true;
   }
   if (m->d_akg_const) return DK_OK;
@@ -893,7 +893,7 @@ extern "C" int dk_akg_dev(dk_model* m, const double* d_x, int64_t N, double new_
   const int64_t ntiles = (N + BN - 1) / BN;
   const int grid = (int)std::min<int64_t>(ntiles, m->grid);
   if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
-  k_akg_fused<<<grid, NT, SM_TOTAL, st>>>(m->dm, type, new_noise_var, d_x, N, ntiles, m->d_vscratch, m->d_wscratch,
+  k_akg_fused<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, type, new_noise_var, d_x, N, ntiles, m->d_vscratch, m->d_wscratch,
                                            m->scratch_doubles_per_cta, m->d_akg_scratch, d_out);
   if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
   m->launches++;

@@ -74,11 +74,13 @@ k_grad_fused(const DevModel M, const CritParams P, const double* __restrict__ x,
   double* wpanel = wscratch + (size_t)blockIdx.x * (panel_doubles + COEF_DOUBLES);
   double* coef = wpanel + panel_doubles;  // [COEF_ROWS][64]
   const int n = M.n, d = M.d, p = M.p;
+  pipeline_init(smem, tid);
+  unsigned stage_base = 0;
 
 #pragma unroll 1
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t c0 = tile * BN;
-    forward_tile(M, x, N, c0, vpanel, smem, tid);
+    forward_tile<true>(M, x, N, c0, vpanel, smem, tid, &stage_base);
 
     // ---- epilogue 1: value + outer-derivative coefficients per candidate ----
     if (tid < BN) {
@@ -135,7 +137,7 @@ k_grad_fused(const DevModel M, const CritParams P, const double* __restrict__ x,
             acc[mi][ni][e] = v;
           }
       }
-      solve_block_row(acc, M.tiles_bwd, I, wpanel, smem, tid);
+      solve_block_row<true>(acc, M.tiles_bwd, I, wpanel, smem, tid, &stage_base);
       __syncthreads();
     }
 

@@ -163,6 +163,20 @@ __device__ __forceinline__ void bulk_load(void* dst, const void* src, unsigned b
                : "memory");
 }
 
+// Barriers of the bulk-copy pipeline live right after the fixed shared-memory map (SM_TOTAL + PIPE_SMEM bytes).
+constexpr int PIPE_SMEM = 64;
+__device__ __forceinline__ void pipeline_init(unsigned char* smem, int tid) {
+  unsigned long long* bars = reinterpret_cast<unsigned long long*>(smem + SM_TOTAL);
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; s++) {
+      mbar_init(&bars[s], 1);                 // full: one arrive.expect_tx by the issuing thread
+      mbar_init(&bars[STAGES + s], NT / 32);  // empty: one arrive per consumer warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+}
+
 // ---------------------------------------------------------------------------------------
 // One block row of the blocked substitution given its right-hand side already in `acc`
 // (C-fragment layout).  On return acc holds V_I; the panel chunk for rows of block I has been
@@ -446,15 +460,7 @@ k_predict_fused_tma(const DevModel M, const CritParams P, const double* __restri
   const double* xs = reinterpret_cast<const double*>(smem + SM_CAND_OFF);
   const double* s2acc = reinterpret_cast<const double*>(smem + SM_S2_OFF);
   double* panel = vscratch + (size_t)blockIdx.x * panel_doubles;
-  unsigned long long* bars = reinterpret_cast<unsigned long long*>(smem + SM_TOTAL);
-  if (tid == 0) {
-    for (int s = 0; s < STAGES; s++) {
-      mbar_init(&bars[s], 1);               // full: one arrive.expect_tx by the issuing thread
-      mbar_init(&bars[STAGES + s], NT / 32);  // empty: one arrive per consumer warp
-    }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads();
+  pipeline_init(smem, tid);
   unsigned stage_base = 0;
 #pragma unroll 1
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {

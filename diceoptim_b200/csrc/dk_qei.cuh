@@ -78,7 +78,7 @@ __device__ __forceinline__ void qei_tile_moments(const DevModel& M, int type, in
                                                  int64_t B, int64_t b0, double* __restrict__ panel,
                                                  double* __restrict__ gram, double* __restrict__ moments,
                                                  double* __restrict__ coef, bool round_x, unsigned char* smem,
-                                                 int tid) {
+                                                 int tid, unsigned* stage_base) {
   const int warp = tid >> 5, lane = tid & 31, wm = warp >> 1, wn = warp & 1;
   double* Cbuf = reinterpret_cast<double*>(smem);
   double* Xs = reinterpret_cast<double*>(smem + SM_XS_OFF);
@@ -118,7 +118,7 @@ __device__ __forceinline__ void qei_tile_moments(const DevModel& M, int type, in
         acc[mi][ni][1] = v.y;
       }
     __syncthreads();
-    solve_block_row(acc, M.tiles_fwd, I, panel, smem, tid);
+    solve_block_row<true>(acc, M.tiles_fwd, I, panel, smem, tid, stage_base);
     // ---- Gram products of each 4-column batch: a lane pair (lane ^ 1) covers one batch of an 8-column
     //      fragment; the even lane holds points (0,1), the odd lane (2,3); 5 products each. ----
     {
@@ -240,9 +240,11 @@ k_qei_moments(const DevModel M, int type, int q, const double* __restrict__ x, i
   extern __shared__ __align__(128) unsigned char smem[];
   double* panel = vscratch + (size_t)blockIdx.x * panel_doubles;
   double* gram = auxscratch + (size_t)blockIdx.x * QEI_AUX_DOUBLES;
+  pipeline_init(smem, threadIdx.x);
+  unsigned stage_base = 0;
 #pragma unroll 1
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
-    qei_tile_moments(M, type, q, x, B, tile * QB, panel, gram, moments, nullptr, true, smem, threadIdx.x);
+    qei_tile_moments(M, type, q, x, B, tile * QB, panel, gram, moments, nullptr, true, smem, threadIdx.x, &stage_base);
 }
 
 // covZk (R/qEI.R:240-261) on a q x q matrix stored with leading dimension 4
@@ -378,11 +380,13 @@ k_qei_grad_moments(const DevModel M, int type, int q, const double* __restrict__
   double* gram = auxscratch + (size_t)blockIdx.x * QEI_AUX_DOUBLES;
   const int n = M.n, d = M.d, p = M.p;
   const size_t dstride = qei_deriv_stride(d);
+  pipeline_init(smem, tid);
+  unsigned stage_base = 0;
 
 #pragma unroll 1
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t b0 = tile * QB;
-    qei_tile_moments(M, type, q, x, B, b0, vpanel, gram, moments, coef, false, smem, tid);
+    qei_tile_moments(M, type, q, x, B, b0, vpanel, gram, moments, coef, false, smem, tid, &stage_base);
 
     // ---- backward blocked solve: wt_l = T^-1 (v_l + M r_l) for all 64 columns ----
 #pragma unroll 1
@@ -406,7 +410,7 @@ k_qei_grad_moments(const DevModel M, int type, int q, const double* __restrict__
             acc[mi][ni][e] = v;
           }
       }
-      solve_block_row(acc, M.tiles_bwd, I, wpanel, smem, tid);
+      solve_block_row<true>(acc, M.tiles_bwd, I, wpanel, smem, tid, &stage_base);
       __syncthreads();
     }
 

@@ -1,5 +1,5 @@
 """Short driver for ncu: a few launches of the fused kernels on the cfg4 model (n=2000, d=10).
-usage: python tools/profile_ei.py [N] [reps] [grad]"""
+usage: python tools/profile_ei.py [N] [reps] [ei|grad|akg]   (DK_CFG selects the synth config)"""
 import ctypes as C
 import os
 import sys
@@ -15,7 +15,8 @@ from diceoptim_b200 import _lib, synth
 
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
-grad = len(sys.argv) > 3 and sys.argv[3] == "grad"
+mode = sys.argv[3] if len(sys.argv) > 3 else "ei"
+grad = mode == "grad"
 cfg = os.environ.get("DK_CFG", "cfg4_sphere10_n2000")
 lib = _lib.load()
 km = synth.config_model(cfg)
@@ -27,7 +28,9 @@ gr = torch.empty((km.d, N), dtype=torch.float64, device="cuda") if grad else Non
 plugin = float(np.min(km.y))
 ms = []
 for _ in range(reps):
-    if grad:
+    if mode == "akg":
+        _lib.check(lib.dk_akg_dev(h.ptr, C.c_void_p(x.data_ptr()), N, 0.1, 1, C.c_void_p(ei.data_ptr()), None), "akg")
+    elif grad:
         _lib.check(lib.dk_ei_grad_dev(h.ptr, C.c_void_p(x.data_ptr()), N, plugin, 1, 1, 0, C.c_void_p(gr.data_ptr()),
                                       C.c_void_p(ei.data_ptr()), None), "grad")
     else:
