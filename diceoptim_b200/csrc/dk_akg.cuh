@@ -16,14 +16,16 @@
 // AKG values agree, the order of the noise-level slopes is not reproduced.
 //
 // Per candidate tile: forward solve, epilogue (mk.x, sk.x, r), backward solve, then for each of the 64
-// candidates a shared-memory bitonic sort of (b, rank-of-a) keys by the whole CTA, and finally 64 threads
-// walk their candidates' envelopes in parallel with stacks in per-CTA global scratch.
+// candidates a convex-hull pre-filter (16 extreme directions) and a shared-memory bitonic sort of the surviving
+// (b, rank-of-a) keys by the whole CTA, and finally 64 threads walk their candidates' envelopes in parallel
+// with stacks in per-CTA global scratch.
 #pragma once
 #include "dk_grad.cuh"
 
 namespace dk {
 
 constexpr int AKG_MAX_SORT = 8192;  // n + 1 <= 8192: keys (8 B) + ranks (4 B) fill region 0 exactly
+constexpr int AKG_DIRS = 16;        // directions of the hull pre-filter (two per warp)
 
 // per-CTA scratch: sorted a, sorted b, stack a, stack b, stack cend : 5 arrays [n+1][64]
 __host__ __device__ inline size_t akg_scratch_doubles(int n) { return (size_t)5 * (n + 1) * BN; }
@@ -49,8 +51,6 @@ k_akg_fused(const DevModel M, int type, double tau2, const double* __restrict__ 
   double* ka = sb + (size_t)m0 * BN;                                      // stack a
   double* kb = ka + (size_t)m0 * BN;                                      // stack b
   double* kc = kb + (size_t)m0 * BN;                                      // stack cend
-  int P2 = 1;
-  while (P2 < m0) P2 <<= 1;
   pipeline_init(smem, tid);
   unsigned stage_base = 0;
 
@@ -100,9 +100,19 @@ k_akg_fused(const DevModel M, int type, double tau2, const double* __restrict__ 
       __syncthreads();
     }
 
-    // ---- per candidate: keys (b, rank of a) -> bitonic sort in smem -> sorted (a, b) to scratch ----
-    double* keyb = reinterpret_cast<double*>(smem);                 // [P2]
-    int* keyr = reinterpret_cast<int*>(smem + (size_t)AKG_MAX_SORT * 8);  // [P2]
+    // ---- per candidate: slopes b -> hull pre-filter -> bitonic sort of the survivors -> sorted (a, b) ----
+    // Only lines on the upper envelope (the upper convex hull of the points (b, a)) contribute.  The extreme
+    // points in AKG_DIRS directions are hull vertices; a point clearly below a chord between two of them
+    // cannot be on the hull, so it is dropped before the sort (the reference's stack scan would pop or skip
+    // it without effect on the breakpoints of the surviving lines).  Survivors are sorted by (b, rank of a)
+    // exactly as order(B, A) does and go through the reference's scan unchanged.
+    double* keyb = reinterpret_cast<double*>(smem);                        // [8192] all slopes, then survivor keys
+    int* keyr = reinterpret_cast<int*>(smem + (size_t)AKG_MAX_SORT * 8);   // [8192] survivor ranks
+    double* red = reinterpret_cast<double*>(smem + (size_t)AKG_MAX_SORT * 8);       // reduction scratch (aliases keyr)
+    double* chb = red + 64;                                                // chain vertices b [AKG_DIRS]
+    double* cha = chb + AKG_DIRS;                                          // chain vertices a
+    int* s_cnt = reinterpret_cast<int*>(smem + SM_S2_OFF);                 // survivor counter, then cnt[64] at +8
+    int* cnt = s_cnt + 2;
 #pragma unroll 1
     for (int c = 0; c < BN; c++) {
       const double mkx = __ldcg(coef + c), skx = __ldcg(coef + BN + c);
@@ -115,35 +125,141 @@ k_akg_fused(const DevModel M, int type, double tau2, const double* __restrict__ 
         if (__ldg(M.akg_a_sorted + mid) <= ax) lo = mid + 1; else hi = mid;
       }
       const int rank_x = 2 * lo - 1;
-      for (int j = tid; j < P2; j += NT) {
-        double b; int r;
+      // 1. slopes of all n + 1 lines; running min / max of b
+      double bmin = INFINITY, bmax = -INFINITY;
+      for (int j = tid; j < m0; j += NT) {
+        double b;
         if (j < n) {
           const int i = __ldg(M.akg_perm + j);  // design row with the j-th smallest a
           b = __ldg(M.akg_delta + i) * panel_at(wpanel, n - 1 - i, c) / den;
-          r = 2 * j;
-        } else if (j == n) {
-          b = skx * skx / den; r = rank_x;
         } else {
-          b = INFINITY; r = 0x7fffffff;
+          b = skx * skx / den;
         }
-        keyb[j] = b; keyr[j] = r;
+        keyb[j] = b;
+        bmin = fmin(bmin, b); bmax = fmax(bmax, b);
       }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        bmin = fmin(bmin, __shfl_xor_sync(0xffffffffu, bmin, o));
+        bmax = fmax(bmax, __shfl_xor_sync(0xffffffffu, bmax, o));
+      }
+      if (lane == 0) { red[warp] = bmin; red[8 + warp] = bmax; }
+      if (tid == 0) *s_cnt = 0;
+      __syncthreads();
+      bmin = red[0]; bmax = red[8];
+#pragma unroll
+      for (int w = 1; w < 8; w++) { bmin = fmin(bmin, red[w]); bmax = fmax(bmax, red[8 + w]); }
+      const double amin = fmin(__ldg(M.akg_a_sorted), ax), amax = fmax(__ldg(M.akg_a_sorted + n - 1), ax);
+      const double isb = (bmax > bmin) ? 1.0 / (bmax - bmin) : 0.0, isa = (amax > amin) ? 1.0 / (amax - amin) : 0.0;
+      // 2. extreme point per direction: warp w takes directions 2w, 2w + 1 (angles from 0 to pi)
+      {
+        double cs[2], sn[2], best[2] = {-INFINITY, -INFINITY};
+        int bi[2] = {0, 0};
+#pragma unroll
+        for (int u = 0; u < 2; u++) sincospi((double)(2 * warp + u) / (AKG_DIRS - 1), &sn[u], &cs[u]);
+        for (int j = lane; j < m0; j += 32) {
+          const double bs = (keyb[j] - bmin) * isb;
+          const double as = (((j < n) ? __ldg(M.akg_a_sorted + j) : ax) - amin) * isa;
+#pragma unroll
+          for (int u = 0; u < 2; u++) {
+            const double pv = fma(cs[u], bs, sn[u] * as);
+            if (pv > best[u]) { best[u] = pv; bi[u] = j; }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            const double ob = __shfl_xor_sync(0xffffffffu, best[u], o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi[u], o);
+            if (ob > best[u] || (ob == best[u] && oi < bi[u])) { best[u] = ob; bi[u] = oi; }
+          }
+          if (lane == 0) {
+            chb[2 * warp + u] = keyb[bi[u]];
+            cha[2 * warp + u] = (bi[u] < n) ? __ldg(M.akg_a_sorted + bi[u]) : ax;
+          }
+        }
+      }
+      __syncthreads();
+      // 3. drop points clearly below a chord of the chain; survivors (b, rank) -> global staging (kc, ka).
+      //    A chord between ANY two data points lies inside the hull, so the test is safe whatever the vertices.
+      double* clo = cha + AKG_DIRS;   // per chord: b-span [clo, chi], value = cic + csl * b
+      double* chi = clo + AKG_DIRS;
+      double* csl = chi + AKG_DIRS;
+      double* cic = csl + AKG_DIRS;
+      if (tid < AKG_DIRS - 1) {
+        const double b0 = chb[tid], b1 = chb[tid + 1];
+        const double blo = fmin(b0, b1), bhi = fmax(b0, b1);
+        const bool ok = bhi > blo;
+        const double sl = ok ? (cha[tid + 1] - cha[tid]) / (b1 - b0) : 0.0;
+        clo[tid] = ok ? blo : INFINITY;   // empty span: never tested
+        chi[tid] = ok ? bhi : -INFINITY;
+        csl[tid] = sl;
+        cic[tid] = cha[tid] - sl * b0;
+      }
+      __syncthreads();
+      {
+        const double tol = 1e-9 * (amax - amin) + 1e-300;
+        for (int j = tid; j < m0; j += NT) {
+          const double bj = keyb[j];
+          const double aj = (j < n) ? __ldg(M.akg_a_sorted + j) : ax;
+          bool keep = true;
+#pragma unroll
+          for (int s = 0; s < AKG_DIRS - 1; s++)
+            if (bj >= clo[s] && bj <= chi[s] && aj < fma(csl[s], bj, cic[s]) - tol) keep = false;
+          if (keep) {
+            const int pos = atomicAdd(s_cnt, 1);
+            kc[(size_t)pos * BN + c] = bj;
+            ka[(size_t)pos * BN + c] = (double)((j < n) ? 2 * j : rank_x);
+          }
+        }
+      }
+      __syncthreads();
+      const int ms = *s_cnt;  // survivors
+      int P2 = 2;
+      while (P2 < ms) P2 <<= 1;
+      for (int j = tid; j < P2; j += NT) {
+        if (j < ms) {
+          keyb[j] = __ldcg(kc + (size_t)j * BN + c);
+          keyr[j] = (int)__ldcg(ka + (size_t)j * BN + c);
+        } else {
+          keyb[j] = INFINITY; keyr[j] = 0x7fffffff;
+        }
+      }
+      if (tid == 0) cnt[c] = ms;
       __syncthreads();
       for (int k2 = 2; k2 <= P2; k2 <<= 1)
         for (int j2 = k2 >> 1; j2 > 0; j2 >>= 1) {
-          for (int t = tid; t < P2; t += NT) {
-            const int partner = t ^ j2;
-            if (partner > t) {
-              const bool up = (t & k2) == 0;
-              const double b1 = keyb[t], b2 = keyb[partner];
-              const int r1 = keyr[t], r2 = keyr[partner];
-              const bool swap = up ? akg_less(b2, r2, b1, r1) : akg_less(b1, r1, b2, r2);
-              if (swap) { keyb[t] = b2; keyb[partner] = b1; keyr[t] = r2; keyr[partner] = r1; }
+          // pair pi <-> (t, t | j2) with bit j2 of t clear: every lane has work, and the four pairs a thread
+          // takes per step are loaded before any is stored (they are disjoint), so the loads overlap
+          const int npairs = P2 >> 1;
+          for (int p0 = tid; p0 < npairs; p0 += 4 * NT) {
+            double b1[4], b2[4];
+            int r1[4], r2[4], tt[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+              const int pi = p0 + u * NT;
+              tt[u] = -1;
+              if (pi < npairs) {
+                const int t = ((pi & ~(j2 - 1)) << 1) | (pi & (j2 - 1));
+                tt[u] = t;
+                b1[u] = keyb[t]; b2[u] = keyb[t | j2];
+                r1[u] = keyr[t]; r2[u] = keyr[t | j2];
+              }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+              if (tt[u] >= 0) {
+                const int t = tt[u];
+                const bool up = (t & k2) == 0;
+                const bool swap = up ? akg_less(b2[u], r2[u], b1[u], r1[u]) : akg_less(b1[u], r1[u], b2[u], r2[u]);
+                if (swap) { keyb[t] = b2[u]; keyb[t | j2] = b1[u]; keyr[t] = r2[u]; keyr[t | j2] = r1[u]; }
+              }
             }
           }
           __syncthreads();
         }
-      for (int j = tid; j < m0; j += NT) {
+      for (int j = tid; j < ms; j += NT) {
         const int r = keyr[j];
         sb[(size_t)j * BN + c] = keyb[j];
         sa[(size_t)j * BN + c] = (r & 1) ? ax : __ldg(M.akg_a_sorted + (r >> 1));
@@ -157,6 +273,7 @@ k_akg_fused(const DevModel M, int type, double tau2, const double* __restrict__ 
       const double mkx = __ldcg(coef + c), skx = __ldcg(coef + BN + c);
       double res = 0.0;
       if (!(skx < sqrt(M.sd2) / 1e6 || M.sd2 < 1e-20)) {  // R/AKG.R:115
+        const int m0 = cnt[c];    // lines that survived the hull pre-filter, sorted by (b, a)
         int len = 0;              // stack length
         double ta = 0.0, tb = 0.0;  // top of stack (a, b)
         double cbelow = -1e36;      // cend of the element below the top
