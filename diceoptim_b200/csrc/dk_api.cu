@@ -152,6 +152,8 @@ int ensure_bwd(dk_model* m) {
   DK_CUDA_TRY(cudaMemcpy(m->d_tiles_bwd, tiles.data(), tiles.size() * 8, cudaMemcpyHostToDevice));
   rc = dev_alloc(m, &m->d_wscratch, (size_t)m->grid * (m->scratch_doubles_per_cta + COEF_DOUBLES));
   if (rc) return rc;
+  rc = dev_alloc(m, &m->d_cscratch, (size_t)m->grid * m->scratch_doubles_per_cta);  // covariance panels (gradients)
+  if (rc) return rc;
   m->dm.tiles_bwd = m->d_tiles_bwd;
   return DK_OK;
 }
@@ -203,7 +205,7 @@ int launch_grad(dk_model* m, const CritParams& P, const double* d_x, int64_t N, 
   const int grid = (int)std::min<int64_t>(ntiles, m->grid);
   if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
   k_grad_fused<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->d_wscratch,
-                                            m->scratch_doubles_per_cta, d_grad, d_main);
+                                            m->d_cscratch, m->scratch_doubles_per_cta, d_grad, d_main);
   if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
   m->launches++;
   DK_CUDA_TRY(cudaGetLastError());
@@ -398,7 +400,7 @@ void dk_model_destroy(dk_model* m) {
   DeviceGuard guard(m->device);
   cudaDeviceSynchronize();
   cudaFree(m->d_tiles_fwd); cudaFree(m->d_tiles_bwd); cudaFree(m->d_Xrm); cudaFree(m->d_small);
-  cudaFree(m->d_vscratch); cudaFree(m->d_wscratch); cudaFree(m->d_io); cudaFree(m->d_red);
+  cudaFree(m->d_vscratch); cudaFree(m->d_wscratch); cudaFree(m->d_cscratch); cudaFree(m->d_io); cudaFree(m->d_red);
   cudaFree(m->d_aux); cudaFree(m->d_mom); cudaFree(m->d_deriv);
   if (m->stream) cudaStreamDestroy(m->stream);
   if (m->ev0) cudaEventDestroy(m->ev0);
@@ -789,7 +791,7 @@ extern "C" int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q,
   const int grid = (int)std::min<int64_t>(ntiles, m->grid);
   if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
   k_qei_grad_moments<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, type, q, d_x, B, ntiles, m->d_vscratch, m->d_wscratch,
-                                                  m->scratch_doubles_per_cta, m->d_aux, m->d_mom, m->d_deriv);
+                                                  m->d_cscratch, m->scratch_doubles_per_cta, m->d_aux, m->d_mom, m->d_deriv);
   DK_CUDA_TRY(cudaGetLastError());
   const int64_t threads = B * 4;
   k_qei_grad_cdf<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(m->d_mom, m->d_deriv, B, q, m->d, plugin, minimization,

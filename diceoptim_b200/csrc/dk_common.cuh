@@ -113,6 +113,7 @@ struct dk_model {
   double* d_small = nullptr;     // beta | RM | tuuinv | alpha | KinvF | noise_var
   double* d_vscratch = nullptr;  // per-CTA V panels (forward solve), grid x n_pad x 64 doubles
   double* d_wscratch = nullptr;  // per-CTA W panels (backward solve)
+  double* d_cscratch = nullptr;  // per-CTA covariance panels kept for the gradient kernels
   double* d_aux = nullptr;       // per-CTA Gram accumulators of the qEI kernel
   double* d_mom = nullptr;       // per-batch (mu, Sigma, mask) of the qEI kernels, grow-only
   size_t mom_doubles = 0;

@@ -20,43 +20,44 @@ namespace dk {
 constexpr int COEF_ROWS = 2 + DK_MAX_P;  // cA, cW, r[p]
 constexpr int COEF_DOUBLES = COEF_ROWS * BN;
 
+// 1 / x for x >= 1: hardware seed (about 20 bits) + two Newton steps; a few ulp, no special cases needed here
+__device__ __forceinline__ double rcp_pos(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  r = fma(fma(-x, r, 1.0), r, r);
+  r = fma(fma(-x, r, 1.0), r, r);
+  return r;
+}
+
+// g_k += sum_i c_i omega_i dlogk_k(x - X_i),  omega_i = cA alpha_i + cW wt_i[cw]  (covVector.dx contracted with the
+// adjoint weights).  c_i comes from the covariance panel the forward pass kept; rows i = slice, slice + 4, ...
+// With t = (x_k - X_ik) w_k and a = |t|:  gauss -t w ; exp -sign(t) w ; matern3_2 -w t / (1 + a) ;
+// matern5_2 -w (t / 3)(1 + a) / (1 + a + a^2 / 3) ; powexp -sign(t) p a^(p-1) w.
 template <int KERNEL>
 __device__ __forceinline__ void grad_accumulate(const DevModel& M, const double* __restrict__ xs,
-                                                const double* __restrict__ wpanel, int c, int slice, double cA,
-                                                double cW, double (&g)[DK_MAX_D], int cw = -1) {
+                                                const double* __restrict__ cpanel, const double* __restrict__ wpanel,
+                                                int c, int slice, double cA, double cW, double (&g)[DK_MAX_D],
+                                                int cw = -1) {
   if (cw < 0) cw = c;  // column of the W panel that supplies the weights (qEI.grad pairs point c with point cw)
   const int n = M.n, d = M.d;
 #pragma unroll 1
   for (int i = slice; i < n; i += 4) {
     const double* Xi = M.Xrm + (size_t)i * d;
-    // covariance c_i (same arithmetic as covgen_rows)
-    double s = 0.0, pr = 1.0;
-#pragma unroll 1
-    for (int k = 0; k < d; k++) {
-      const double a = fabs(__ldg(Xi + k) - xs[k * BN + c]) * M.w[k];
-      if (KERNEL == DK_GAUSS) s = fma(0.5 * a, a, s);
-      else if (KERNEL == DK_EXP) s += a;
-      else if (KERNEL == DK_MATERN3_2) { pr *= (1.0 + a); s += a; }
-      else if (KERNEL == DK_MATERN5_2) { pr *= fma(a, fma(a, 1.0 / 3.0, 1.0), 1.0); s += a; }
-      else s += pow(a, M.shape[k]);
-    }
     const double omega = cA * __ldg(M.alpha + i) + cW * panel_at(wpanel, n - 1 - i, cw);
-    const double cw = M.sd2 * pr * exp(-s) * omega;
-    // covVector.dx: c_i * d log k / d x_k
+    const double cwv = __ldcg(cpanel + (size_t)i * BN + c) * omega;
 #pragma unroll
     for (int k = 0; k < DK_MAX_D; k++) {
       if (k < d) {
-        const double diff = xs[k * BN + c] - __ldg(Xi + k);
         const double wk = M.w[k];
-        const double a = fabs(diff) * wk;
-        const double sg = (diff > 0.0) ? 1.0 : ((diff < 0.0) ? -1.0 : 0.0);
+        const double t = (xs[k * BN + c] - __ldg(Xi + k)) * wk;
+        const double a = fabs(t);
         double dl;
-        if (KERNEL == DK_GAUSS) dl = -diff * wk * wk;
-        else if (KERNEL == DK_EXP) dl = -sg * wk;
-        else if (KERNEL == DK_MATERN3_2) dl = -sg * wk * a / (1.0 + a);
-        else if (KERNEL == DK_MATERN5_2) dl = -sg * wk * (a * (1.0 / 3.0)) * (1.0 + a) / fma(a, fma(a, 1.0 / 3.0, 1.0), 1.0);
-        else dl = (a > 0.0) ? -sg * M.shape[k] * pow(a, M.shape[k] - 1.0) * wk : 0.0;
-        g[k] = fma(cw, dl, g[k]);
+        if (KERNEL == DK_GAUSS) dl = -t * wk;
+        else if (KERNEL == DK_EXP) dl = (t > 0.0) ? -wk : ((t < 0.0) ? wk : 0.0);
+        else if (KERNEL == DK_MATERN3_2) dl = -wk * t * rcp_pos(1.0 + a);
+        else if (KERNEL == DK_MATERN5_2) dl = -(wk * (1.0 / 3.0)) * t * (1.0 + a) * rcp_pos(fma(a, fma(a, 1.0 / 3.0, 1.0), 1.0));
+        else dl = (a > 0.0) ? -copysign(M.shape[k] * pow(a, M.shape[k] - 1.0) * wk, t) : 0.0;
+        g[k] = fma(cwv, dl, g[k]);
       }
     }
   }
@@ -64,8 +65,8 @@ __device__ __forceinline__ void grad_accumulate(const DevModel& M, const double*
 
 __global__ void __launch_bounds__(NT, 2)
 k_grad_fused(const DevModel M, const CritParams P, const double* __restrict__ x, int64_t N, int64_t ntiles,
-             double* __restrict__ vscratch, double* __restrict__ wscratch, size_t panel_doubles,
-             double* __restrict__ out_grad, double* __restrict__ out_main) {
+             double* __restrict__ vscratch, double* __restrict__ wscratch, double* __restrict__ cscratch,
+             size_t panel_doubles, double* __restrict__ out_grad, double* __restrict__ out_main) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, wm = warp >> 1, wn = warp & 1;
   const double* xs = reinterpret_cast<const double*>(smem + SM_CAND_OFF);
@@ -73,6 +74,7 @@ k_grad_fused(const DevModel M, const CritParams P, const double* __restrict__ x,
   double* vpanel = vscratch + (size_t)blockIdx.x * panel_doubles;
   double* wpanel = wscratch + (size_t)blockIdx.x * (panel_doubles + COEF_DOUBLES);
   double* coef = wpanel + panel_doubles;  // [COEF_ROWS][64]
+  double* cpanel = cscratch + (size_t)blockIdx.x * panel_doubles;  // covariance columns, row-major [i][64]
   const int n = M.n, d = M.d, p = M.p;
   pipeline_init(smem, tid);
   unsigned stage_base = 0;
@@ -80,7 +82,7 @@ k_grad_fused(const DevModel M, const CritParams P, const double* __restrict__ x,
 #pragma unroll 1
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t c0 = tile * BN;
-    forward_tile<true>(M, x, N, c0, vpanel, smem, tid, &stage_base);
+    forward_tile<true>(M, x, N, c0, vpanel, smem, tid, &stage_base, cpanel);
 
     // ---- epilogue 1: value + outer-derivative coefficients per candidate ----
     if (tid < BN) {
@@ -149,11 +151,11 @@ k_grad_fused(const DevModel M, const CritParams P, const double* __restrict__ x,
 #pragma unroll
       for (int k = 0; k < DK_MAX_D; k++) g[k] = 0.0;
       switch (M.kernel) {
-        case DK_GAUSS: grad_accumulate<DK_GAUSS>(M, xs, wpanel, c, slice, cA, cW, g); break;
-        case DK_EXP: grad_accumulate<DK_EXP>(M, xs, wpanel, c, slice, cA, cW, g); break;
-        case DK_MATERN3_2: grad_accumulate<DK_MATERN3_2>(M, xs, wpanel, c, slice, cA, cW, g); break;
-        case DK_MATERN5_2: grad_accumulate<DK_MATERN5_2>(M, xs, wpanel, c, slice, cA, cW, g); break;
-        default: grad_accumulate<DK_POWEXP>(M, xs, wpanel, c, slice, cA, cW, g); break;
+        case DK_GAUSS: grad_accumulate<DK_GAUSS>(M, xs, cpanel, wpanel, c, slice, cA, cW, g); break;
+        case DK_EXP: grad_accumulate<DK_EXP>(M, xs, cpanel, wpanel, c, slice, cA, cW, g); break;
+        case DK_MATERN3_2: grad_accumulate<DK_MATERN3_2>(M, xs, cpanel, wpanel, c, slice, cA, cW, g); break;
+        case DK_MATERN5_2: grad_accumulate<DK_MATERN5_2>(M, xs, cpanel, wpanel, c, slice, cA, cW, g); break;
+        default: grad_accumulate<DK_POWEXP>(M, xs, cpanel, wpanel, c, slice, cA, cW, g); break;
       }
       double* gbuf = reinterpret_cast<double*>(smem);  // [4][DK_MAX_D][64] in region 0
 #pragma unroll

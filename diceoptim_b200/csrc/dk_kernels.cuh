@@ -374,10 +374,12 @@ __device__ __noinline__ void crit_epilogue(const DevModel& M, const CritParams& 
 // cov-gen -> solve -> s2.  On return (after a __syncthreads) the panel holds V (and the
 // augmented rows), s2acc the per-warp-row partial sums of v^2, xs the candidate tile.
 // ---------------------------------------------------------------------------------------
+// cpanel (optional): the covariance columns c(x_j) themselves are kept, row-major [i][64], for the gradient
+// kernels (covVector.dx needs c again: dc = c .* dlogk).
 template <bool TMA = false>
 __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __restrict__ x, int64_t N, int64_t c0,
                                              double* __restrict__ panel, unsigned char* smem, int tid,
-                                             unsigned* stage_base = nullptr) {
+                                             unsigned* stage_base = nullptr, double* __restrict__ cpanel = nullptr) {
   const int warp = tid >> 5, lane = tid & 31, wm = warp >> 1, wn = warp & 1;
   double* Cbuf = reinterpret_cast<double*>(smem);
   double* Xs = reinterpret_cast<double*>(smem + SM_XS_OFF);
@@ -412,6 +414,9 @@ __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __
             Cbuf + (32 * wm + 8 * mi + (lane >> 2)) * CB_STRIDE + 32 * wn + 8 * ni + 2 * (lane & 3));
         acc[mi][ni][0] = v.x;
         acc[mi][ni][1] = v.y;
+        if (cpanel)
+          *reinterpret_cast<double2*>(cpanel + (size_t)(I * BM + 32 * wm + 8 * mi + (lane >> 2)) * BN + 32 * wn + 8 * ni +
+                                      2 * (lane & 3)) = v;
       }
     __syncthreads();
     // ---- P3..P5 ----

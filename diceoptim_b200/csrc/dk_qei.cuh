@@ -78,7 +78,7 @@ __device__ __forceinline__ void qei_tile_moments(const DevModel& M, int type, in
                                                  int64_t B, int64_t b0, double* __restrict__ panel,
                                                  double* __restrict__ gram, double* __restrict__ moments,
                                                  double* __restrict__ coef, bool round_x, unsigned char* smem,
-                                                 int tid, unsigned* stage_base) {
+                                                 int tid, unsigned* stage_base, double* __restrict__ cpanel = nullptr) {
   const int warp = tid >> 5, lane = tid & 31, wm = warp >> 1, wn = warp & 1;
   double* Cbuf = reinterpret_cast<double*>(smem);
   double* Xs = reinterpret_cast<double*>(smem + SM_XS_OFF);
@@ -116,6 +116,9 @@ __device__ __forceinline__ void qei_tile_moments(const DevModel& M, int type, in
             Cbuf + (32 * wm + 8 * mi + (lane >> 2)) * CB_STRIDE + 32 * wn + 8 * ni + 2 * (lane & 3));
         acc[mi][ni][0] = v.x;
         acc[mi][ni][1] = v.y;
+        if (cpanel)
+          *reinterpret_cast<double2*>(cpanel + (size_t)(I * BM + 32 * wm + 8 * mi + (lane >> 2)) * BN + 32 * wn + 8 * ni +
+                                      2 * (lane & 3)) = v;
       }
     __syncthreads();
     solve_block_row<true>(acc, M.tiles_fwd, I, panel, smem, tid, stage_base);
@@ -369,8 +372,9 @@ __host__ __device__ inline size_t qei_deriv_stride(int d) { return (size_t)20 * 
 
 __global__ void __launch_bounds__(NT, 2)
 k_qei_grad_moments(const DevModel M, int type, int q, const double* __restrict__ x, int64_t B, int64_t ntiles,
-                   double* __restrict__ vscratch, double* __restrict__ wscratch, size_t panel_doubles,
-                   double* __restrict__ auxscratch, double* __restrict__ moments, double* __restrict__ deriv) {
+                   double* __restrict__ vscratch, double* __restrict__ wscratch, double* __restrict__ cscratch,
+                   size_t panel_doubles, double* __restrict__ auxscratch, double* __restrict__ moments,
+                   double* __restrict__ deriv) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, wm = warp >> 1, wn = warp & 1;
   const double* xs = reinterpret_cast<const double*>(smem + SM_CAND_OFF);
@@ -378,6 +382,7 @@ k_qei_grad_moments(const DevModel M, int type, int q, const double* __restrict__
   double* wpanel = wscratch + (size_t)blockIdx.x * (panel_doubles + COEF_DOUBLES);
   double* coef = wpanel + panel_doubles;
   double* gram = auxscratch + (size_t)blockIdx.x * QEI_AUX_DOUBLES;
+  double* cpanel = cscratch + (size_t)blockIdx.x * panel_doubles;
   const int n = M.n, d = M.d, p = M.p;
   const size_t dstride = qei_deriv_stride(d);
   pipeline_init(smem, tid);
@@ -386,7 +391,7 @@ k_qei_grad_moments(const DevModel M, int type, int q, const double* __restrict__
 #pragma unroll 1
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t b0 = tile * QB;
-    qei_tile_moments(M, type, q, x, B, b0, vpanel, gram, moments, coef, false, smem, tid, &stage_base);
+    qei_tile_moments(M, type, q, x, B, b0, vpanel, gram, moments, coef, false, smem, tid, &stage_base, cpanel);
 
     // ---- backward blocked solve: wt_l = T^-1 (v_l + M r_l) for all 64 columns ----
 #pragma unroll 1
@@ -425,11 +430,11 @@ k_qei_grad_moments(const DevModel M, int type, int q, const double* __restrict__
       const double cA = pass == 0 ? 1.0 : 0.0, cW = pass == 0 ? 0.0 : 1.0;
       const int cw = pass == 0 ? c : 4 * g + (pass - 1);
       switch (M.kernel) {
-        case DK_GAUSS: grad_accumulate<DK_GAUSS>(M, xs, wpanel, c, slice, cA, cW, gk, cw); break;
-        case DK_EXP: grad_accumulate<DK_EXP>(M, xs, wpanel, c, slice, cA, cW, gk, cw); break;
-        case DK_MATERN3_2: grad_accumulate<DK_MATERN3_2>(M, xs, wpanel, c, slice, cA, cW, gk, cw); break;
-        case DK_MATERN5_2: grad_accumulate<DK_MATERN5_2>(M, xs, wpanel, c, slice, cA, cW, gk, cw); break;
-        default: grad_accumulate<DK_POWEXP>(M, xs, wpanel, c, slice, cA, cW, gk, cw); break;
+        case DK_GAUSS: grad_accumulate<DK_GAUSS>(M, xs, cpanel, wpanel, c, slice, cA, cW, gk, cw); break;
+        case DK_EXP: grad_accumulate<DK_EXP>(M, xs, cpanel, wpanel, c, slice, cA, cW, gk, cw); break;
+        case DK_MATERN3_2: grad_accumulate<DK_MATERN3_2>(M, xs, cpanel, wpanel, c, slice, cA, cW, gk, cw); break;
+        case DK_MATERN5_2: grad_accumulate<DK_MATERN5_2>(M, xs, cpanel, wpanel, c, slice, cA, cW, gk, cw); break;
+        default: grad_accumulate<DK_POWEXP>(M, xs, cpanel, wpanel, c, slice, cA, cW, gk, cw); break;
       }
 #pragma unroll
       for (int k = 0; k < DK_MAX_D; k++)
