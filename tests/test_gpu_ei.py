@@ -209,3 +209,33 @@ def test_sample_from_ei_weights_and_draw(gpu_lib):
     assert out.shape == (7, 3) and np.all((out >= 0) & (out <= 1))
     assert sampleFromEI(km, n=1, seed=3, initdistrib=pts).shape == (1, 3)
     km.release()
+
+
+def test_cfg2_full_size_properties(gpu_lib):
+    """BASELINE config 2 at full size (hartman4, gauss, n = 200, N = 10^6): size-independent properties.
+    (i) a random subsample agrees with the oracle; (ii) screening the whole set equals the best of the
+    screens of its shards (the multi-GPU merge rule) and the argmax of the full EI vector; (iii) evaluating a
+    permuted candidate set permutes the result bit-for-bit (tiles do not leak into each other)."""
+    from diceoptim_b200 import EI, screen_EI, synth, parallel
+    from oracle import diceoptim as do
+    km = synth.config_model("cfg2_hartman4_n200")
+    x = synth.config_candidates("cfg2_hartman4_n200")
+    N = x.shape[0]
+    assert N == 1_000_000
+    ei = EI(x, km)
+    assert not np.isnan(ei).any() and np.all(ei >= 0)
+    sub = np.random.default_rng(0).choice(N, 1500, replace=False)
+    ref = do.EI(x[sub], to_oracle(km))
+    assert np.all(np.abs(ei[sub] - ref) <= 1e-9 * np.abs(ref) + 1e-12 * ref.max())
+    idx, val = screen_EI(x, km, k=3)
+    order = np.lexsort((np.arange(N), -ei))[:3]
+    assert list(idx) == list(order) and np.array_equal(val, ei[order])
+    shards = [parallel.shard_range(N, r, 4) for r in range(4)]
+    pairs = []
+    for lo, hi in shards:
+        i1, v1 = screen_EI(x[lo:hi], km)
+        pairs.append((v1[0], lo + i1[0]))
+    assert parallel.merge_argmax(pairs) == (val[0], idx[0])
+    perm = np.random.default_rng(1).permutation(N)
+    assert np.array_equal(EI(x[perm], km), ei[perm])
+    km.release()
