@@ -223,7 +223,8 @@ def test_cfg2_full_size_properties(gpu_lib):
     N = x.shape[0]
     assert N == 1_000_000
     ei = EI(x, km)
-    assert not np.isnan(ei).any() and np.all(ei >= 0)
+    assert int(np.isnan(ei).sum()) == 0
+    assert ei.min() >= -1e-14 * ei.max(), (ei.min(), int((ei < 0).sum()))   # (m - mean) Phi(u) + sd phi(u) rounds around 0 in the far tail
     sub = np.random.default_rng(0).choice(N, 1500, replace=False)
     ref = do.EI(x[sub], to_oracle(km))
     assert np.all(np.abs(ei[sub] - ref) <= 1e-9 * np.abs(ref) + 1e-12 * ref.max())
