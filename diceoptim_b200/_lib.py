@@ -56,6 +56,8 @@ SIGNATURES = {
     "dk_sample_weights_dev": (_I, [_V, _V, _L, _D, _I, _V, _V]),
     "dk_akg": (_I, [_V, _V, _L, _D, _I, _V]),
     "dk_akg_dev": (_I, [_V, _V, _L, _D, _I, _V, _V]),
+    "dk_akg_grad": (_I, [_V, _V, _L, _D, _I, _V, _V]),
+    "dk_akg_grad_dev": (_I, [_V, _V, _L, _D, _I, _V, _V, _V]),
     "dk_qei": (_I, [_V, _V, _L, _I, _D, _I, _I, _V]),
     "dk_qei_dev": (_I, [_V, _V, _L, _I, _D, _I, _I, _V, _V]),
     "dk_qei_grad": (_I, [_V, _V, _L, _I, _D, _I, _I, _V]),

@@ -305,3 +305,14 @@ def max_qEI(model: KM, npoints, lower, upper, crit="exact", minimization=True, o
         if best is None or -res.fun > best[1]:
             best = (res.x.reshape(npoints, d), float(-res.fun))
     return {"par": best[0], "value": best[1]}
+
+
+def AKG_grad(x, model: KM, new_noise_var=0.0, type="UK", envir=None, device=0):
+    """Gradient of AKG, R/AKG.grad.R:65-281 (envir = NULL path): length d for one point, N x d for a matrix."""
+    single = np.asarray(x).ndim <= 1
+    x = _as_candidates(x, model.d)
+    N = x.shape[0]
+    grad = np.empty((N, model.d), order="F")
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_akg_grad(h.ptr, _vp(x), N, float(new_noise_var), _type_id(type), _vp(grad), None), "dk_akg_grad")
+    return grad[0].copy() if single else grad

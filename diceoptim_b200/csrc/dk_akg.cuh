@@ -27,17 +27,32 @@ namespace dk {
 constexpr int AKG_MAX_SORT = 8192;  // n + 1 <= 8192: keys (8 B) + ranks (4 B) fill region 0 exactly
 constexpr int AKG_DIRS = 16;        // directions of the hull pre-filter (two per warp)
 
-// per-CTA scratch: sorted a, sorted b, stack a, stack b, stack cend : 5 arrays [n+1][64]
-__host__ __device__ inline size_t akg_scratch_doubles(int n) { return (size_t)5 * (n + 1) * BN; }
+constexpr int AKG_GRAD_MAX_HULL = 256;  // envelope members whose K^-1 rows the gradient kernel contracts
+
+// per-CTA scratch: sorted a, sorted b, stack a, stack b, stack cend, sorted rank, stack rank : 7 arrays [n+1][64]
+__host__ __device__ inline size_t akg_scratch_doubles(int n) { return (size_t)7 * (n + 1) * BN; }
+// per-CTA scratch of the gradient passes: one d x 64 block per weight vector (alpha, wt, p columns of T^-1 M, hull rows)
+__host__ __device__ inline size_t akg_grad_scratch_doubles(int d) {
+  return (size_t)(2 + DK_MAX_P + AKG_GRAD_MAX_HULL) * d * BN;
+}
 
 __device__ __forceinline__ bool akg_less(double b1, int r1, double b2, int r2) {
   return b1 < b2 || (b1 == b2 && r1 < r2);
 }
 
+// GRAD = true adds AKG.grad (R/AKG.grad.R:65-281, envir = NULL path).  In the engine's terms, with
+//   G1 = dc'alpha + beta f.deltax (gradient of mk.x), G2 = dc'wt, sk2.grad = -2 G2 + 2 r'f.deltax,
+//   G3 = (T^-1 M)'dc (UK), q_k = tuuinv (f.deltax[,k] - G3[,k]), H_t = (K^-1 dc)_{i_t} for envelope member i_t,
+// the per-line gradients are  A.grad = -G1 (own line) or 0,  B.grad = (delta_i H_t + 2 delta_i (T^-1 M)_i q)/den
+// - sk2.grad cn_i / (2 den^3) (design line i; the factor 2 is the reference's, :148) or
+// sk^2 (2 tau2 + sk^2)/den^4 sk2.grad / (2 sQ) (own line), and the sum of :258-264 follows, ct.grad as coded at :256.
+// m_min.grad is identically zero in the reference (:268-276).  dc = c .* dlogk is contracted once per weight vector.
+template <bool GRAD>
 __global__ void __launch_bounds__(NT, 2)
 k_akg_fused(const DevModel M, int type, double tau2, const double* __restrict__ x, int64_t N, int64_t ntiles,
             double* __restrict__ vscratch, double* __restrict__ wscratch, size_t panel_doubles,
-            double* __restrict__ akgscratch, double* __restrict__ out) {
+            double* __restrict__ akgscratch, double* __restrict__ out, double* __restrict__ cscratch,
+            const double* __restrict__ Kinv, double* __restrict__ gscratch, double* __restrict__ out_grad) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, wm = warp >> 1, wn = warp & 1;
   const double* xs = reinterpret_cast<const double*>(smem + SM_CAND_OFF);
@@ -51,13 +66,16 @@ k_akg_fused(const DevModel M, int type, double tau2, const double* __restrict__ 
   double* ka = sb + (size_t)m0 * BN;                                      // stack a
   double* kb = ka + (size_t)m0 * BN;                                      // stack b
   double* kc = kb + (size_t)m0 * BN;                                      // stack cend
+  double* sr = kc + (size_t)m0 * BN;                                      // sorted rank (as double)
+  double* kr = sr + (size_t)m0 * BN;                                      // stack rank
+  double* cpanel = GRAD ? cscratch + (size_t)blockIdx.x * panel_doubles : nullptr;
   pipeline_init(smem, tid);
   unsigned stage_base = 0;
 
 #pragma unroll 1
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t c0 = tile * BN;
-    forward_tile<true>(M, x, N, c0, vpanel, smem, tid, &stage_base);
+    forward_tile<true>(M, x, N, c0, vpanel, smem, tid, &stage_base, cpanel);
 
     if (tid < BN) {
       const int c = tid;
@@ -263,11 +281,14 @@ k_akg_fused(const DevModel M, int type, double tau2, const double* __restrict__ 
         const int r = keyr[j];
         sb[(size_t)j * BN + c] = keyb[j];
         sa[(size_t)j * BN + c] = (r & 1) ? ax : __ldg(M.akg_a_sorted + (r >> 1));
+        if (GRAD) sr[(size_t)j * BN + c] = (double)r;
       }
       __syncthreads();
     }
 
     // ---- 64 threads: drop equal slopes (keep the last), upper-envelope stack, Phi/phi sum ----
+    int* hlen = cnt + BN;  // envelope length per candidate (gradient kernel)
+    if (GRAD && tid < BN) hlen[tid] = 0;
     if (tid < BN && c0 + tid < N) {
       const int c = tid;
       const double mkx = __ldcg(coef + c), skx = __ldcg(coef + BN + c);
@@ -283,6 +304,7 @@ k_akg_fused(const DevModel M, int type, double tau2, const double* __restrict__ 
           const double aj = __ldcg(sa + (size_t)j * BN + c);
           if (len == 0) {
             ka[c] = aj; kb[c] = bj; ta = aj; tb = bj; len = 1;
+            if (GRAD) kr[c] = __ldcg(sr + (size_t)j * BN + c);
             continue;
           }
           int count = 0;
@@ -298,6 +320,7 @@ k_akg_fused(const DevModel M, int type, double tau2, const double* __restrict__ 
               kc[(size_t)(len - 1) * BN + c] = cu;
               cbelow = cu;
               ka[(size_t)len * BN + c] = aj; kb[(size_t)len * BN + c] = bj;
+              if (GRAD) kr[(size_t)len * BN + c] = __ldcg(sr + (size_t)j * BN + c);
               ta = aj; tb = bj; len++;
               break;
             }
@@ -314,8 +337,179 @@ k_akg_fused(const DevModel M, int type, double tau2, const double* __restrict__ 
         }
         const double m_min = fmin(M.akg_min_mkX, mkx);
         res = maxnew + m_min;  // AKG <- maxNew - (-m_min)
+        if (GRAD) hlen[c] = len;
       }
-      out[c0 + c] = res;
+      if (out) out[c0 + c] = res;
+    }
+    __syncthreads();
+
+    if constexpr (GRAD) {
+      const int d = M.d;
+      const int pu = (type == DK_UK) ? p : 0;
+      int maxlen = 0;
+      for (int c2 = 0; c2 < BN; c2++) maxlen = max(maxlen, hlen[c2]);
+      maxlen = min(maxlen, AKG_GRAD_MAX_HULL);
+      const int npass = 2 + pu + maxlen;
+      double* gbuf = reinterpret_cast<double*>(smem);  // [4][DK_MAX_D][64]
+      double* G = gscratch + (size_t)blockIdx.x * akg_grad_scratch_doubles(d);  // [pass][k][64]
+      {
+        const int c = tid & (BN - 1), slice = tid >> 6;
+#pragma unroll 1
+        for (int pass = 0; pass < npass; pass++) {
+          double g[DK_MAX_D];
+#pragma unroll
+          for (int k = 0; k < DK_MAX_D; k++) g[k] = 0.0;
+          const double* wvec = nullptr;
+          bool use_panel = false;
+          if (pass == 0) wvec = M.alpha;
+          else if (pass == 1) use_panel = true;
+          else if (pass < 2 + pu) wvec = M.KinvF + (size_t)(pass - 2) * n;
+          else {
+            const int t = pass - 2 - pu;
+            if (t < hlen[c]) {
+              const int r = (int)kr[(size_t)t * BN + c];
+              if (!(r & 1)) wvec = Kinv + (size_t)__ldg(M.akg_perm + (r >> 1)) * n;  // row of K^-1 (symmetric)
+            }
+          }
+          if (use_panel) {
+            switch (M.kernel) {
+              case DK_GAUSS: grad_accumulate<DK_GAUSS>(M, xs, cpanel, wpanel, c, slice, 0.0, 1.0, g); break;
+              case DK_EXP: grad_accumulate<DK_EXP>(M, xs, cpanel, wpanel, c, slice, 0.0, 1.0, g); break;
+              case DK_MATERN3_2: grad_accumulate<DK_MATERN3_2>(M, xs, cpanel, wpanel, c, slice, 0.0, 1.0, g); break;
+              case DK_MATERN5_2: grad_accumulate<DK_MATERN5_2>(M, xs, cpanel, wpanel, c, slice, 0.0, 1.0, g); break;
+              default: grad_accumulate<DK_POWEXP>(M, xs, cpanel, wpanel, c, slice, 0.0, 1.0, g); break;
+            }
+          } else if (wvec) {
+            switch (M.kernel) {
+              case DK_GAUSS: grad_accumulate_vec<DK_GAUSS>(M, xs, cpanel, wvec, c, slice, g); break;
+              case DK_EXP: grad_accumulate_vec<DK_EXP>(M, xs, cpanel, wvec, c, slice, g); break;
+              case DK_MATERN3_2: grad_accumulate_vec<DK_MATERN3_2>(M, xs, cpanel, wvec, c, slice, g); break;
+              case DK_MATERN5_2: grad_accumulate_vec<DK_MATERN5_2>(M, xs, cpanel, wvec, c, slice, g); break;
+              default: grad_accumulate_vec<DK_POWEXP>(M, xs, cpanel, wvec, c, slice, g); break;
+            }
+          }
+#pragma unroll
+          for (int k = 0; k < DK_MAX_D; k++)
+            if (k < d) gbuf[(slice * DK_MAX_D + k) * BN + c] = g[k];
+          __syncthreads();
+          for (int k = slice; k < d; k += 4)
+            G[((size_t)pass * d + k) * BN + c] = ((gbuf[(0 * DK_MAX_D + k) * BN + c] + gbuf[(1 * DK_MAX_D + k) * BN + c]) +
+                                                  gbuf[(2 * DK_MAX_D + k) * BN + c]) + gbuf[(3 * DK_MAX_D + k) * BN + c];
+          __syncthreads();
+        }
+      }
+      // ---- assembly: one thread per candidate walks its envelope ----
+      if (tid < BN && c0 + tid < N) {
+        const int c = tid, len = hlen[c];
+        const int64_t gi = c0 + c;
+        if (len == 0) {
+          for (int k = 0; k < d; k++) out_grad[gi + (int64_t)k * N] = 0.0;          // R/AKG.grad.R:126-127
+        } else if (len > AKG_GRAD_MAX_HULL) {
+          for (int k = 0; k < d; k++) out_grad[gi + (int64_t)k * N] = nan("");      // envelope longer than the scratch
+        } else {
+          const double skx = __ldcg(coef + BN + c);
+          const double den2 = tau2 + skx * skx, den = sqrt(den2), sQ = skx * skx / den;
+          const bool lin = M.trend == DK_TREND_LINEAR;
+          double grad[DK_MAX_D], sk2g[DK_MAX_D], meang[DK_MAX_D];
+          double atg_p[DK_MAX_D], btg_p[DK_MAX_D];
+          for (int k = 0; k < d; k++) {
+            grad[k] = 0.0;
+            meang[k] = __ldcg(G + ((size_t)0 * d + k) * BN + c) + (lin ? __ldg(M.beta + 1 + k) : 0.0);
+            sk2g[k] = -2.0 * __ldcg(G + ((size_t)1 * d + k) * BN + c) + (lin ? 2.0 * __ldcg(coef + (2 + 1 + k) * BN + c) : 0.0);
+          }
+          double at_p = 0.0, bt_p = 0.0, lo = -1e36;
+          for (int t = 0; t < len; t++) {
+            const double at = ka[(size_t)t * BN + c], bt = kb[(size_t)t * BN + c], hi = kc[(size_t)t * BN + c];
+            const int r = (int)kr[(size_t)t * BN + c];
+            const bool own = r & 1;
+            const int row = own ? 0 : __ldg(M.akg_perm + (r >> 1));
+            const double delta = own ? 0.0 : __ldg(M.akg_delta + row);
+            const double cn_i = bt * den;
+            const double pl = normcdf(hi) - normcdf(lo), dl = dnorm_std(lo) - dnorm_std(hi);
+            const double philo = dnorm_std(lo);
+            for (int k = 0; k < d; k++) {
+              double atg, btg;
+              if (own) {
+                atg = -meang[k];
+                btg = (skx * skx * (2.0 * tau2 + skx * skx) / (den2 * den2)) * sk2g[k] / (2.0 * sQ);
+              } else {
+                double cng = delta * __ldcg(G + ((size_t)(2 + pu + t) * d + k) * BN + c);
+                if (pu) {
+                  // mu.x.grad[k, i] = 2 delta_i (T^-1 M)[i, ] tuuinv (f.deltax[, k] - G3[, k])
+                  double mu = 0.0;
+                  for (int j = 0; j < p; j++) {
+                    double qj = 0.0;
+                    for (int j2 = 0; j2 < p; j2++) {
+                      const double fd = (lin && j2 == 1 + k) ? 1.0 : 0.0;
+                      qj = fma(__ldg(M.tuuinv + j + j2 * p), fd - __ldcg(G + ((size_t)(2 + j2) * d + k) * BN + c), qj);
+                    }
+                    mu = fma(__ldg(M.KinvF + row + (size_t)j * n), qj, mu);
+                  }
+                  cng = fma(2.0 * delta, mu, cng);
+                }
+                atg = 0.0;
+                btg = cng / den - sk2g[k] * cn_i * (0.5 / (den2 * den));
+              }
+              double gk = grad[k] + atg * pl + btg * dl;
+              if (t > 0) {
+                const double ctg = (atg_p[k] - atg) - (at_p - at) * (btg - btg_p[k]) / (bt - bt_p);
+                gk += ctg * philo * ((at_p + bt_p * lo) - (at + bt * lo));
+              }
+              grad[k] = gk;
+              atg_p[k] = atg; btg_p[k] = btg;
+            }
+            at_p = at; bt_p = bt; lo = hi;
+          }
+          for (int k = 0; k < d; k++) out_grad[gi + (int64_t)k * N] = grad[k];
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// K^-1 = T^-1 T^-T, 64 columns per tile: forward and backward blocked solves of identity columns with the same
+// DMMA code (model set-up for AKG.grad; candidate independent).
+__global__ void __launch_bounds__(NT, 2)
+k_kinv(const DevModel M, int64_t ntiles, double* __restrict__ vscratch, double* __restrict__ wscratch,
+       size_t panel_doubles, double* __restrict__ Kinv) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, wm = warp >> 1, wn = warp & 1;
+  double* vpanel = vscratch + (size_t)blockIdx.x * panel_doubles;
+  double* wpanel = wscratch + (size_t)blockIdx.x * (panel_doubles + COEF_DOUBLES);
+  const int n = M.n;
+  pipeline_init(smem, tid);
+  unsigned stage_base = 0;
+#pragma unroll 1
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int j0 = (int)tile * BN;
+    for (int pass = 0; pass < 2; pass++) {
+      const int nb = pass == 0 ? M.nblk : M.nblk_b;
+#pragma unroll 1
+      for (int I = 0; I < nb; I++) {
+        double acc[4][4][2];
+#pragma unroll
+        for (int mi = 0; mi < 4; mi++) {
+          const int ip = I * BM + 32 * wm + 8 * mi + (lane >> 2);
+#pragma unroll
+          for (int ni = 0; ni < 4; ni++)
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+              const int c = 32 * wn + 8 * ni + 2 * (lane & 3) + e;
+              double v = 0.0;
+              if (pass == 0) v = (ip == j0 + c && ip < n) ? 1.0 : 0.0;            // identity column
+              else if (ip < n) v = panel_at(vpanel, n - 1 - ip, c);               // flipped forward solution
+              acc[mi][ni][e] = v;
+            }
+        }
+        solve_block_row<true>(acc, pass == 0 ? M.tiles_fwd : M.tiles_bwd, I, pass == 0 ? vpanel : wpanel, smem, tid,
+                              &stage_base);
+        __syncthreads();
+      }
+    }
+    for (int idx = tid; idx < n * BN; idx += NT) {
+      const int i = idx % n, c = idx / n;
+      if (j0 + c < n) Kinv[(size_t)i + (size_t)(j0 + c) * n] = panel_at(wpanel, n - 1 - i, c);
     }
     __syncthreads();
   }

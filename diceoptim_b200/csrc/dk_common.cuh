@@ -137,6 +137,8 @@ struct dk_model {
   double* d_akg_const = nullptr; // a_sorted | delta
   int* d_akg_perm = nullptr;
   double* d_akg_scratch = nullptr;
+  double* d_Kinv = nullptr;        // K^-1, n x n (AKG.grad only, built lazily on the device)
+  double* d_akg_gscratch = nullptr; // per-CTA blocks of the AKG.grad contraction passes
   long long launches = 0;        // kernels launched through this handle
   int timing = 0;                // bracket the solve kernel with events
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;

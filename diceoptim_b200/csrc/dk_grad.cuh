@@ -29,10 +29,32 @@ __device__ __forceinline__ double rcp_pos(double x) {
   return r;
 }
 
-// g_k += sum_i c_i omega_i dlogk_k(x - X_i),  omega_i = cA alpha_i + cW wt_i[cw]  (covVector.dx contracted with the
-// adjoint weights).  c_i comes from the covariance panel the forward pass kept; rows i = slice, slice + 4, ...
+// g_k += cwv * dlogk_k(x - X_i) for all k (covVector.dx of one design row, already weighted).
 // With t = (x_k - X_ik) w_k and a = |t|:  gauss -t w ; exp -sign(t) w ; matern3_2 -w t / (1 + a) ;
 // matern5_2 -w (t / 3)(1 + a) / (1 + a + a^2 / 3) ; powexp -sign(t) p a^(p-1) w.
+template <int KERNEL>
+__device__ __forceinline__ void accum_dlogk(const DevModel& M, const double* __restrict__ xs,
+                                            const double* __restrict__ Xi, int c, double cwv, double (&g)[DK_MAX_D]) {
+  const int d = M.d;
+#pragma unroll
+  for (int k = 0; k < DK_MAX_D; k++) {
+    if (k < d) {
+      const double wk = M.w[k];
+      const double t = (xs[k * BN + c] - __ldg(Xi + k)) * wk;
+      const double a = fabs(t);
+      double dl;
+      if (KERNEL == DK_GAUSS) dl = -t * wk;
+      else if (KERNEL == DK_EXP) dl = (t > 0.0) ? -wk : ((t < 0.0) ? wk : 0.0);
+      else if (KERNEL == DK_MATERN3_2) dl = -wk * t * rcp_pos(1.0 + a);
+      else if (KERNEL == DK_MATERN5_2) dl = -(wk * (1.0 / 3.0)) * t * (1.0 + a) * rcp_pos(fma(a, fma(a, 1.0 / 3.0, 1.0), 1.0));
+      else dl = (a > 0.0) ? -copysign(M.shape[k] * pow(a, M.shape[k] - 1.0) * wk, t) : 0.0;
+      g[k] = fma(cwv, dl, g[k]);
+    }
+  }
+}
+
+// g_k += sum_i c_i omega_i dlogk_k(x - X_i),  omega_i = cA alpha_i + cW wt_i[cw]  (covVector.dx contracted with the
+// adjoint weights).  c_i comes from the covariance panel the forward pass kept; rows i = slice, slice + 4, ...
 template <int KERNEL>
 __device__ __forceinline__ void grad_accumulate(const DevModel& M, const double* __restrict__ xs,
                                                 const double* __restrict__ cpanel, const double* __restrict__ wpanel,
@@ -42,24 +64,22 @@ __device__ __forceinline__ void grad_accumulate(const DevModel& M, const double*
   const int n = M.n, d = M.d;
 #pragma unroll 1
   for (int i = slice; i < n; i += 4) {
-    const double* Xi = M.Xrm + (size_t)i * d;
     const double omega = cA * __ldg(M.alpha + i) + cW * panel_at(wpanel, n - 1 - i, cw);
     const double cwv = __ldcg(cpanel + (size_t)i * BN + c) * omega;
-#pragma unroll
-    for (int k = 0; k < DK_MAX_D; k++) {
-      if (k < d) {
-        const double wk = M.w[k];
-        const double t = (xs[k * BN + c] - __ldg(Xi + k)) * wk;
-        const double a = fabs(t);
-        double dl;
-        if (KERNEL == DK_GAUSS) dl = -t * wk;
-        else if (KERNEL == DK_EXP) dl = (t > 0.0) ? -wk : ((t < 0.0) ? wk : 0.0);
-        else if (KERNEL == DK_MATERN3_2) dl = -wk * t * rcp_pos(1.0 + a);
-        else if (KERNEL == DK_MATERN5_2) dl = -(wk * (1.0 / 3.0)) * t * (1.0 + a) * rcp_pos(fma(a, fma(a, 1.0 / 3.0, 1.0), 1.0));
-        else dl = (a > 0.0) ? -copysign(M.shape[k] * pow(a, M.shape[k] - 1.0) * wk, t) : 0.0;
-        g[k] = fma(cwv, dl, g[k]);
-      }
-    }
+    accum_dlogk<KERNEL>(M, xs, M.Xrm + (size_t)i * d, c, cwv, g);
+  }
+}
+
+// Same contraction with the weights read from a plain vector (stride 1): rows of K^-1, columns of T^-1 M, alpha.
+template <int KERNEL>
+__device__ __forceinline__ void grad_accumulate_vec(const DevModel& M, const double* __restrict__ xs,
+                                                    const double* __restrict__ cpanel, const double* __restrict__ wvec,
+                                                    int c, int slice, double (&g)[DK_MAX_D]) {
+  const int n = M.n, d = M.d;
+#pragma unroll 1
+  for (int i = slice; i < n; i += 4) {
+    const double cwv = __ldcg(cpanel + (size_t)i * BN + c) * __ldg(wvec + i);
+    accum_dlogk<KERNEL>(M, xs, M.Xrm + (size_t)i * d, c, cwv, g);
   }
 }
 

@@ -135,6 +135,14 @@ int dk_sample_weights_dev(dk_model* m, const double* d_x, int64_t N, double T, i
 int dk_akg(dk_model* m, const double* x, int64_t N, double new_noise_var, int type, double* out);
 int dk_akg_dev(dk_model* m, const double* d_x, int64_t N, double new_noise_var, int type, double* d_out, void* stream);
 
+/* AKG.grad(x, model, new.noise.var, type) for every row of x — replaces /root/reference/R/AKG.grad.R:65-281
+ * (envir = NULL path; the reference's quirks are kept: factor 2 in mu.x.grad, m_min.grad never taken).
+ * out_grad is N x d; out_akg (N, the AKG values from the same pass) may be NULL.  Builds K^-1 on the device at
+ * the first call (n^2 doubles).  A candidate whose envelope has more than 256 lines gets NaN. */
+int dk_akg_grad(dk_model* m, const double* x, int64_t N, double new_noise_var, int type, double* out_grad, double* out_akg);
+int dk_akg_grad_dev(dk_model* m, const double* d_x, int64_t N, double new_noise_var, int type, double* d_grad,
+                    double* d_akg, void* stream);
+
 /* qEI(x, model, plugin, type, minimization) for B batches of q points — replaces
  * /root/reference/R/qEI.R:119-261 (incl. covZk / get_cik / get_sigmaik and the duplicate test of
  * R/qEI.R:124-128).  x is (B*q) x d column-major; rows b*q .. b*q+q-1 form batch b.  1 <= q <= DK_MAX_Q.

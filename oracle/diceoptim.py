@@ -504,3 +504,89 @@ def qEI_grad(x, model, plugin=None, type="UK", minimization=True, fastCompute=Tr
     if np.isnan(G.sum()):
         return np.zeros((q, d))
     return G
+
+
+# ----------------------------------------------------------------------------------------
+# AKG.grad (R/AKG.grad.R:65-281), envir = NULL path
+# ----------------------------------------------------------------------------------------
+def AKG_grad(x, model, new_noise_var=0.0, type="UK", envir=None):
+    """Line-by-line restatement, reference quirks included: mu.x.grad carries a factor 2 (:148), ct.grad lacks
+    the 1/(bt[i+1]-bt[i]) scaling (:256; it multiplies a term that vanishes at the breakpoints), and m_min.grad
+    is never taken because which.min(c(m_min, mk.x)) is 1 whenever mk.x attains the minimum (:268-276)."""
+    x = np.asarray(x, float).ravel()
+    d, n = model.d, model.n
+    tau2 = new_noise_var
+    T, z, U, F_X = model.T, model.z, model.M, model.F
+    cov = model.covariance
+    predx = dk.predict_km(model, x[None, :], type=type)
+    mk_x = predx["mean"][0]; sk_x = predx["sd"][0]
+    c_x = predx["c"][:, 0]; V_x = predx["Tinv.c"][:, 0]
+    F_x = dk.model_matrix(model.trend, x[None, :])
+    if sk_x < np.sqrt(cov.sd2) / 1e6 or cov.sd2 < 1e-20:      # :126
+        return np.zeros(d)
+    predX = dk.predict_km(model, model.X, type=type)
+    mk_X = predX["mean"]; V_X = predX["Tinv.c"]
+    if type == "UK":
+        tuuinv = np.linalg.inv(U.T @ U)
+        mu_x = ((F_X - V_X.T @ U) @ tuuinv @ (F_x - V_x[None, :] @ U).T).ravel()
+    else:
+        mu_x = 0.0
+    cn = c_x - V_X.T @ V_x + mu_x
+    cn = np.append(cn, sk_x ** 2)
+    a = np.append(mk_X, mk_x)
+    den2 = tau2 + sk_x ** 2
+    b = cn / np.sqrt(den2)
+    sQ = b[n]
+    dc = dk.cov_vector_dx(cov, x, model.X, c_x)
+    fdx = dk.trend_deltax(model.trend, d)
+    W = solve_triangular(T, dc, trans="T", lower=False)
+    a_grad = np.zeros((d, n + 1))
+    a_grad[:, n] = W.T @ z + model.trend_coef @ fdx
+    b_grad = np.zeros((d, n + 1))
+    if type == "UK":
+        sk2_grad = (-2.0 * V_x @ W + 2.0 * (F_x - V_x[None, :] @ U) @ tuuinv @ (fdx - (W.T @ U).T)).ravel()
+        mu_x_grad = (2.0 * (F_X - V_X.T @ U) @ tuuinv @ (fdx - (W.T @ U).T)).T      # d x n
+    else:
+        sk2_grad = (-2.0 * V_x @ W).ravel()
+        mu_x_grad = np.zeros((d, n))
+    cn_grad = dc.T - (V_X.T @ W).T + mu_x_grad
+    b_grad[:, :n] = cn_grad / np.sqrt(den2) - np.outer(sk2_grad, cn[:n]) * (0.5 / den2 ** 1.5)
+    b_grad[:, n] = (sk_x ** 2 * (2 * tau2 + sk_x ** 2) / den2 ** 2) * sk2_grad / (2.0 * sQ)
+    A = -a; B = b; B_grad = b_grad; A_grad = -a_grad
+    Isort = np.lexsort((A, B))
+    bs = B[Isort]; as_ = A[Isort]; bg = B_grad[:, Isort]; ag = A_grad[:, Isort]
+    keep = np.ones(bs.size, bool)
+    for i in range(n):
+        if bs[i + 1] == bs[i]:
+            keep[i] = False
+    bs = bs[keep]; as_ = as_[keep]; bg = bg[:, keep]; ag = ag[:, keep]
+    nobs = as_.size - 1
+    C = np.zeros(nobs + 2); C[0] = -1e36; C[-1] = 1e36
+    A1 = [0]
+    for k in range(2, nobs + 2):
+        nondom = 1
+        if k != nobs + 1 and as_[k] >= as_[k - 1] and bs[k - 1] == bs[k]:
+            nondom = 0
+        if nondom:
+            count = 0
+            while count < 1000:
+                count += 1
+                u = A1[-1] + 1
+                C[u] = (as_[u - 1] - as_[k - 1]) / (bs[k - 1] - bs[u - 1])
+                if len(A1) > 1 and C[u] <= C[A1[-2] + 1]:
+                    A1.pop()
+                else:
+                    A1.append(k - 1)
+                    break
+    A1 = np.asarray(A1)
+    at = as_[A1]; bt = bs[A1]; ct = C[np.concatenate(([0], A1 + 1))]
+    nt = at.size
+    atg = ag[:, A1]; btg = bg[:, A1]
+    ctg = np.zeros((d, nt + 1))
+    for i in range(nt - 1):
+        ctg[:, i + 1] = (atg[:, i] - atg[:, i + 1]) - (at[i] - at[i + 1]) * (btg[:, i + 1] - btg[:, i]) / (bt[i + 1] - bt[i])
+    g = np.zeros(d)
+    for k in range(nt):
+        g += (atg[:, k] * (pnorm(ct[k + 1]) - pnorm(ct[k])) + btg[:, k] * (dnorm(ct[k]) - dnorm(ct[k + 1]))
+              + ctg[:, k + 1] * dnorm(ct[k + 1]) * (at[k] + bt[k] * ct[k + 1]) - ctg[:, k] * dnorm(ct[k]) * (at[k] + bt[k] * ct[k]))
+    return g

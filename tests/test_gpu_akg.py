@@ -62,3 +62,39 @@ def test_akg_zero_at_design_points_and_size_limit(gpu_lib):
     km = small_model("matern5_2", "const", n=25, d=2, seed=1)          # noise-free: sk.x = 0 at the design
     assert np.all(AKG(km.X[:5], km, new_noise_var=0.1) == 0.0)          # guard of R/AKG.R:115
     km.release()
+
+
+@pytest.mark.parametrize("trend,type", [("const", "UK"), ("const", "SK"), ("linear", "UK")])
+def test_akg_grad_matches_oracle(gpu_lib, trend, type):
+    """AKG.grad (R/AKG.grad.R) vs the oracle's restatement (reference quirks included); the oracle itself is
+    checked against finite differences of AKG for type SK in tests/test_oracle_basic.py."""
+    from diceoptim_b200 import AKG_grad
+    from oracle import diceoptim as do
+    rng = np.random.default_rng(11)
+    km = small_model("matern5_2", trend, n=90, d=3, seed=421, noise_var=0.02 + 0.03 * rng.random(90))
+    ko = to_oracle(km)
+    x = rng.random((40, 3))
+    got = AKG_grad(x, km, new_noise_var=0.02, type=type)
+    assert got.shape == (40, 3)
+    for j in range(40):
+        ref = do.AKG_grad(x[j], ko, new_noise_var=0.02, type=type)
+        assert np.max(np.abs(got[j] - ref)) <= 1e-7 * np.max(np.abs(ref)) + 1e-13, (j, got[j], ref)
+    assert np.allclose(AKG_grad(x[3], km, new_noise_var=0.02, type=type), got[3], rtol=1e-12, atol=1e-300)
+    km.release()
+
+
+def test_akg_grad_other_kernels_and_guard(gpu_lib):
+    from diceoptim_b200 import AKG_grad
+    from oracle import diceoptim as do
+    rng = np.random.default_rng(2)
+    for name in ("gauss", "matern3_2"):
+        km = small_model(name, "const", n=40, d=2, seed=5, noise_var=0.05)
+        x = rng.random((12, 2))
+        got = AKG_grad(x, km, new_noise_var=0.05)
+        for j in range(12):
+            ref = do.AKG_grad(x[j], to_oracle(km), new_noise_var=0.05)
+            assert np.max(np.abs(got[j] - ref)) <= 1e-7 * np.max(np.abs(ref)) + 1e-13
+        km.release()
+    kd = small_model("matern5_2", "const", n=25, d=2, seed=1)
+    assert np.all(AKG_grad(kd.X[:4], kd, new_noise_var=0.1) == 0.0)     # sk.x = 0 at the design: zero gradient
+    kd.release()

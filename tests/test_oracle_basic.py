@@ -66,3 +66,22 @@ def test_akg_runs_and_is_nonnegative():
     m = to_oracle(synth.make_km(X, y, "matern5_2", [0.4, 0.5], float(np.var(y)), noise_var=0.2))
     vals = [do.AKG(x, m, new_noise_var=0.2) for x in rng.random((10, 2))]
     assert all(np.isfinite(v) and v >= -1e-12 for v in vals)
+
+
+def test_akg_grad_oracle_vs_finite_differences_sk():
+    """SK only: for UK the reference's mu.x.grad carries a spurious factor 2 (R/AKG.grad.R:148), restated as is."""
+    from diceoptim_b200 import synth
+    rng = np.random.default_rng(3)
+    m = to_oracle(small_model("matern5_2", "const", n=25, d=2, seed=421, noise_var=0.02 + 0.03 * rng.random(25)))
+    checked = 0
+    for _ in range(12):
+        x = rng.random(2)
+        g = do.AKG_grad(x, m, new_noise_var=0.02, type="SK")
+        if np.max(np.abs(g)) < 1e-9:
+            continue
+        h = 1e-6
+        fd = np.array([(do.AKG(x + h * e, m, new_noise_var=0.02, type="SK") - do.AKG(x - h * e, m, new_noise_var=0.02, type="SK")) / (2 * h)
+                       for e in np.eye(2)])
+        assert np.max(np.abs(g - fd)) <= 1e-3 * np.max(np.abs(g)) + 1e-12
+        checked += 1
+    assert checked >= 2
