@@ -6,8 +6,8 @@ include/dk_b200.h), the ctypes binding, and the host-side mirror of the R interf
 DiceKriging; ``synth`` only builds km objects with FIXED hyper-parameters for tests and bench.
 """
 from .km import KM, Covariance, DeviceModel  # noqa: F401
-from .api import (AKG, AKG_grad, EI, EI_grad, kriging_quantile, kriging_quantile_grad, max_crit, max_qEI, predict, qEI, qEI_grad,  # noqa: F401
+from .api import (AEI, AKG, AKG_grad, EI, EQI, EI_grad, kriging_quantile, kriging_quantile_grad, max_crit, max_qEI, predict, qEI, qEI_grad,  # noqa: F401
                   sampleFromEI, screen_EI)
 
-__all__ = ["AKG", "AKG_grad", "KM", "Covariance", "DeviceModel", "EI", "EI_grad", "kriging_quantile", "kriging_quantile_grad",
+__all__ = ["AEI", "EQI", "AKG", "AKG_grad", "KM", "Covariance", "DeviceModel", "EI", "EI_grad", "kriging_quantile", "kriging_quantile_grad",
            "max_crit", "max_qEI", "predict", "qEI", "qEI_grad", "sampleFromEI", "screen_EI"]

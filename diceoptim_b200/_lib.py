@@ -54,6 +54,10 @@ SIGNATURES = {
     "dk_screen_ei": (_I, [_V, _V, _I, _L, _D, _I, _I, _I, _I, _V, _V, _V]),
     "dk_sample_weights": (_I, [_V, _V, _L, _D, _I, _V]),
     "dk_sample_weights_dev": (_I, [_V, _V, _L, _D, _I, _V, _V]),
+    "dk_aei": (_I, [_V, _V, _L, _D, _D, _I, _V]),
+    "dk_aei_dev": (_I, [_V, _V, _L, _D, _D, _I, _V, _V]),
+    "dk_eqi": (_I, [_V, _V, _L, _D, _D, _D, _I, _V]),
+    "dk_eqi_dev": (_I, [_V, _V, _L, _D, _D, _D, _I, _V, _V]),
     "dk_akg": (_I, [_V, _V, _L, _D, _I, _V]),
     "dk_akg_dev": (_I, [_V, _V, _L, _D, _I, _V, _V]),
     "dk_akg_grad": (_I, [_V, _V, _L, _D, _I, _V, _V]),

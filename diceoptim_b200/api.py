@@ -316,3 +316,30 @@ def AKG_grad(x, model: KM, new_noise_var=0.0, type="UK", envir=None, device=0):
     h = model.handle(device)
     _lib.check(_lib.load().dk_akg_grad(h.ptr, _vp(x), N, float(new_noise_var), _type_id(type), _vp(grad), None), "dk_akg_grad")
     return grad[0].copy() if single else grad
+
+
+def AEI(x, model: KM, new_noise_var=0.0, y_min=None, type="UK", envir=None, device=0):
+    """Augmented expected improvement, R/AEI.R:105-146 (rows batched)."""
+    single = np.asarray(x).ndim <= 1
+    if y_min is None:                                        # R/AEI.R:116-122
+        pr = predict(model, model.X, type=type, device=device)
+        y_min = float(pr["mean"][int(np.argmin(pr["mean"] + ndtri(0.75) * pr["sd"]))])
+    x = _as_candidates(x, model.d)
+    out = np.empty(x.shape[0])
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_aei(h.ptr, _vp(x), x.shape[0], float(y_min), float(new_noise_var), _type_id(type), _vp(out)), "dk_aei")
+    return float(out[0]) if single else out
+
+
+def EQI(x, model: KM, new_noise_var=0.0, beta=0.9, q_min=None, type="UK", envir=None, device=0):
+    """Expected quantile improvement, R/EQI.R:100-151 (rows batched)."""
+    single = np.asarray(x).ndim <= 1
+    if q_min is None:                                        # R/EQI.R:110-112
+        pr = predict(model, model.X, type=type, device=device)
+        q_min = float(np.min(pr["mean"] + ndtri(beta) * pr["sd"]))
+    x = _as_candidates(x, model.d)
+    out = np.empty(x.shape[0])
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_eqi(h.ptr, _vp(x), x.shape[0], float(q_min), float(new_noise_var), float(ndtri(beta)),
+                                  _type_id(type), _vp(out)), "dk_eqi")
+    return float(out[0]) if single else out

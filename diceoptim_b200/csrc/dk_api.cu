@@ -1010,3 +1010,58 @@ extern "C" int dk_akg_grad(dk_model* m, const double* x, int64_t N, double new_n
   if ((rc = h.fetch(out_akg, d_akg, N))) return rc;
   return h.finish();
 }
+
+#ifdef DK_PHASE_TIMING
+/* Debug build only (tools/phase_timing.py): copy out the per-phase cycle counters. */
+extern "C" int dk_debug_phase_cycles(unsigned long long* out8) {
+  DK_CUDA_TRY(cudaMemcpyFromSymbol(out8, dk::g_phase_cycles, 8 * sizeof(unsigned long long)));
+  return DK_OK;
+}
+#endif
+
+// ------------------------------------------------------------------------------------------
+// AEI (R/AEI.R:105-146) and EQI (R/EQI.R:100-151): noisy-criteria epilogues on the same predict kernel
+// ------------------------------------------------------------------------------------------
+extern "C" int dk_aei_dev(dk_model* m, const double* d_x, int64_t N, double y_min, double new_noise_var, int type,
+                          double* d_out, void* stream) {
+  int rc = check_call(m, d_x, N);
+  if (rc) return rc;
+  if (!d_out) return fail(DK_ERR_ARG, "d_out is NULL");
+  if (!(new_noise_var >= 0)) return fail(DK_ERR_ARG, "new.noise.var must be >= 0");
+  DeviceGuard guard(m->device);
+  CritParams P{MODE_AEI, type, 1, 0, y_min, 0.0, new_noise_var, m->dm.sd2};
+  return launch_predict(m, P, d_x, N, d_out, nullptr, nullptr, (cudaStream_t)stream);
+}
+extern "C" int dk_eqi_dev(dk_model* m, const double* d_x, int64_t N, double q_min, double new_noise_var, double qnorm_beta,
+                          int type, double* d_out, void* stream) {
+  int rc = check_call(m, d_x, N);
+  if (rc) return rc;
+  if (!d_out) return fail(DK_ERR_ARG, "d_out is NULL");
+  if (!(new_noise_var >= 0)) return fail(DK_ERR_ARG, "new.noise.var must be >= 0");
+  DeviceGuard guard(m->device);
+  CritParams P{MODE_EQI, type, 1, 0, q_min, qnorm_beta, new_noise_var, m->dm.sd2};
+  return launch_predict(m, P, d_x, N, d_out, nullptr, nullptr, (cudaStream_t)stream);
+}
+extern "C" int dk_aei(dk_model* m, const double* x, int64_t N, double y_min, double new_noise_var, int type, double* out) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (!out) return fail(DK_ERR_ARG, "out is NULL");
+  DeviceGuard guard(m->device);
+  HostCall h;
+  if ((rc = h.init(m, x, N, (size_t)N))) return rc;
+  if ((rc = dk_aei_dev(m, h.d_x, N, y_min, new_noise_var, type, h.d_out, m->stream))) return rc;
+  if ((rc = h.fetch(out, h.d_out, N))) return rc;
+  return h.finish();
+}
+extern "C" int dk_eqi(dk_model* m, const double* x, int64_t N, double q_min, double new_noise_var, double qnorm_beta, int type,
+                      double* out) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (!out) return fail(DK_ERR_ARG, "out is NULL");
+  DeviceGuard guard(m->device);
+  HostCall h;
+  if ((rc = h.init(m, x, N, (size_t)N))) return rc;
+  if ((rc = dk_eqi_dev(m, h.d_x, N, q_min, new_noise_var, qnorm_beta, type, h.d_out, m->stream))) return rc;
+  if ((rc = h.fetch(out, h.d_out, N))) return rc;
+  return h.finish();
+}

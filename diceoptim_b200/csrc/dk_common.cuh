@@ -23,7 +23,7 @@ constexpr int BM = 128;
 constexpr int BN = 64;
 constexpr int KC = 16;
 constexpr int NT = 256;          // threads per CTA: 8 warps as 4 (rows) x 2 (cols), warp tile 32 x 32
-constexpr int STAGES = 3;
+constexpr int STAGES = 4;   // 4 x 24 KB = region 0 exactly (the design-row staging is dead during the GEMM phase)
 constexpr int A_TILE = BM * KC;  // doubles
 constexpr int B_TILE = KC * BN;  // doubles
 constexpr int CB_STRIDE = 72;    // row stride (doubles) of the covariance staging tile
@@ -79,11 +79,13 @@ struct DevModel {
   double theta[DK_MAX_D];
 };
 
-enum Mode { MODE_PREDICT = 0, MODE_EI = 1, MODE_QUANTILE = 2, MODE_EI_WEIGHT = 3 };
+enum Mode { MODE_PREDICT = 0, MODE_EI = 1, MODE_QUANTILE = 2, MODE_EI_WEIGHT = 3, MODE_AEI = 4, MODE_EQI = 5 };
 
 struct CritParams {
   int mode, type, minimization, proxy;
   double plugin, qnorm_beta;
+  double tau2;  // new.noise.var (AEI, EQI)
+  double sd2;   // covariance@sd2 for the negligible-sd guards of AEI / EQI
 };
 
 // ---------------------------------------------------------------------------------------

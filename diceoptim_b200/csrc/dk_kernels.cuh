@@ -20,6 +20,24 @@
 
 namespace dk {
 
+// Optional per-phase cycle accounting (build with -DDK_PHASE_TIMING; tools/phase_timing.py): thread 0 of every CTA
+// adds the cycles between marks to g_phase_cycles[phase].  Not compiled into the shipped library.
+#ifdef DK_PHASE_TIMING
+__device__ unsigned long long g_phase_cycles[8];
+#define DK_MARK(ph)                                                                  \
+  do {                                                                               \
+    if (threadIdx.x == 0) {                                                          \
+      const long long now__ = clock64();                                             \
+      atomicAdd(&g_phase_cycles[ph], (unsigned long long)(now__ - dk_t0__));         \
+      dk_t0__ = now__;                                                               \
+    }                                                                                \
+  } while (0)
+#define DK_MARK_INIT long long dk_t0__ = clock64()
+#else
+#define DK_MARK(ph) do { } while (0)
+#define DK_MARK_INIT do { } while (0)
+#endif
+
 __device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
   asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
       : "+d"(c[0]), "+d"(c[1])
@@ -191,6 +209,7 @@ template <bool TMA = false>
 __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const double* __restrict__ tiles, int I,
                                                 double* __restrict__ panel, unsigned char* smem, int tid,
                                                 unsigned* stage_base = nullptr) {
+  DK_MARK_INIT;
   const int warp = tid >> 5, lane = tid & 31, wm = warp >> 1, wn = warp & 1;
   double* ring = reinterpret_cast<double*>(smem);
   const double* Atiles = tiles + tile_base(I) * A_TILE;
@@ -223,6 +242,7 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
     }
     *stage_base = base + nk;
     __syncthreads();  // every warp is done with the ring: region 0 can change role
+    DK_MARK(2);
   } else {
   // ---- P3: acc += (-L_IJ) V_J over all k-chunks left of the diagonal block -----------------
 #pragma unroll
@@ -285,6 +305,7 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
       mma_stage(acc, Abuf + (j & 1) * A_TILE, Rbuf + j * B_TILE, wm, wn, lane);
   }
 
+  DK_MARK(3);
   // ---- P5: publish V_I to the panel (fragment-ordered B tiles) -----------------------------
 #pragma unroll
   for (int mi = 0; mi < 4; mi++) {
@@ -300,6 +321,7 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
   }
   // the panel is next read through the async proxy (bulk copies): order these generic-proxy stores before it
   if constexpr (TMA) asm volatile("fence.proxy.async.global;" ::: "memory");
+  DK_MARK(4);
 }
 
 __device__ __forceinline__ double panel_at(const double* panel, int row, int col) {
@@ -352,6 +374,20 @@ __device__ __forceinline__ double crit_value(const CritParams& P, double mean, d
     if (ei != ei) ei = P.minimization ? (P.plugin - mean) : (mean - P.plugin);
     return ei > 0.0 ? ei : 0.0;
   }
+  if (P.mode == MODE_AEI) {
+    // R/AEI.R:128-143: EI against y.min times the noise penalty 1 - tau / sqrt(tau^2 + sk^2); 0 when sk is negligible
+    if (sd < sqrt(P.sd2) / 1e6) return 0.0;
+    const double diff = P.plugin - mean, xcr = diff / sd;
+    return (diff * normcdf(xcr) + sd * dnorm_std(xcr)) * (1.0 - sqrt(P.tau2) / sqrt(P.tau2 + sd * sd));
+  }
+  if (P.mode == MODE_EQI) {
+    // R/EQI.R:121-148: improvement of the future beta-quantile; mq, sq from the old mean / sd and new.noise.var
+    if (sd < sqrt(P.sd2) / 1e6) return 0.0;
+    const double mq = mean + P.qnorm_beta * sqrt((P.tau2 * sd * sd) / (P.tau2 + sd * sd));
+    const double sq = sd * sd / sqrt(P.tau2 + sd * sd);
+    const double xcr = (P.plugin - mq) / sq;
+    return sq * (xcr * normcdf(xcr) + dnorm_std(xcr));
+  }
   const double km = P.minimization ? mean : -mean;
   const double diff = P.plugin - km;
   if (P.proxy) return diff;
@@ -394,8 +430,10 @@ __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __
   }
   if (tid < 4 * BN) s2acc[tid] = 0.0;
 
+  DK_MARK_INIT;
 #pragma unroll 1
   for (int I = 0; I < M.nblk; I++) {
+    DK_MARK(6);
     // ---- P1: design rows of this block -> smem, then covariance block -> Cbuf ----
     {
       const double* src = M.Xrm + (size_t)I * BM * d;
@@ -419,8 +457,10 @@ __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __
                                       2 * (lane & 3)) = v;
       }
     __syncthreads();
+    DK_MARK(0);  // P1 + P2: cov-gen and fragment load
     // ---- P3..P5 ----
     solve_block_row<TMA>(acc, M.tiles_fwd, I, panel, smem, tid, stage_base);
+    DK_MARK(7);  // (solve_block_row accounts 2 = GEMM, 3 = diagonal, 4 = panel store itself)
     // ---- s2 += sum over this block's real rows of v^2 (fixed order: rows, then lanes, then warps) ----
     {
       double part[4][2];
@@ -449,6 +489,7 @@ __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __
         }
     }
     __syncthreads();  // panel writes + s2acc visible; region 0 free for the next block row
+    DK_MARK(5);  // s2 reduction + barrier
   }
 }
 

@@ -130,6 +130,15 @@ int dk_screen_ei(dk_model* m, const double* x, int x_on_device, int64_t N, doubl
 int dk_sample_weights(dk_model* m, const double* x, int64_t N, double T, int minimization, double* out_w);
 int dk_sample_weights_dev(dk_model* m, const double* d_x, int64_t N, double T, int minimization, double* d_w, void* stream);
 
+/* AEI(x, model, new.noise.var, y.min, type) and EQI(x, model, new.noise.var, beta, q.min, type) for every row of x
+ * — replace /root/reference/R/AEI.R:105-146 and R/EQI.R:100-151.  y_min / q_min must be given (the R defaults come
+ * from one dk_predict over model@X: mk[which.min(mk + qnorm(0.75) sk)] and min(mk + qnorm(beta) sk)). */
+int dk_aei(dk_model* m, const double* x, int64_t N, double y_min, double new_noise_var, int type, double* out);
+int dk_aei_dev(dk_model* m, const double* d_x, int64_t N, double y_min, double new_noise_var, int type, double* d_out, void* stream);
+int dk_eqi(dk_model* m, const double* x, int64_t N, double q_min, double new_noise_var, double qnorm_beta, int type, double* out);
+int dk_eqi_dev(dk_model* m, const double* d_x, int64_t N, double q_min, double new_noise_var, double qnorm_beta, int type,
+               double* d_out, void* stream);
+
 /* AKG(x, model, new.noise.var, type) for every row of x (the reference evaluates one row per call and
  * re-predicts at the whole design each time) — replaces /root/reference/R/AKG.R:93-229.  Needs n + 1 <= 8192. */
 int dk_akg(dk_model* m, const double* x, int64_t N, double new_noise_var, int type, double* out);

@@ -590,3 +590,33 @@ def AKG_grad(x, model, new_noise_var=0.0, type="UK", envir=None):
         g += (atg[:, k] * (pnorm(ct[k + 1]) - pnorm(ct[k])) + btg[:, k] * (dnorm(ct[k]) - dnorm(ct[k + 1]))
               + ctg[:, k + 1] * dnorm(ct[k + 1]) * (at[k] + bt[k] * ct[k + 1]) - ctg[:, k] * dnorm(ct[k]) * (at[k] + bt[k] * ct[k]))
     return g
+
+
+def AEI(x, model, new_noise_var=0.0, y_min=None, type="UK", envir=None):
+    """R/AEI.R:105-146 at one point."""
+    x = np.asarray(x, float).ravel()
+    if y_min is None:
+        pr = dk.predict_km(model, model.X, type=type)
+        y_min = pr["mean"][int(np.argmin(pr["mean"] + qnorm(0.75) * pr["sd"]))]
+    pr = dk.predict_km(model, x[None, :], type=type)
+    mk, sk = pr["mean"][0], pr["sd"][0]
+    if sk < np.sqrt(model.covariance.sd2) / 1e6:
+        return 0.0
+    xcr = (y_min - mk) / sk
+    return float(((y_min - mk) * pnorm(xcr) + sk * dnorm(xcr)) * (1.0 - np.sqrt(new_noise_var) / np.sqrt(new_noise_var + sk ** 2)))
+
+
+def EQI(x, model, new_noise_var=0.0, beta=0.9, q_min=None, type="UK", envir=None):
+    """R/EQI.R:100-151 at one point."""
+    x = np.asarray(x, float).ravel()
+    if q_min is None:
+        pr = dk.predict_km(model, model.X, type=type)
+        q_min = np.min(pr["mean"] + qnorm(beta) * pr["sd"])
+    pr = dk.predict_km(model, x[None, :], type=type)
+    mk, sk = pr["mean"][0], pr["sd"][0]
+    if sk < np.sqrt(model.covariance.sd2) / 1e6:
+        return 0.0
+    mq = mk + qnorm(beta) * np.sqrt((new_noise_var * sk ** 2) / (new_noise_var + sk ** 2))
+    sq = sk ** 2 / np.sqrt(new_noise_var + sk ** 2)
+    xcr = (q_min - mq) / sq
+    return float(sq * (xcr * pnorm(xcr) + dnorm(xcr)))

@@ -98,3 +98,22 @@ def test_akg_grad_other_kernels_and_guard(gpu_lib):
     kd = small_model("matern5_2", "const", n=25, d=2, seed=1)
     assert np.all(AKG_grad(kd.X[:4], kd, new_noise_var=0.1) == 0.0)     # sk.x = 0 at the design: zero gradient
     kd.release()
+
+
+def test_aei_and_eqi_match_oracle(gpu_lib):
+    """The noisy-criteria family of SURVEY 8(f): AEI (R/AEI.R) and EQI (R/EQI.R), default y.min / q.min included."""
+    from diceoptim_b200 import AEI, EQI
+    from oracle import diceoptim as do
+    rng = np.random.default_rng(9)
+    for type in ("UK", "SK"):
+        km = small_model("matern5_2", "const", n=60, d=3, seed=421, noise_var=0.03)
+        ko = to_oracle(km)
+        x = np.vstack([rng.random((50, 3)), km.X[:2]])
+        a = AEI(x, km, new_noise_var=0.03, type=type)
+        e = EQI(x, km, new_noise_var=0.03, beta=0.9, type=type)
+        ra = np.array([do.AEI(xi, ko, new_noise_var=0.03, type=type) for xi in x])
+        re = np.array([do.EQI(xi, ko, new_noise_var=0.03, beta=0.9, type=type) for xi in x])
+        assert np.all(np.abs(a - ra) <= 1e-9 * np.abs(ra) + 1e-12 * ra.max())
+        assert np.all(np.abs(e - re) <= 1e-9 * np.abs(re) + 1e-12 * re.max())
+        assert isinstance(AEI(x[0], km, new_noise_var=0.03, type=type), float)
+        km.release()
