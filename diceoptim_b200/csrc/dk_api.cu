@@ -267,11 +267,12 @@ int dk_model_create(const dk_model_desc* D, dk_model** out) {
   dm.kernel = D->kernel; dm.trend = D->trend; dm.nugget_flag = D->nugget_flag ? 1 : 0;
   dm.sd2 = D->sd2; dm.nugget = D->nugget;
   dm.total_sd2 = D->sd2 + (D->nugget_flag ? D->nugget : 0.0);
-  for (int k = 0; k < DK_MAX_D; k++) { dm.w[k] = 0; dm.shape[k] = 1; dm.theta[k] = 1; }
+  for (int k = 0; k < DK_MAX_D; k++) { dm.w[k] = 0; dm.iw[k] = 0; dm.shape[k] = 1; dm.theta[k] = 1; }
   for (int k = 0; k < d; k++) {
     const double th = D->theta[k];
     dm.theta[k] = th;
     dm.w[k] = D->kernel == DK_MATERN3_2 ? std::sqrt(3.0) / th : D->kernel == DK_MATERN5_2 ? std::sqrt(5.0) / th : 1.0 / th;
+    dm.iw[k] = 1.0 / dm.w[k];
     if (D->shape) dm.shape[k] = D->shape[k];
   }
 
@@ -291,9 +292,15 @@ int dk_model_create(const dk_model_desc* D, dk_model** out) {
     std::vector<double> Xrm((size_t)dm.n_pad * d, 0.0);
     for (int i = 0; i < n; i++)
       for (int k = 0; k < d; k++) Xrm[(size_t)i * d + k] = D->X[(size_t)i + (size_t)k * n];
-    if ((rc = dev_alloc(m, &m->d_Xrm, Xrm.size()))) return bail(rc);
+    if ((rc = dev_alloc(m, &m->d_Xrm, 2 * Xrm.size()))) return bail(rc);
     cudaMemcpy(m->d_Xrm, Xrm.data(), Xrm.size() * 8, cudaMemcpyHostToDevice);
     dm.Xrm = m->d_Xrm;
+    {
+      std::vector<double> Xs(Xrm.size());
+      for (size_t i = 0; i < Xrm.size(); i++) Xs[i] = Xrm[i] * dm.w[i % d];
+      cudaMemcpy(m->d_Xrm + Xrm.size(), Xs.data(), Xs.size() * 8, cudaMemcpyHostToDevice);
+      dm.Xrm_s = m->d_Xrm + Xrm.size();
+    }
 
     // ---- small candidate-independent arrays (SURVEY 8(a1) "derived once per model") ----
     // G = M'M ; RM = chol(G) upper (predict.km: T.M <- chol(t(M)%*%M)) ; tuuinv = solve(G) (R/EI.grad.R:169)
@@ -385,6 +392,9 @@ int dk_model_create(const dk_model_desc* D, dk_model** out) {
 
   // ---- per-CTA V panels: two resident CTAs per SM ----
   m->grid = 2 * m->num_sms;
+  if (const char* e = std::getenv("DK_CTAS_PER_SM")) {  // experiment knob: 1 = one resident CTA per SM
+    if (std::atoi(e) == 1) m->grid = m->num_sms;
+  }
   m->scratch_doubles_per_cta = (size_t)dm.n_pad * BN;
   if ((rc = dev_alloc(m, &m->d_vscratch, (size_t)m->grid * m->scratch_doubles_per_cta))) return bail(rc);
   if (cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess)

@@ -23,7 +23,12 @@ constexpr int BM = 128;
 constexpr int BN = 64;
 constexpr int KC = 16;
 constexpr int NT = 256;          // threads per CTA: 8 warps as 4 (rows) x 2 (cols), warp tile 32 x 32
-constexpr int STAGES = 4;   // 4 x 24 KB = region 0 exactly (the design-row staging is dead during the GEMM phase)
+#ifdef DK_X_STAGES3
+constexpr int STAGES = 3;
+#else
+constexpr int STAGES = 4;
+#endif
+// ^   // 4 x 24 KB = region 0 exactly (the design-row staging is dead during the GEMM phase)
 constexpr int A_TILE = BM * KC;  // doubles
 constexpr int B_TILE = KC * BN;  // doubles
 constexpr int CB_STRIDE = 72;    // row stride (doubles) of the covariance staging tile
@@ -62,6 +67,7 @@ struct DevModel {
   const double* tiles_fwd;  // forward tiles: -L_aug off-diagonal, block inverses on the diagonal
   const double* tiles_bwd;  // backward (flipped T) tiles, same format; NULL until a gradient call
   const double* Xrm;        // [n_pad][d] row-major design (pad rows zero)
+  const double* Xrm_s;      // the same rows scaled by w_k (cov-gen operand)
   const double* beta;       // p
   const double* RM;         // chol(M'M) upper, p x p column-major
   const double* tuuinv;     // (M'M)^-1, p x p
@@ -75,6 +81,7 @@ struct DevModel {
   const int* akg_perm;         // n: design row with the j-th smallest a
   double akg_min_mkX;          // min_i mk.X_i
   double w[DK_MAX_D];       // per-dimension scale of |h|: 1/theta (gauss, exp, powexp), sqrt3/theta, sqrt5/theta
+  double iw[DK_MAX_D];      // 1 / w_k
   double shape[DK_MAX_D];   // powexp exponents
   double theta[DK_MAX_D];
 };

@@ -82,33 +82,38 @@ __device__ __forceinline__ void load_tile_async(double* dst, const double* __res
 // 1-D kernels as DiceKriging codes them; matern kernels in product form
 // prod(1 + a + a^2/3) * exp(-sum a), algebraically the reference's exp(-sum(a - log(1+a+a^2/3))).
 // ---------------------------------------------------------------------------------------
-template <int KERNEL>
+// Xs holds the design rows PRE-SCALED by w_k (DevModel::Xrm_s); the candidate coordinate is scaled once per k, so a
+// pair costs one DADD per dimension for a = |X_ik w_k - x_jk w_k|.  Eight rows x two columns = 16 independent
+// chains per thread keep the FP64 pipe fed (the phase is latency-bound with fewer).
+template <int KERNEL, bool NUG>
 __device__ __forceinline__ void covgen_rows(const DevModel& M, const double* __restrict__ Xs,
                                             const double* __restrict__ xs, double* __restrict__ Cbuf,
                                             int row0_global, int warp, int lane) {
+  constexpr int RB = 8;
   const int d = M.d;
 #pragma unroll 1
-  for (int rr = 0; rr < 16; rr += 4) {
-    double s[4][2], pr[4][2], hs[4][2];
+  for (int rr = 0; rr < 16; rr += RB) {
+    double s[RB][2], pr[RB][2], hs[NUG ? RB : 1][2];
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
+    for (int j = 0; j < RB; j++) {
       s[j][0] = s[j][1] = 0.0;
       pr[j][0] = pr[j][1] = 1.0;
-      hs[j][0] = hs[j][1] = 0.0;
+      if (NUG) hs[j][0] = hs[j][1] = 0.0;
     }
     const double* Xr = Xs + (16 * warp + rr) * d;
 #pragma unroll 1
     for (int k = 0; k < d; k++) {
-      const double c0 = xs[k * BN + lane], c1 = xs[k * BN + lane + 32];
       const double wk = M.w[k];
+      // __dmul_rn / __dsub_rn: never contracted into an FMA, so a pair's value cannot depend on its tile position
+      const double c0 = __dmul_rn(xs[k * BN + lane], wk), c1 = __dmul_rn(xs[k * BN + lane + 32], wk);
+      const double iwk = NUG ? M.iw[k] : 0.0;
 #pragma unroll
-      for (int j = 0; j < 4; j++) {
+      for (int j = 0; j < RB; j++) {
         const double xr = Xr[j * d + k];
 #pragma unroll
         for (int e = 0; e < 2; e++) {
-          const double h = fabs(xr - (e ? c1 : c0));
-          const double a = h * wk;
-          if (M.nugget_flag) hs[j][e] += h;
+          const double a = fabs(__dsub_rn(xr, e ? c1 : c0));
+          if (NUG) hs[j][e] = fma(a, iwk, hs[j][e]);
           if (KERNEL == DK_GAUSS) {
             s[j][e] = fma(0.5 * a, a, s[j][e]);
           } else if (KERNEL == DK_EXP) {
@@ -126,28 +131,34 @@ __device__ __forceinline__ void covgen_rows(const DevModel& M, const double* __r
       }
     }
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
+    for (int j = 0; j < RB; j++) {
       const int r = 16 * warp + rr + j;
       const bool live = (row0_global + r) < M.n;
 #pragma unroll
       for (int e = 0; e < 2; e++) {
         double c = M.sd2 * pr[j][e] * exp(-s[j][e]);
-        if (M.nugget_flag && hs[j][e] < 1e-15) c += M.nugget;  // covMat1Mat2(nugget.flag=TRUE) white-noise term
+        if (NUG && hs[j][e] < 1e-15) c += M.nugget;  // covMat1Mat2(nugget.flag=TRUE) white-noise term
         Cbuf[r * CB_STRIDE + lane + 32 * e] = live ? c : 0.0;
       }
     }
   }
 }
 
+template <bool NUG>
+__device__ __forceinline__ void covgen_block_n(const DevModel& M, const double* Xs, const double* xs, double* Cbuf,
+                                               int row0_global, int warp, int lane) {
+  switch (M.kernel) {
+    case DK_GAUSS: covgen_rows<DK_GAUSS, NUG>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
+    case DK_EXP: covgen_rows<DK_EXP, NUG>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
+    case DK_MATERN3_2: covgen_rows<DK_MATERN3_2, NUG>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
+    case DK_MATERN5_2: covgen_rows<DK_MATERN5_2, NUG>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
+    default: covgen_rows<DK_POWEXP, NUG>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
+  }
+}
 __device__ __forceinline__ void covgen_block(const DevModel& M, const double* Xs, const double* xs, double* Cbuf,
                                              int row0_global, int warp, int lane) {
-  switch (M.kernel) {
-    case DK_GAUSS: covgen_rows<DK_GAUSS>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
-    case DK_EXP: covgen_rows<DK_EXP>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
-    case DK_MATERN3_2: covgen_rows<DK_MATERN3_2>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
-    case DK_MATERN5_2: covgen_rows<DK_MATERN5_2>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
-    default: covgen_rows<DK_POWEXP>(M, Xs, xs, Cbuf, row0_global, warp, lane); break;
-  }
+  if (M.nugget_flag) covgen_block_n<true>(M, Xs, xs, Cbuf, row0_global, warp, lane);
+  else covgen_block_n<false>(M, Xs, xs, Cbuf, row0_global, warp, lane);
 }
 
 // ---- mbarrier + bulk-copy (TMA 1-D) helpers for the warp-synchronous variant of the GEMM phase ----
@@ -220,13 +231,22 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
     unsigned long long* empty = full + STAGES;
     const unsigned base = *stage_base;
     constexpr unsigned STAGE_BYTES = (A_TILE + B_TILE) * 8;
+    // Region 0 was last written through the generic proxy (covariance tile, design rows, diagonal-phase buffers) and
+    // the panel by generic global stores; every thread orders its own accesses against the async proxy, then the
+    // CTA meets, and only then does thread 0 start issuing bulk copies into / from those locations.
+    asm volatile("fence.proxy.async;" ::: "memory");
+    __syncthreads();
     auto issue = [&](int idx) {  // thread 0 only
       const unsigned gi = base + idx, slot = gi % STAGES, par = (gi / STAGES) & 1;
       mbar_wait(&empty[slot], par ^ 1);  // every warp has released the slot's previous contents
       double* dst = ring + slot * (A_TILE + B_TILE);
       mbar_arrive_expect_tx(&full[slot], STAGE_BYTES);
       bulk_load(dst, Atiles + (size_t)idx * A_TILE, A_TILE * 8, &full[slot]);
+#ifdef DK_X_BSTATIC
+      bulk_load(dst + A_TILE, Atiles + (size_t)idx * A_TILE, B_TILE * 8, &full[slot]);  // experiment: static B source
+#else
       bulk_load(dst + A_TILE, panel + (size_t)idx * B_TILE, B_TILE * 8, &full[slot]);
+#endif
     };
     if (tid == 0)
       for (int s = 0; s < STAGES - 1 && s < nk; s++) issue(s);
@@ -237,8 +257,15 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
       mbar_wait(&full[slot], par);
       const double* s = ring + slot * (A_TILE + B_TILE);
       mma_stage(acc, s, s + A_TILE, wm, wn, lane);
+#ifndef DK_X_NOCONSFENCE
+      // this slot is refilled through the async proxy: order this lane's generic-proxy reads of it before that
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[slot]);
+#ifdef DK_X_SYNCSTAGE
+      __syncthreads();
+#endif
     }
     *stage_base = base + nk;
     __syncthreads();  // every warp is done with the ring: region 0 can change role
@@ -293,11 +320,16 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
         acc[mi][ni][e] = 0.0;
       }
   }
+#ifdef DK_X_NODIAG
+  const int ndiag = 1;
+#else
+  const int ndiag = CHUNKS_PER_BLOCK;
+#endif
 #pragma unroll 1
-  for (int j = 0; j < CHUNKS_PER_BLOCK; j++) {
+  for (int j = 0; j < ndiag; j++) {
     cp_async_wait<0>();
     __syncthreads();
-    if (j + 1 < CHUNKS_PER_BLOCK) {
+    if (j + 1 < ndiag) {
       load_tile_async(Abuf + ((j + 1) & 1) * A_TILE, Dtiles + (size_t)(j + 1) * A_TILE, A_TILE, tid);
       cp_async_commit();
     }
@@ -316,11 +348,16 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
 #pragma unroll
       for (int e = 0; e < 2; e++) {
         const int nn = 32 * wn + 8 * ni + 2 * (lane & 3) + e;
-        panel[(size_t)chunk * B_TILE + b_tile_index(k, nn)] = acc[mi][ni][e];
+        __stcg(panel + (size_t)chunk * B_TILE + b_tile_index(k, nn), acc[mi][ni][e]);  // straight to L2
       }
   }
-  // the panel is next read through the async proxy (bulk copies): order these generic-proxy stores before it
-  if constexpr (TMA) asm volatile("fence.proxy.async.global;" ::: "memory");
+  // The panel is next read by bulk copies, i.e. through the async proxy and straight from L2.  The block-level
+  // barrier that follows only makes these generic-proxy stores visible at CTA scope (L1), so they are first
+  // pushed to GPU scope (__threadfence) and then ordered against the async proxy.
+  if constexpr (TMA) {
+    __threadfence();
+    asm volatile("fence.proxy.async.global;" ::: "memory");
+  }
   DK_MARK(4);
 }
 
@@ -436,11 +473,13 @@ __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __
     DK_MARK(6);
     // ---- P1: design rows of this block -> smem, then covariance block -> Cbuf ----
     {
-      const double* src = M.Xrm + (size_t)I * BM * d;
+      const double* src = M.Xrm_s + (size_t)I * BM * d;  // design rows pre-scaled by w_k
       for (int i = tid; i < BM * d; i += NT) Xs[i] = __ldg(src + i);
     }
     __syncthreads();
+#ifndef DK_X_NOCOV
     covgen_block(M, Xs, xs, Cbuf, I * BM, warp, lane);
+#endif
     __syncthreads();
     // ---- P2: Cbuf -> accumulator fragments ----
     double acc[4][4][2];
@@ -508,6 +547,12 @@ k_predict_fused_tma(const DevModel M, const CritParams P, const double* __restri
   double* panel = vscratch + (size_t)blockIdx.x * panel_doubles;
   pipeline_init(smem, tid);
   unsigned stage_base = 0;
+#ifdef DK_EXPERIMENT_STAGGER
+  if (blockIdx.x >= gridDim.x / 2) {  // experiment: desynchronise the two CTAs of an SM
+    const long long t0 = clock64();
+    while (clock64() - t0 < DK_EXPERIMENT_STAGGER) { }
+  }
+#endif
 #pragma unroll 1
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t c0 = tile * BN;

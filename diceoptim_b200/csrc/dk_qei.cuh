@@ -101,7 +101,7 @@ __device__ __forceinline__ void qei_tile_moments(const DevModel& M, int type, in
 #pragma unroll 1
   for (int I = 0; I < M.nblk; I++) {
     {
-      const double* src = M.Xrm + (size_t)I * BM * d;
+      const double* src = M.Xrm_s + (size_t)I * BM * d;  // design rows pre-scaled by w_k
       for (int i = tid; i < BM * d; i += NT) Xs[i] = __ldg(src + i);
     }
     __syncthreads();
