@@ -162,7 +162,11 @@ bool g_attr_done[64] = {};
 int set_kernel_attrs(int device) {
   if (device < 64 && g_attr_done[device]) return DK_OK;
   DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
-  DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_fused_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
+#define DK_ATTR_TMA(K)                                                                                                  \
+  DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_fused_tma<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM)); \
+  DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_fused_tma<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
+  DK_ATTR_TMA(DK_GAUSS) DK_ATTR_TMA(DK_EXP) DK_ATTR_TMA(DK_MATERN3_2) DK_ATTR_TMA(DK_MATERN5_2) DK_ATTR_TMA(DK_POWEXP)
+#undef DK_ATTR_TMA
   DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
   if (device < 64) g_attr_done[device] = true;
   return DK_OK;
@@ -184,10 +188,23 @@ int launch_predict(dk_model* m, const CritParams& P, const double* d_x, int64_t 
   if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
   // default: bulk-copy + mbarrier pipeline (+8.6 % at cfg4); DK_PIPELINE=cpasync selects the cp.async / __syncthreads ring
   static const bool use_tma = [] { const char* e = std::getenv("DK_PIPELINE"); return !(e && std::strcmp(e, "cpasync") == 0); }();
-  if (use_tma)
-    k_predict_fused_tma<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch,
-                                                          m->scratch_doubles_per_cta, d_main, d_mean, d_sd);
-  else
+  if (use_tma) {
+    // one instantiation per covariance kernel and nugget path: each carries only the code it runs
+#define DK_LAUNCH_TMA(K)                                                                                               \
+  case K:                                                                                                              \
+    if (m->dm.nugget_flag)                                                                                             \
+      k_predict_fused_tma<K, true><<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch,     \
+                                                                         m->scratch_doubles_per_cta, d_main, d_mean, d_sd); \
+    else                                                                                                               \
+      k_predict_fused_tma<K, false><<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch,    \
+                                                                          m->scratch_doubles_per_cta, d_main, d_mean, d_sd); \
+    break;
+    switch (m->dm.kernel) {
+      DK_LAUNCH_TMA(DK_GAUSS) DK_LAUNCH_TMA(DK_EXP) DK_LAUNCH_TMA(DK_MATERN3_2) DK_LAUNCH_TMA(DK_MATERN5_2)
+      default: DK_LAUNCH_TMA(DK_POWEXP)
+    }
+#undef DK_LAUNCH_TMA
+  } else
     k_predict_fused<<<grid, NT, SM_TOTAL, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->scratch_doubles_per_cta,
                                                  d_main, d_mean, d_sd);
   if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }

@@ -449,7 +449,9 @@ __device__ __noinline__ void crit_epilogue(const DevModel& M, const CritParams& 
 // ---------------------------------------------------------------------------------------
 // cpanel (optional): the covariance columns c(x_j) themselves are kept, row-major [i][64], for the gradient
 // kernels (covVector.dx needs c again: dc = c .* dlogk).
-template <bool TMA = false>
+// KSEL >= 0 fixes the covariance kernel (and NUGSEL the nugget path) at compile time, so the instantiation carries
+// only the code it runs (the generic version inlines all five kernels: 240 KB of SASS).
+template <bool TMA = false, int KSEL = -1, bool NUGSEL = false>
 __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __restrict__ x, int64_t N, int64_t c0,
                                              double* __restrict__ panel, unsigned char* smem, int tid,
                                              unsigned* stage_base = nullptr, double* __restrict__ cpanel = nullptr) {
@@ -478,7 +480,8 @@ __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __
     }
     __syncthreads();
 #ifndef DK_X_NOCOV
-    covgen_block(M, Xs, xs, Cbuf, I * BM, warp, lane);
+    if constexpr (KSEL >= 0) covgen_rows<KSEL, NUGSEL>(M, Xs, xs, Cbuf, I * BM, warp, lane);
+    else covgen_block(M, Xs, xs, Cbuf, I * BM, warp, lane);
 #endif
     __syncthreads();
     // ---- P2: Cbuf -> accumulator fragments ----
@@ -536,6 +539,7 @@ __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __
 // The fused forward kernel: persistent CTAs, two per SM, each looping over candidate tiles.
 // ---------------------------------------------------------------------------------------
 // Same kernel with the GEMM phase fed by bulk asynchronous copies + mbarriers (SM_TOTAL + 64 B of shared memory).
+template <int KSEL, bool NUGSEL>
 __global__ void __launch_bounds__(NT, 2)
 k_predict_fused_tma(const DevModel M, const CritParams P, const double* __restrict__ x, int64_t N, int64_t ntiles,
                     double* __restrict__ vscratch, size_t panel_doubles, double* __restrict__ out_main,
@@ -556,7 +560,7 @@ k_predict_fused_tma(const DevModel M, const CritParams P, const double* __restri
 #pragma unroll 1
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t c0 = tile * BN;
-    forward_tile<true>(M, x, N, c0, panel, smem, tid, &stage_base);
+    forward_tile<true, KSEL, NUGSEL>(M, x, N, c0, panel, smem, tid, &stage_base);
     if (tid < BN && c0 + tid < N)
       crit_epilogue(M, P, panel, xs, s2acc, tid, c0 + tid, out_main, out_mean, out_sd);
     __syncthreads();
