@@ -58,6 +58,10 @@ SIGNATURES = {
     "dk_aei_dev": (_I, [_V, _V, _L, _D, _D, _I, _V, _V]),
     "dk_eqi": (_I, [_V, _V, _L, _D, _D, _D, _I, _V]),
     "dk_eqi_dev": (_I, [_V, _V, _L, _D, _D, _D, _I, _V, _V]),
+    "dk_aei_grad": (_I, [_V, _V, _L, _D, _D, _I, _V]),
+    "dk_aei_grad_dev": (_I, [_V, _V, _L, _D, _D, _I, _V, _V, _V]),
+    "dk_eqi_grad": (_I, [_V, _V, _L, _D, _D, _D, _I, _V]),
+    "dk_eqi_grad_dev": (_I, [_V, _V, _L, _D, _D, _D, _I, _V, _V, _V]),
     "dk_akg": (_I, [_V, _V, _L, _D, _I, _V]),
     "dk_akg_dev": (_I, [_V, _V, _L, _D, _I, _V, _V]),
     "dk_akg_grad": (_I, [_V, _V, _L, _D, _I, _V, _V]),

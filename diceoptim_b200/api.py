@@ -343,3 +343,35 @@ def EQI(x, model: KM, new_noise_var=0.0, beta=0.9, q_min=None, type="UK", envir=
     _lib.check(_lib.load().dk_eqi(h.ptr, _vp(x), x.shape[0], float(q_min), float(new_noise_var), float(ndtri(beta)),
                                   _type_id(type), _vp(out)), "dk_eqi")
     return float(out[0]) if single else out
+
+
+def _default_y_min(model, type, device):
+    pr = predict(model, model.X, type=type, device=device)          # R/AEI.R:116-122
+    return float(pr["mean"][int(np.argmin(pr["mean"] + ndtri(0.75) * pr["sd"]))])
+
+
+def AEI_grad(x, model: KM, new_noise_var=0.0, y_min=None, type="UK", envir=None, device=0):
+    """Gradient of AEI, R/AEI.grad.R:65-154 (rows batched)."""
+    single = np.asarray(x).ndim <= 1
+    if y_min is None:
+        y_min = _default_y_min(model, type, device)
+    x = _as_candidates(x, model.d)
+    g = np.empty((x.shape[0], model.d), order="F")
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_aei_grad(h.ptr, _vp(x), x.shape[0], float(y_min), float(new_noise_var), _type_id(type), _vp(g)),
+               "dk_aei_grad")
+    return g[0].copy() if single else g
+
+
+def EQI_grad(x, model: KM, new_noise_var=0.0, beta=0.9, q_min=None, type="UK", envir=None, device=0):
+    """Gradient of EQI, R/EQI.grad.R:66-146 (rows batched)."""
+    single = np.asarray(x).ndim <= 1
+    if q_min is None:
+        pr = predict(model, model.X, type=type, device=device)
+        q_min = float(np.min(pr["mean"] + ndtri(beta) * pr["sd"]))
+    x = _as_candidates(x, model.d)
+    g = np.empty((x.shape[0], model.d), order="F")
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_eqi_grad(h.ptr, _vp(x), x.shape[0], float(q_min), float(new_noise_var), float(ndtri(beta)),
+                                       _type_id(type), _vp(g)), "dk_eqi_grad")
+    return g[0].copy() if single else g

@@ -167,7 +167,8 @@ int set_kernel_attrs(int device) {
   DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_fused_tma<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
   DK_ATTR_TMA(DK_GAUSS) DK_ATTR_TMA(DK_EXP) DK_ATTR_TMA(DK_MATERN3_2) DK_ATTR_TMA(DK_MATERN5_2) DK_ATTR_TMA(DK_POWEXP)
 #undef DK_ATTR_TMA
-  DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
+  DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_fused<-1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
+  DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_fused<DK_MATERN5_2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
   if (device < 64) g_attr_done[device] = true;
   return DK_OK;
 }
@@ -221,8 +222,12 @@ int launch_grad(dk_model* m, const CritParams& P, const double* d_x, int64_t N, 
   const int64_t ntiles = (N + BN - 1) / BN;
   const int grid = (int)std::min<int64_t>(ntiles, m->grid);
   if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
-  k_grad_fused<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->d_wscratch,
-                                            m->d_cscratch, m->scratch_doubles_per_cta, d_grad, d_main);
+  if (m->dm.kernel == DK_MATERN5_2 && !m->dm.nugget_flag)
+    k_grad_fused<DK_MATERN5_2><<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->d_wscratch,
+                                                                     m->d_cscratch, m->scratch_doubles_per_cta, d_grad, d_main);
+  else
+    k_grad_fused<-1><<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->d_wscratch,
+                                                           m->d_cscratch, m->scratch_doubles_per_cta, d_grad, d_main);
   if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
   m->launches++;
   DK_CUDA_TRY(cudaGetLastError());
@@ -1090,5 +1095,51 @@ extern "C" int dk_eqi(dk_model* m, const double* x, int64_t N, double q_min, dou
   if ((rc = h.init(m, x, N, (size_t)N))) return rc;
   if ((rc = dk_eqi_dev(m, h.d_x, N, q_min, new_noise_var, qnorm_beta, type, h.d_out, m->stream))) return rc;
   if ((rc = h.fetch(out, h.d_out, N))) return rc;
+  return h.finish();
+}
+
+// AEI.grad (R/AEI.grad.R:65-154) and EQI.grad (R/EQI.grad.R:66-146): the gradient kernel with other outer derivatives
+extern "C" int dk_aei_grad_dev(dk_model* m, const double* d_x, int64_t N, double y_min, double new_noise_var, int type,
+                               double* d_grad, double* d_aei, void* stream) {
+  int rc = check_call(m, d_x, N);
+  if (rc) return rc;
+  if (!d_grad) return fail(DK_ERR_ARG, "d_grad is NULL");
+  if (!(new_noise_var >= 0)) return fail(DK_ERR_ARG, "new.noise.var must be >= 0");
+  DeviceGuard guard(m->device);
+  CritParams P{MODE_AEI, type, 1, 0, y_min, 0.0, new_noise_var, m->dm.sd2};
+  return launch_grad(m, P, d_x, N, d_grad, d_aei, (cudaStream_t)stream);
+}
+extern "C" int dk_eqi_grad_dev(dk_model* m, const double* d_x, int64_t N, double q_min, double new_noise_var,
+                               double qnorm_beta, int type, double* d_grad, double* d_eqi, void* stream) {
+  int rc = check_call(m, d_x, N);
+  if (rc) return rc;
+  if (!d_grad) return fail(DK_ERR_ARG, "d_grad is NULL");
+  if (!(new_noise_var >= 0)) return fail(DK_ERR_ARG, "new.noise.var must be >= 0");
+  DeviceGuard guard(m->device);
+  CritParams P{MODE_EQI, type, 1, 0, q_min, qnorm_beta, new_noise_var, m->dm.sd2};
+  return launch_grad(m, P, d_x, N, d_grad, d_eqi, (cudaStream_t)stream);
+}
+extern "C" int dk_aei_grad(dk_model* m, const double* x, int64_t N, double y_min, double new_noise_var, int type,
+                           double* out_grad) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (!out_grad) return fail(DK_ERR_ARG, "out_grad is NULL");
+  DeviceGuard guard(m->device);
+  HostCall h;
+  if ((rc = h.init(m, x, N, (size_t)N * (m->d + 1)))) return rc;
+  if ((rc = dk_aei_grad_dev(m, h.d_x, N, y_min, new_noise_var, type, h.d_out, h.d_out + (size_t)N * m->d, m->stream))) return rc;
+  if ((rc = h.fetch(out_grad, h.d_out, (size_t)N * m->d))) return rc;
+  return h.finish();
+}
+extern "C" int dk_eqi_grad(dk_model* m, const double* x, int64_t N, double q_min, double new_noise_var, double qnorm_beta,
+                           int type, double* out_grad) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (!out_grad) return fail(DK_ERR_ARG, "out_grad is NULL");
+  DeviceGuard guard(m->device);
+  HostCall h;
+  if ((rc = h.init(m, x, N, (size_t)N * (m->d + 1)))) return rc;
+  if ((rc = dk_eqi_grad_dev(m, h.d_x, N, q_min, new_noise_var, qnorm_beta, type, h.d_out, h.d_out + (size_t)N * m->d, m->stream))) return rc;
+  if ((rc = h.fetch(out_grad, h.d_out, (size_t)N * m->d))) return rc;
   return h.finish();
 }

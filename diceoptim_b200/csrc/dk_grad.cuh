@@ -83,6 +83,9 @@ __device__ __forceinline__ void grad_accumulate_vec(const DevModel& M, const dou
   }
 }
 
+// KSEL = -1: any covariance kernel (runtime switch); KSEL = DK_MATERN5_2: the km default, without nugget, as its own
+// instantiation so that it carries only the code it runs.
+template <int KSEL>
 __global__ void __launch_bounds__(NT, 2)
 k_grad_fused(const DevModel M, const CritParams P, const double* __restrict__ x, int64_t N, int64_t ntiles,
              double* __restrict__ vscratch, double* __restrict__ wscratch, double* __restrict__ cscratch,
@@ -102,7 +105,7 @@ k_grad_fused(const DevModel M, const CritParams P, const double* __restrict__ x,
 #pragma unroll 1
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t c0 = tile * BN;
-    forward_tile<true>(M, x, N, c0, vpanel, smem, tid, &stage_base, cpanel);
+    forward_tile<true, KSEL, false>(M, x, N, c0, vpanel, smem, tid, &stage_base, cpanel);
 
     // ---- epilogue 1: value + outer-derivative coefficients per candidate ----
     if (tid < BN) {
@@ -116,6 +119,27 @@ k_grad_fused(const DevModel M, const CritParams P, const double* __restrict__ x,
         cA = 1.0;
         if (sd < sqrt(M.sd2) / 1e6) { cW = 0.0; drop_r = true; }
         else cW = -P.qnorm_beta / sd;
+      } else if (P.mode == MODE_AEI) {  // R/AEI.grad.R:117-147: ei.grad * pen + ei.val * pen.grad
+        if (sd < sqrt(P.sd2) / 1e6) { cA = 0.0; cW = 0.0; drop_r = true; }
+        else {
+          const double diff = P.plugin - mean, xcr = diff / sd, Phi = normcdf(xcr), phi = dnorm_std(xcr);
+          const double v2 = P.tau2 + sd * sd, pen = 1.0 - sqrt(P.tau2) / sqrt(v2);
+          const double eival = diff * Phi + sd * phi;
+          const double kappa = phi * pen / (2.0 * sd) + eival * sqrt(P.tau2) / (2.0 * v2 * sqrt(v2));  // on sk2.grad
+          cA = -Phi * pen;
+          cW = -2.0 * kappa;
+        }
+      } else if (P.mode == MODE_EQI) {  // R/EQI.grad.R:112-141: -Phi mq.grad + phi sq.grad
+        if (sd < sqrt(P.sd2) / 1e6) { cA = 0.0; cW = 0.0; drop_r = true; }
+        else {
+          const double t2 = P.tau2, v2 = t2 + sd * sd;
+          const double mq = mean + P.qnorm_beta * sqrt(t2 * sd * sd / v2), sq = sd * sd / sqrt(v2);
+          const double xcr = (P.plugin - mq) / sq, Phi = normcdf(xcr), phi = dnorm_std(xcr);
+          const double g1 = P.qnorm_beta * t2 * sqrt(t2) / (2.0 * sd * v2 * sqrt(v2));
+          const double kappa = -Phi * g1 + phi * (sd * sd * (2.0 * t2 + sd * sd) / (v2 * v2)) / (2.0 * sq);
+          cA = -Phi;
+          cW = -2.0 * kappa;
+        }
       } else {  // EI
         const double sgn = P.minimization ? 1.0 : -1.0;
         if (sd / sqrt(M.sd2) < 1e-6) { cA = 0.0; cW = 0.0; drop_r = true; }
@@ -170,7 +194,8 @@ k_grad_fused(const DevModel M, const CritParams P, const double* __restrict__ x,
       double g[DK_MAX_D];
 #pragma unroll
       for (int k = 0; k < DK_MAX_D; k++) g[k] = 0.0;
-      switch (M.kernel) {
+      if constexpr (KSEL >= 0) grad_accumulate<KSEL>(M, xs, cpanel, wpanel, c, slice, cA, cW, g);
+      else switch (M.kernel) {
         case DK_GAUSS: grad_accumulate<DK_GAUSS>(M, xs, cpanel, wpanel, c, slice, cA, cW, g); break;
         case DK_EXP: grad_accumulate<DK_EXP>(M, xs, cpanel, wpanel, c, slice, cA, cW, g); break;
         case DK_MATERN3_2: grad_accumulate<DK_MATERN3_2>(M, xs, cpanel, wpanel, c, slice, cA, cW, g); break;

@@ -139,6 +139,16 @@ int dk_eqi(dk_model* m, const double* x, int64_t N, double q_min, double new_noi
 int dk_eqi_dev(dk_model* m, const double* d_x, int64_t N, double q_min, double new_noise_var, double qnorm_beta, int type,
                double* d_out, void* stream);
 
+/* AEI.grad / EQI.grad for every row of x — replace /root/reference/R/AEI.grad.R:65-154 and R/EQI.grad.R:66-146
+ * (N x d outputs; same y_min / q_min conventions as dk_aei / dk_eqi). */
+int dk_aei_grad(dk_model* m, const double* x, int64_t N, double y_min, double new_noise_var, int type, double* out_grad);
+int dk_aei_grad_dev(dk_model* m, const double* d_x, int64_t N, double y_min, double new_noise_var, int type, double* d_grad,
+                    double* d_aei, void* stream);
+int dk_eqi_grad(dk_model* m, const double* x, int64_t N, double q_min, double new_noise_var, double qnorm_beta, int type,
+                double* out_grad);
+int dk_eqi_grad_dev(dk_model* m, const double* d_x, int64_t N, double q_min, double new_noise_var, double qnorm_beta, int type,
+                    double* d_grad, double* d_eqi, void* stream);
+
 /* AKG(x, model, new.noise.var, type) for every row of x (the reference evaluates one row per call and
  * re-predicts at the whole design each time) — replaces /root/reference/R/AKG.R:93-229.  Needs n + 1 <= 8192. */
 int dk_akg(dk_model* m, const double* x, int64_t N, double new_noise_var, int type, double* out);

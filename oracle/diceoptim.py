@@ -620,3 +620,44 @@ def EQI(x, model, new_noise_var=0.0, beta=0.9, q_min=None, type="UK", envir=None
     sq = sk ** 2 / np.sqrt(new_noise_var + sk ** 2)
     xcr = (q_min - mq) / sq
     return float(sq * (xcr * pnorm(xcr) + dnorm(xcr)))
+
+
+def AEI_grad(x, model, new_noise_var=0.0, y_min=None, type="UK", envir=None):
+    """R/AEI.grad.R:65-154 at one point."""
+    x = np.asarray(x, float).ravel()
+    if y_min is None:
+        pr = dk.predict_km(model, model.X, type=type)
+        y_min = pr["mean"][int(np.argmin(pr["mean"] + qnorm(0.75) * pr["sd"]))]
+    pr = dk.predict_km(model, x[None, :], type=type)
+    mk, sk = pr["mean"][0], pr["sd"][0]
+    if sk < np.sqrt(model.covariance.sd2) / 1e6:
+        return np.zeros(model.d)
+    xcr = (y_min - mk) / sk; prob = pnorm(xcr); dens = dnorm(xcr)
+    ei_val = (y_min - mk) * prob + sk * dens
+    pen = 1.0 - np.sqrt(new_noise_var) / np.sqrt(new_noise_var + sk ** 2)
+    mk_grad, sk2_grad = _mean_sd2_grad(x, model, type, pr["Tinv.c"][:, 0], pr["c"][:, 0], sd_guard_zero=False)
+    sk_grad = sk2_grad / (2.0 * sk)
+    ei_grad = -mk_grad * prob + sk_grad * dens
+    pen_grad = np.sqrt(new_noise_var) / 2.0 * sk2_grad * (new_noise_var + sk ** 2) ** (-1.5)
+    return ei_grad * pen + ei_val * pen_grad
+
+
+def EQI_grad(x, model, new_noise_var=0.0, beta=0.9, q_min=None, type="UK", envir=None):
+    """R/EQI.grad.R:66-146 at one point."""
+    x = np.asarray(x, float).ravel()
+    if q_min is None:
+        pr = dk.predict_km(model, model.X, type=type)
+        q_min = np.min(pr["mean"] + qnorm(beta) * pr["sd"])
+    pr = dk.predict_km(model, x[None, :], type=type)
+    mk, sk = pr["mean"][0], pr["sd"][0]
+    if sk < np.sqrt(model.covariance.sd2) / 1e6:
+        return np.zeros(model.d)
+    t2 = new_noise_var
+    mq = mk + qnorm(beta) * np.sqrt(t2 * sk ** 2 / (t2 + sk ** 2))
+    sq = sk ** 2 / np.sqrt(t2 + sk ** 2)
+    xcr = (q_min - mq) / sq; prob = pnorm(xcr); dens = dnorm(xcr)
+    mk_grad, sk2_grad = _mean_sd2_grad(x, model, type, pr["Tinv.c"][:, 0], pr["c"][:, 0], sd_guard_zero=False)
+    mq_grad = mk_grad + qnorm(beta) * t2 ** 1.5 / (2.0 * sk * (sk ** 2 + t2) ** 1.5) * sk2_grad
+    sq2_grad = (sk ** 2) * (2 * t2 + sk ** 2) / (t2 + sk ** 2) ** 2 * sk2_grad
+    sq_grad = sq2_grad / (2.0 * sq)
+    return -prob * mq_grad + dens * sq_grad

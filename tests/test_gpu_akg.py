@@ -117,3 +117,21 @@ def test_aei_and_eqi_match_oracle(gpu_lib):
         assert np.all(np.abs(e - re) <= 1e-9 * np.abs(re) + 1e-12 * re.max())
         assert isinstance(AEI(x[0], km, new_noise_var=0.03, type=type), float)
         km.release()
+
+
+@pytest.mark.parametrize("trend,type", [("const", "UK"), ("const", "SK"), ("linear", "UK")])
+def test_aei_grad_and_eqi_grad_match_oracle(gpu_lib, trend, type):
+    from diceoptim_b200 import AEI_grad, EQI_grad
+    from oracle import diceoptim as do
+    rng = np.random.default_rng(12)
+    km = small_model("matern5_2", trend, n=70, d=3, seed=421, noise_var=0.03)
+    ko = to_oracle(km)
+    x = np.vstack([rng.random((30, 3)), km.X[:1]])
+    ga = AEI_grad(x, km, new_noise_var=0.03, type=type)
+    ge = EQI_grad(x, km, new_noise_var=0.03, beta=0.9, type=type)
+    for j in range(x.shape[0]):
+        ra = do.AEI_grad(x[j], ko, new_noise_var=0.03, type=type)
+        re = do.EQI_grad(x[j], ko, new_noise_var=0.03, beta=0.9, type=type)
+        assert np.max(np.abs(ga[j] - ra)) <= 1e-8 * np.max(np.abs(ra)) + 1e-14
+        assert np.max(np.abs(ge[j] - re)) <= 1e-8 * np.max(np.abs(re)) + 1e-14
+    km.release()
