@@ -776,8 +776,11 @@ extern "C" int dk_qei_dev(dk_model* m, const double* d_x, int64_t B, int q, doub
   k_qei_moments<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, type, q, d_x, B, ntiles, m->d_vscratch, m->scratch_doubles_per_cta,
                                              m->d_aux, m->d_mom);
   DK_CUDA_TRY(cudaGetLastError());
-  const int64_t threads = B * 4;
-  k_qei_cdf<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(m->d_mom, B, q, plugin, minimization, d_out);
+  static const int64_t warp_below = [] { const char* e = std::getenv("DK_QEI_WARP_BELOW"); return e ? std::atoll(e) : (int64_t)12288; }();  // measured crossover (cfg3): 2048 batches 0.64 vs 2.06 ms, 18944: 5.4 vs 5.0 ms
+  if (B < warp_below)  // few batches: a warp per batch (path-integral nodes spread over lanes) hides latency better
+    k_qei_cdf_warp<<<(unsigned)((B + 3) / 4), 128, 0, st>>>(m->d_mom, B, q, plugin, minimization, d_out);
+  else
+    k_qei_cdf<<<(unsigned)((B * 4 + 127) / 128), 128, 0, st>>>(m->d_mom, B, q, plugin, minimization, d_out);
   if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
   m->launches += 2;
   DK_CUDA_TRY(cudaGetLastError());

@@ -263,6 +263,7 @@ __device__ __forceinline__ void covzk_dev(int q, const double* S, int k, double*
     }
 }
 
+// Four lanes per batch (one per k): the throughput version, used when there are enough batches to fill the GPU.
 __global__ void __launch_bounds__(128)
 k_qei_cdf(const double* __restrict__ moments, int64_t B, int q, double plugin, int minimization,
           double* __restrict__ out) {
@@ -337,6 +338,93 @@ k_qei_cdf(const double* __restrict__ moments, int64_t B, int q, double plugin, i
   const double t0 = __shfl_sync(0xffffffffu, term, base + 0), t1 = __shfl_sync(0xffffffffu, term, base + 1);
   const double t2 = __shfl_sync(0xffffffffu, term, base + 2), t3 = __shfl_sync(0xffffffffu, term, base + 3);
   if (valid && k == 0) {
+    double res;
+    if (qq == 0) {
+      res = 0.0;                                   // every point duplicates the design (R/qEI.R:127)
+    } else if (qq == 1) {
+      // EI(x, model, plugin, type, envir): minimization takes its default TRUE (R/qEI.R:132-134)
+      const double sd = sqrt(fmax(Sg[0], 0.0)), diff = plugin - mu[0], xcr = diff / sd;
+      res = diff * normcdf(xcr) + sd * dnorm_std(xcr);
+    } else {
+      res = ((t0 + t1) + t2) + t3;
+    }
+    out[b] = res;
+  }
+}
+
+
+// One warp per batch: lane = 8 k + s (the low-latency version for small B).  The 8 lanes of group k share the q-variate CDF p_k (path-integral nodes dealt
+// round-robin, dk_mvn.cuh) and lane (k, s) evaluates the (q-1)-variate CDF of the second-term entry i = k + s.
+__global__ void __launch_bounds__(128)
+k_qei_cdf_warp(const double* __restrict__ moments, int64_t B, int q, double plugin, int minimization,
+               double* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t b = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int k = lane >> 3, s = lane & 7;
+  const bool valid = b < B;
+  const double* mom = moments + (valid ? b : 0) * MOM_STRIDE;
+  const int mask = (int)mom[20];
+  int idx[4], qq = 0;
+  for (int a = 0; a < q; a++)
+    if (mask & (1 << a)) idx[qq++] = a;
+  for (int a = qq; a < 4; a++) idx[a] = 0;
+  double mu[4], Sg[16];
+  for (int i = 0; i < 4; i++) {
+    mu[i] = mom[idx[i]];
+    for (int j = 0; j < 4; j++) Sg[i * 4 + j] = mom[4 + idx[i] * 4 + idx[j]];
+  }
+  const bool active = valid && qq >= 2 && k < qq;
+  double Sk[16], mk[4], bk[4], xk[4];
+  for (int i = 0; i < 16; i++) Sk[i] = 0.0;
+  for (int i = 0; i < 4; i++) mk[i] = bk[i] = xk[i] = 0.0;
+  if (active) {
+    covzk_dev(qq, Sg, k, Sk);
+    for (int i = 0; i < qq; i++) {
+      mk[i] = (i == k) ? -mu[k] : mu[i] - mu[k];
+      bk[i] = (i == k) ? -plugin : 0.0;
+      if (minimization) { mk[i] = -mk[i]; bk[i] = -bk[i]; }
+      xk[i] = bk[i] - mk[i];
+    }
+  }
+  // qq is the same for the whole warp (one batch): every lane runs the cooperative CDF, inactive groups idle inside
+  const double pk = (valid && qq >= 2) ? pmnorm_coop(active, qq, xk, Sk, s) : 0.0;
+  double symval = 0.0;  // sym[k][k + s]
+  const int i = k + s;
+  if (active && i < qq) {
+    const double sii = Sk[i * 4 + i], sdi = sqrt(sii);
+    const double phi_ik = dnorm_std((bk[i] - mk[i]) / sdi) / sdi;
+    double cik[4], sik[16];
+    int r = 0;
+    for (int u = 0; u < qq; u++) {
+      if (u == i) continue;
+      cik[r] = (bk[u] - mk[u]) - (bk[i] - mk[i]) * (Sk[i * 4 + u] / sii);
+      int cc = 0;
+      for (int v = 0; v < qq; v++) {
+        if (v == i) continue;
+        sik[r * 4 + cc] = Sk[u * 4 + v] - Sk[u * 4 + i] * Sk[v * 4 + i] / sii;
+        cc++;
+      }
+      r++;
+    }
+    symval = phi_ik * pmnorm_dev(qq - 1, cik, sik);
+  }
+  // group leader k gathers sym[k][i] (i >= k: lane (k, i - k)) and sym[i][k] (i < k: lane (i, k - i))
+  double second = 0.0;
+#pragma unroll
+  for (int ii = 0; ii < 4; ii++) {
+    const int lo = ii < k ? ii : k, hi = ii < k ? k : ii;
+    const double v = __shfl_sync(0xffffffffu, symval, lo * 8 + (hi - lo));
+    if (active && ii < qq) second = fma(v, Sk[ii * 4 + k], second);
+  }
+  double term = 0.0;
+  if (active) {
+    double first = (mu[k] - plugin) * pk;
+    if (minimization) first = -first;
+    term = first + second;
+  }
+  const double t0 = __shfl_sync(0xffffffffu, term, 0), t1 = __shfl_sync(0xffffffffu, term, 8);
+  const double t2 = __shfl_sync(0xffffffffu, term, 16), t3 = __shfl_sync(0xffffffffu, term, 24);
+  if (valid && lane == 0) {
     double res;
     if (qq == 0) {
       res = 0.0;                                   // every point duplicates the design (R/qEI.R:127)
