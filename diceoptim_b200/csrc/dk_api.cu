@@ -8,6 +8,8 @@
 
 #include "dk_kernels.cuh"
 #include "dk_grad.cuh"
+#include "dk_qei.cuh"
+#include "dk_akg.cuh"
 #include "dk_reduce.cuh"
 
 namespace dk {
@@ -27,6 +29,13 @@ int fail(int code, const char* fmt, ...) {
 }
 
 namespace {
+
+// cudaMalloc'ed scratch of the debug / test entry points, freed on every exit path
+struct DevBuf {
+  double* p = nullptr;
+  cudaError_t alloc(size_t doubles) { return cudaMalloc(&p, doubles * sizeof(double)); }
+  ~DevBuf() { if (p) cudaFree(p); }
+};
 
 struct DeviceGuard {
   int prev = -1;
@@ -643,11 +652,12 @@ int dk_debug_plain(dk_model* m, const double* x, int64_t N, int mode, double plu
   if (rc) return rc;
   DeviceGuard guard(m->device);
   const int n = m->n, p = m->p;
-  double *d_T = nullptr, *d_zM = nullptr, *d_v = nullptr, *d_xo = nullptr;
-  DK_CUDA_TRY(cudaMalloc(&d_T, (size_t)n * n * 8));
-  DK_CUDA_TRY(cudaMalloc(&d_zM, (size_t)n * (p + 1) * 8));
-  DK_CUDA_TRY(cudaMalloc(&d_v, (size_t)n * N * 8));
-  DK_CUDA_TRY(cudaMalloc(&d_xo, (size_t)N * (m->d + 3) * 8));
+  DevBuf bT, bzM, bv, bxo;
+  DK_CUDA_TRY(bT.alloc((size_t)n * n));
+  DK_CUDA_TRY(bzM.alloc((size_t)n * (p + 1)));
+  DK_CUDA_TRY(bv.alloc((size_t)n * N));
+  DK_CUDA_TRY(bxo.alloc((size_t)N * (m->d + 3)));
+  double *d_T = bT.p, *d_zM = bzM.p, *d_v = bv.p, *d_xo = bxo.p;
   DK_CUDA_TRY(cudaMemcpy(d_T, m->h_T, (size_t)n * n * 8, cudaMemcpyHostToDevice));
   DK_CUDA_TRY(cudaMemcpy(d_zM, m->h_zM, (size_t)n * (p + 1) * 8, cudaMemcpyHostToDevice));
   DK_CUDA_TRY(cudaMemcpy(d_xo, x, (size_t)N * m->d * 8, cudaMemcpyHostToDevice));
@@ -660,7 +670,6 @@ int dk_debug_plain(dk_model* m, const double* x, int64_t N, int mode, double plu
   if (out_main) DK_CUDA_TRY(cudaMemcpy(out_main, d_main, N * 8, cudaMemcpyDeviceToHost));
   if (out_mean) DK_CUDA_TRY(cudaMemcpy(out_mean, d_main + N, N * 8, cudaMemcpyDeviceToHost));
   if (out_sd) DK_CUDA_TRY(cudaMemcpy(out_sd, d_main + 2 * N, N * 8, cudaMemcpyDeviceToHost));
-  cudaFree(d_T); cudaFree(d_zM); cudaFree(d_v); cudaFree(d_xo);
   return DK_OK;
 }
 
@@ -734,7 +743,6 @@ extern "C" int dk_ei_dev_noalloc(dk_model* m, const double* d_x, int64_t N, doub
 // ------------------------------------------------------------------------------------------
 // qEI (R/qEI.R:119-261): batches of q <= DK_MAX_Q points
 // ------------------------------------------------------------------------------------------
-#include "dk_qei.cuh"
 
 namespace {
 bool g_qei_attr_done[64] = {};
@@ -858,23 +866,22 @@ extern "C" int dk_mvn_cdf(int q, int64_t B, const double* h, const double* S, do
   if (q < 1 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "dimension q=%d outside 1..%d", q, DK_MAX_Q);
   if (!h || !S || !out || B < 0) return fail(DK_ERR_ARG, "dk_mvn_cdf: bad argument");
   if (B == 0) return DK_OK;
-  double *d_h = nullptr, *d_S = nullptr, *d_o = nullptr;
-  DK_CUDA_TRY(cudaMalloc(&d_h, B * q * 8));
-  DK_CUDA_TRY(cudaMalloc(&d_S, B * q * q * 8));
-  DK_CUDA_TRY(cudaMalloc(&d_o, B * 8));
+  DevBuf bh, bS, bo;
+  DK_CUDA_TRY(bh.alloc((size_t)B * q));
+  DK_CUDA_TRY(bS.alloc((size_t)B * q * q));
+  DK_CUDA_TRY(bo.alloc((size_t)B));
+  double *d_h = bh.p, *d_S = bS.p, *d_o = bo.p;
   DK_CUDA_TRY(cudaMemcpy(d_h, h, B * q * 8, cudaMemcpyHostToDevice));
   DK_CUDA_TRY(cudaMemcpy(d_S, S, B * q * q * 8, cudaMemcpyHostToDevice));
   k_mvn_cdf_test<<<(unsigned)((B + 63) / 64), 64>>>(q, B, d_h, d_S, d_o);
   DK_CUDA_TRY(cudaGetLastError());
   DK_CUDA_TRY(cudaMemcpy(out, d_o, B * 8, cudaMemcpyDeviceToHost));
-  cudaFree(d_h); cudaFree(d_S); cudaFree(d_o);
   return DK_OK;
 }
 
 // ------------------------------------------------------------------------------------------
 // AKG (R/AKG.R:93-229)
 // ------------------------------------------------------------------------------------------
-#include "dk_akg.cuh"
 
 namespace {
 bool g_akg_attr_done[64] = {};

@@ -23,12 +23,7 @@ constexpr int BM = 128;
 constexpr int BN = 64;
 constexpr int KC = 16;
 constexpr int NT = 256;          // threads per CTA: 8 warps as 4 (rows) x 2 (cols), warp tile 32 x 32
-#ifdef DK_X_STAGES3
-constexpr int STAGES = 3;
-#else
-constexpr int STAGES = 4;
-#endif
-// ^   // 4 x 24 KB = region 0 exactly (the design-row staging is dead during the GEMM phase)
+constexpr int STAGES = 4;   // 4 x 24 KB = region 0 exactly (the design-row staging is dead during the GEMM phase)
 constexpr int A_TILE = BM * KC;  // doubles
 constexpr int B_TILE = KC * BN;  // doubles
 constexpr int CB_STRIDE = 72;    // row stride (doubles) of the covariance staging tile

@@ -242,11 +242,7 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
       double* dst = ring + slot * (A_TILE + B_TILE);
       mbar_arrive_expect_tx(&full[slot], STAGE_BYTES);
       bulk_load(dst, Atiles + (size_t)idx * A_TILE, A_TILE * 8, &full[slot]);
-#ifdef DK_X_BSTATIC
-      bulk_load(dst + A_TILE, Atiles + (size_t)idx * A_TILE, B_TILE * 8, &full[slot]);  // experiment: static B source
-#else
       bulk_load(dst + A_TILE, panel + (size_t)idx * B_TILE, B_TILE * 8, &full[slot]);
-#endif
     };
     if (tid == 0)
       for (int s = 0; s < STAGES - 1 && s < nk; s++) issue(s);
@@ -257,15 +253,11 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
       mbar_wait(&full[slot], par);
       const double* s = ring + slot * (A_TILE + B_TILE);
       mma_stage(acc, s, s + A_TILE, wm, wn, lane);
-#ifndef DK_X_NOCONSFENCE
       // this slot is refilled through the async proxy: order this lane's generic-proxy reads of it before that
+      // (without this fence the refill raced the LDS reads: about one corrupted tile in a thousand)
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-#endif
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[slot]);
-#ifdef DK_X_SYNCSTAGE
-      __syncthreads();
-#endif
     }
     *stage_base = base + nk;
     __syncthreads();  // every warp is done with the ring: region 0 can change role
@@ -320,7 +312,7 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
         acc[mi][ni][e] = 0.0;
       }
   }
-#ifdef DK_X_NODIAG
+#ifdef DK_X_NODIAG  // what-if build: one diagonal stage instead of eight (wrong results, timing only)
   const int ndiag = 1;
 #else
   const int ndiag = CHUNKS_PER_BLOCK;
@@ -479,7 +471,7 @@ __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __
       for (int i = tid; i < BM * d; i += NT) Xs[i] = __ldg(src + i);
     }
     __syncthreads();
-#ifndef DK_X_NOCOV
+#ifndef DK_X_NOCOV  // what-if build (tools/ab_lib.py): cost of cov-gen = time(normal) - time(-DDK_X_NOCOV)
     if constexpr (KSEL >= 0) covgen_rows<KSEL, NUGSEL>(M, Xs, xs, Cbuf, I * BM, warp, lane);
     else covgen_block(M, Xs, xs, Cbuf, I * BM, warp, lane);
 #endif
@@ -551,12 +543,6 @@ k_predict_fused_tma(const DevModel M, const CritParams P, const double* __restri
   double* panel = vscratch + (size_t)blockIdx.x * panel_doubles;
   pipeline_init(smem, tid);
   unsigned stage_base = 0;
-#ifdef DK_EXPERIMENT_STAGGER
-  if (blockIdx.x >= gridDim.x / 2) {  // experiment: desynchronise the two CTAs of an SM
-    const long long t0 = clock64();
-    while (clock64() - t0 < DK_EXPERIMENT_STAGGER) { }
-  }
-#endif
 #pragma unroll 1
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t c0 = tile * BN;
