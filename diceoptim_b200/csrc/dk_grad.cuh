@@ -62,8 +62,17 @@ __device__ __forceinline__ void grad_accumulate(const DevModel& M, const double*
                                                 int cw = -1) {
   if (cw < 0) cw = c;  // column of the W panel that supplies the weights (qEI.grad pairs point c with point cw)
   const int n = M.n, d = M.d;
+  // two design rows per step: their loads are issued together (the pass is latency-bound otherwise)
+  int i = slice;
 #pragma unroll 1
-  for (int i = slice; i < n; i += 4) {
+  for (; i + 4 < n; i += 8) {
+    const double om0 = cA * __ldg(M.alpha + i) + cW * panel_at(wpanel, n - 1 - i, cw);
+    const double om1 = cA * __ldg(M.alpha + i + 4) + cW * panel_at(wpanel, n - 1 - (i + 4), cw);
+    const double c0 = __ldcg(cpanel + (size_t)i * BN + c), c1 = __ldcg(cpanel + (size_t)(i + 4) * BN + c);
+    accum_dlogk<KERNEL>(M, xs, M.Xrm + (size_t)i * d, c, c0 * om0, g);
+    accum_dlogk<KERNEL>(M, xs, M.Xrm + (size_t)(i + 4) * d, c, c1 * om1, g);
+  }
+  if (i < n) {
     const double omega = cA * __ldg(M.alpha + i) + cW * panel_at(wpanel, n - 1 - i, cw);
     const double cwv = __ldcg(cpanel + (size_t)i * BN + c) * omega;
     accum_dlogk<KERNEL>(M, xs, M.Xrm + (size_t)i * d, c, cwv, g);
@@ -162,8 +171,13 @@ k_grad_fused(const DevModel M, const CritParams P, const double* __restrict__ x,
     __syncthreads();
 
     // ---- backward blocked solve with the flipped factor: wt' = flip(T)^-1 flip(v + M r) ----
+#ifdef DK_X_NOBWD  // what-if build: skip the backward solve (timing only)
+    const int nbwd = 0;
+#else
+    const int nbwd = M.nblk_b;
+#endif
 #pragma unroll 1
-    for (int I = 0; I < M.nblk_b; I++) {
+    for (int I = 0; I < nbwd; I++) {
       double acc[4][4][2];
 #pragma unroll
       for (int mi = 0; mi < 4; mi++) {

@@ -240,3 +240,20 @@ def test_cfg2_full_size_properties(gpu_lib):
     perm = np.random.default_rng(1).permutation(N)
     assert np.array_equal(EI(x[perm], km), ei[perm])
     km.release()
+
+
+def test_ill_conditioned_factor(gpu_lib):
+    """cond(K) ~ 1e12 (matern5_2, long range): the blocked solve with explicit 128 x 128 diagonal inverses must stay
+    as accurate as LAPACK's substitution (SURVEY 7 'hard parts'): variance within 1e-10 of sd2.  The mean v'z is itself
+    ill-conditioned here (|z| is huge): GPU and oracle are both ~1e-7 from a long-double solve, so 1e-6 of the scale."""
+    from diceoptim_b200 import synth
+    X = synth.lhs(700, 4, 9)
+    y = np.sin(3.0 * X.sum(1))
+    km = synth.make_km(X, y, "matern5_2", 2.0, float(np.var(y)))
+    x = np.random.default_rng(2).random((300, 4))
+    check_predict(km, x, rtol=1e-6)
+    from diceoptim_b200 import predict
+    from oracle import dicekriging as dk
+    got = predict(km, x); ref = dk.predict_km(to_oracle(km), x, light_return=True)
+    assert np.max(np.abs(got["sd"] ** 2 - ref["sd"] ** 2)) <= 1e-10 * km.covariance.sd2
+    km.release()

@@ -1,4 +1,4 @@
-"""Time the cfg4 EI kernel with an alternative build of the library: python tools/ab_lib.py <lib.so> [N]"""
+"""Time the cfg4 EI (or EI.grad) kernel with an alternative build of the library: python tools/ab_lib.py <lib.so> [N] [ei|grad]"""
 import ctypes as C, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -6,11 +6,16 @@ from diceoptim_b200 import _lib, synth
 _lib.LIB_PATH = os.path.abspath(sys.argv[1])
 lib = _lib.load()
 N = int(sys.argv[2]) if len(sys.argv) > 2 else 1000000
+mode = sys.argv[3] if len(sys.argv) > 3 else "ei"
 km = synth.config_model(os.environ.get("DK_CFG", "cfg4_sphere10_n2000"))
 h = km.handle(0); lib.dk_model_set_timing(h.ptr, 1)
 x = torch.rand((km.d, N), dtype=torch.float64, device="cuda"); ei = torch.empty(N, dtype=torch.float64, device="cuda")
+gr = torch.empty((km.d, N), dtype=torch.float64, device="cuda") if mode == "grad" else None
 ms = []
 for _ in range(3):
-    _lib.check(lib.dk_ei_dev(h.ptr, C.c_void_p(x.data_ptr()), N, float(np.min(km.y)), 1, 1, 0, C.c_void_p(ei.data_ptr()), None, None, None), "ei")
+    if mode == "grad":
+        _lib.check(lib.dk_ei_grad_dev(h.ptr, C.c_void_p(x.data_ptr()), N, float(np.min(km.y)), 1, 1, 0, C.c_void_p(gr.data_ptr()), C.c_void_p(ei.data_ptr()), None), "grad")
+    else:
+        _lib.check(lib.dk_ei_dev(h.ptr, C.c_void_p(x.data_ptr()), N, float(np.min(km.y)), 1, 1, 0, C.c_void_p(ei.data_ptr()), None, None, None), "ei")
     torch.cuda.synchronize(); ms.append(lib.dk_model_last_kernel_ms(h.ptr))
 print(os.path.basename(sys.argv[1]), N, [round(m, 2) for m in ms], "cand/s %.3e" % (N / (min(ms) * 1e-3)), "checksum", float(ei.sum()))
