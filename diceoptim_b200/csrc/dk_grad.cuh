@@ -29,9 +29,19 @@ __device__ __forceinline__ double rcp_pos(double x) {
   return r;
 }
 
+// d log k / d x_k of one design row.  With t = (x_k - X_ik) w_k and a = |t|:  gauss -t w ; exp -sign(t) w ;
+// matern3_2 -w t / (1 + a) ; matern5_2 -w (t / 3)(1 + a) / (1 + a + a^2 / 3) ; powexp -sign(t) p a^(p-1) w.
+template <int KERNEL>
+__device__ __forceinline__ double dlogk_scaled(const DevModel& M, int k, double t, double wk) {
+  const double a = fabs(t);
+  if (KERNEL == DK_GAUSS) return -t * wk;
+  if (KERNEL == DK_EXP) return (t > 0.0) ? -wk : ((t < 0.0) ? wk : 0.0);
+  if (KERNEL == DK_MATERN3_2) return -wk * t * rcp_pos(1.0 + a);
+  if (KERNEL == DK_MATERN5_2) return -(wk * (1.0 / 3.0)) * t * (1.0 + a) * rcp_pos(fma(a, fma(a, 1.0 / 3.0, 1.0), 1.0));
+  return (a > 0.0) ? -copysign(M.shape[k] * pow(a, M.shape[k] - 1.0) * wk, t) : 0.0;
+}
+
 // g_k += cwv * dlogk_k(x - X_i) for all k (covVector.dx of one design row, already weighted).
-// With t = (x_k - X_ik) w_k and a = |t|:  gauss -t w ; exp -sign(t) w ; matern3_2 -w t / (1 + a) ;
-// matern5_2 -w (t / 3)(1 + a) / (1 + a + a^2 / 3) ; powexp -sign(t) p a^(p-1) w.
 template <int KERNEL>
 __device__ __forceinline__ void accum_dlogk(const DevModel& M, const double* __restrict__ xs,
                                             const double* __restrict__ Xi, int c, double cwv, double (&g)[DK_MAX_D]) {
@@ -41,14 +51,7 @@ __device__ __forceinline__ void accum_dlogk(const DevModel& M, const double* __r
     if (k < d) {
       const double wk = M.w[k];
       const double t = (xs[k * BN + c] - __ldg(Xi + k)) * wk;
-      const double a = fabs(t);
-      double dl;
-      if (KERNEL == DK_GAUSS) dl = -t * wk;
-      else if (KERNEL == DK_EXP) dl = (t > 0.0) ? -wk : ((t < 0.0) ? wk : 0.0);
-      else if (KERNEL == DK_MATERN3_2) dl = -wk * t * rcp_pos(1.0 + a);
-      else if (KERNEL == DK_MATERN5_2) dl = -(wk * (1.0 / 3.0)) * t * (1.0 + a) * rcp_pos(fma(a, fma(a, 1.0 / 3.0, 1.0), 1.0));
-      else dl = (a > 0.0) ? -copysign(M.shape[k] * pow(a, M.shape[k] - 1.0) * wk, t) : 0.0;
-      g[k] = fma(cwv, dl, g[k]);
+      g[k] = fma(cwv, dlogk_scaled<KERNEL>(M, k, t, wk), g[k]);
     }
   }
 }

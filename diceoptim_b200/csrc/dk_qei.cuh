@@ -264,7 +264,10 @@ __device__ __forceinline__ void covzk_dev(int q, const double* S, int k, double*
 }
 
 // Four lanes per batch (one per k): the throughput version, used when there are enough batches to fill the GPU.
-__global__ void __launch_bounds__(128)
+#ifndef DK_CDF_MINB
+#define DK_CDF_MINB 4
+#endif
+__global__ void __launch_bounds__(128, DK_CDF_MINB)
 k_qei_cdf(const double* __restrict__ moments, int64_t B, int q, double plugin, int minimization,
           double* __restrict__ out) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -458,6 +461,44 @@ __global__ void k_mvn_cdf_test(int q, int64_t B, const double* __restrict__ h, c
 // per batch: mj[k][j] = d m_k / d x_kj (4 x d) followed by cj[k][l][j] = one-sided d Sigma_kl / d x_kj (16 x d)
 __host__ __device__ inline size_t qei_deriv_stride(int d) { return (size_t)20 * d; }
 
+// The q + 1 derivative contractions of one batch point c (columns 4g .. 4g+3 hold its batch), dims k0 .. k0+3,
+// in ONE sweep over the design rows i = slice, slice + 4, ...:
+//   acc[0][kk]     += c_i alpha_i        dlogk_k(i)     (d m / d x, R/qEI.grad.R:128)
+//   acc[1 + l][kk] += c_i wt_i[4g + l]   dlogk_k(i)     (dc' wt_l of d Sigma_kl / d x, R/qEI.grad.R:130-137)
+// Same per-accumulator order of additions as a sweep per weight vector, so the results do not depend on the fusion.
+template <int KERNEL>
+__device__ __forceinline__ void qei_deriv_accumulate(const DevModel& M, const double* __restrict__ xs,
+                                                     const double* __restrict__ cpanel,
+                                                     const double* __restrict__ wpanel, int c, int slice, int q, int k0,
+                                                     double (&acc)[5][4]) {
+  const int n = M.n, d = M.d, g4 = c & ~3;
+  double xk[4], wk[4];
+#pragma unroll
+  for (int kk = 0; kk < 4; kk++) {
+    const int k = k0 + kk;
+    xk[kk] = (k < d) ? xs[k * BN + c] : 0.0;
+    wk[kk] = (k < d) ? M.w[k] : 0.0;
+  }
+#pragma unroll 2
+  for (int i = slice; i < n; i += 4) {
+    const double ci = __ldcg(cpanel + (size_t)i * BN + c);
+    double om[5];
+    om[0] = ci * __ldg(M.alpha + i);
+#pragma unroll
+    for (int l = 0; l < 4; l++) om[1 + l] = (l < q) ? ci * panel_at(wpanel, n - 1 - i, g4 + l) : 0.0;
+    const double* Xi = M.Xrm + (size_t)i * d;
+#pragma unroll
+    for (int kk = 0; kk < 4; kk++) {
+      const int k = k0 + kk;
+      if (k < d) {
+        const double dl = dlogk_scaled<KERNEL>(M, k, (xk[kk] - __ldg(Xi + k)) * wk[kk], wk[kk]);
+#pragma unroll
+        for (int ps = 0; ps < 5; ps++) acc[ps][kk] = fma(om[ps], dl, acc[ps][kk]);
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(NT, 2)
 k_qei_grad_moments(const DevModel M, int type, int q, const double* __restrict__ x, int64_t B, int64_t ntiles,
                    double* __restrict__ vscratch, double* __restrict__ wscratch, double* __restrict__ cscratch,
@@ -507,43 +548,45 @@ k_qei_grad_moments(const DevModel M, int type, int q, const double* __restrict__
       __syncthreads();
     }
 
-    // ---- derivative passes: pass 0 weights alpha (mean), pass 1 + l weights wt of the batch's point l ----
+    // ---- derivative contractions: weights alpha (mean) and wt of each point l of the batch, four dims per sweep ----
     const int c = tid & (BN - 1), slice = tid >> 6, g = c >> 2, kpt = c & 3;
-    double* gbuf = reinterpret_cast<double*>(smem);  // [4][DK_MAX_D][64]
+    double* gbuf = reinterpret_cast<double*>(smem);  // [4 slices][5 weights][4 dims][64]
+    const int64_t b = b0 + g;
 #pragma unroll 1
-    for (int pass = 0; pass <= q; pass++) {
-      double gk[DK_MAX_D];
+    for (int k0 = 0; k0 < d; k0 += 4) {
+      double acc[5][4];
 #pragma unroll
-      for (int k = 0; k < DK_MAX_D; k++) gk[k] = 0.0;
-      const double cA = pass == 0 ? 1.0 : 0.0, cW = pass == 0 ? 0.0 : 1.0;
-      const int cw = pass == 0 ? c : 4 * g + (pass - 1);
+      for (int ps = 0; ps < 5; ps++)
+#pragma unroll
+        for (int kk = 0; kk < 4; kk++) acc[ps][kk] = 0.0;
       switch (M.kernel) {
-        case DK_GAUSS: grad_accumulate<DK_GAUSS>(M, xs, cpanel, wpanel, c, slice, cA, cW, gk, cw); break;
-        case DK_EXP: grad_accumulate<DK_EXP>(M, xs, cpanel, wpanel, c, slice, cA, cW, gk, cw); break;
-        case DK_MATERN3_2: grad_accumulate<DK_MATERN3_2>(M, xs, cpanel, wpanel, c, slice, cA, cW, gk, cw); break;
-        case DK_MATERN5_2: grad_accumulate<DK_MATERN5_2>(M, xs, cpanel, wpanel, c, slice, cA, cW, gk, cw); break;
-        default: grad_accumulate<DK_POWEXP>(M, xs, cpanel, wpanel, c, slice, cA, cW, gk, cw); break;
+        case DK_GAUSS: qei_deriv_accumulate<DK_GAUSS>(M, xs, cpanel, wpanel, c, slice, q, k0, acc); break;
+        case DK_EXP: qei_deriv_accumulate<DK_EXP>(M, xs, cpanel, wpanel, c, slice, q, k0, acc); break;
+        case DK_MATERN3_2: qei_deriv_accumulate<DK_MATERN3_2>(M, xs, cpanel, wpanel, c, slice, q, k0, acc); break;
+        case DK_MATERN5_2: qei_deriv_accumulate<DK_MATERN5_2>(M, xs, cpanel, wpanel, c, slice, q, k0, acc); break;
+        default: qei_deriv_accumulate<DK_POWEXP>(M, xs, cpanel, wpanel, c, slice, q, k0, acc); break;
       }
 #pragma unroll
-      for (int k = 0; k < DK_MAX_D; k++)
-        if (k < d) gbuf[(slice * DK_MAX_D + k) * BN + c] = gk[k];
+      for (int ps = 0; ps < 5; ps++)
+#pragma unroll
+        for (int kk = 0; kk < 4; kk++) gbuf[((slice * 5 + ps) * 4 + kk) * BN + c] = acc[ps][kk];
       __syncthreads();
-      const int64_t b = b0 + g;
-      if (b < B && kpt < q) {
+      // thread (c, slice) finishes dim k0 + slice for all weights
+      const int k = k0 + slice;
+      if (b < B && kpt < q && k < d) {
         double* dv = deriv + b * dstride;
-        const int l = pass - 1;
-        const double kkl = (pass == 0 || l == kpt) ? 0.0 : cov_pair(M, xs, c, 4 * g + l);
-        for (int k = slice; k < d; k += 4) {
-          const double s = ((gbuf[(0 * DK_MAX_D + k) * BN + c] + gbuf[(1 * DK_MAX_D + k) * BN + c]) +
-                            gbuf[(2 * DK_MAX_D + k) * BN + c]) + gbuf[(3 * DK_MAX_D + k) * BN + c];
-          if (pass == 0) {
+        for (int ps = 0; ps <= q; ps++) {
+          const double s = ((gbuf[((0 * 5 + ps) * 4 + slice) * BN + c] + gbuf[((1 * 5 + ps) * 4 + slice) * BN + c]) +
+                            gbuf[((2 * 5 + ps) * 4 + slice) * BN + c]) + gbuf[((3 * 5 + ps) * 4 + slice) * BN + c];
+          if (ps == 0) {
             double v = s;  // dc_k' alpha
             if (M.trend == DK_TREND_LINEAR) v += __ldg(M.beta + 1 + k);
             dv[kpt * d + k] = v;
           } else {
             // ker.grad(k, l) - dc_k' wt_l + f.deltax' r_l
+            const int l = ps - 1;
             double v = -s;
-            if (l != kpt) v += kkl * dlogk_dev(M, k, xs[k * BN + c] - xs[k * BN + 4 * g + l]);
+            if (l != kpt) v += cov_pair(M, xs, c, 4 * g + l) * dlogk_dev(M, k, xs[k * BN + c] - xs[k * BN + 4 * g + l]);
             if (M.trend == DK_TREND_LINEAR) v += __ldcg(coef + (2 + 1 + k) * BN + 4 * g + l);
             dv[(4 + kpt * 4 + l) * d + k] = v;
           }
