@@ -308,14 +308,21 @@ __device__ __forceinline__ double pmnorm_coop(bool active, int q, const double* 
   return fmin(1.0, fmax(0.0, group8_sum(part)));
 }
 
-// pmnorm(x, varcov = S) for q = 1..4; S row-major with leading dimension 4.
-__device__ __forceinline__ double pmnorm_dev(int q, const double* x, const double* S) {
-  double z[4], R[16];
-  for (int i = 0; i < q; i++) z[i] = x[i] / sqrt(S[i * 4 + i]);
+// pmnorm(x, varcov = S) for q = 1..4; S row-major with leading dimension 4.  Out of line and rolled: the callers
+// reach it from a dozen sites and the square roots / divisions expand to ~100 instructions each.
+__device__ __noinline__ double pmnorm_dev(int q, const double* x, const double* S) {
+  double sd[4], z[4], R[16];
+#pragma unroll 1
+  for (int i = 0; i < q; i++) {
+    sd[i] = sqrt(S[i * 4 + i]);
+    z[i] = x[i] / sd[i];
+  }
   if (q == 1) return phi_cdf(z[0]);
+#pragma unroll 1
   for (int i = 0; i < q; i++)
+#pragma unroll 1
     for (int j = 0; j < q; j++) {
-      const double r = S[i * 4 + j] / (sqrt(S[i * 4 + i]) * sqrt(S[j * 4 + j]));
+      const double r = S[i * 4 + j] / (sd[i] * sd[j]);
       R[i * 4 + j] = (i == j) ? 1.0 : fmax(-1.0, fmin(1.0, r));
     }
   if (q == 2) return bvn_cdf_dev(z[0], z[1], R[1]);

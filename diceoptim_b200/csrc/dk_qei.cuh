@@ -781,6 +781,8 @@ k_qei_grad_cdf(const double* __restrict__ moments, const double* __restrict__ de
     }
 
     const double fac = plugin - kmean[k];
+    double inv_sii[4];
+    for (int i = 0; i < q; i++) inv_sii[i] = 1.0 / Sigk[i * 4 + i];
     for (int l = 0; l < q; l++) {
       for (int j = 0; j < d; j++) {
         // J = symmetrised cov.jacob[l, j, , ]: row/column l carry the one-sided derivatives, (l, l) twice
@@ -824,19 +826,21 @@ k_qei_grad_cdf(const double* __restrict__ moments, const double* __restrict__ de
           const double sdx_ii = Sdx[i * 4 + i];
           const double B1 = Sdx[i * 4 + k] * phi_i[i] * Phi_i[i];
           const double B2 = S_ik * (mdx[i] * dphi_dm[i] + dphi_dS[i] * sdx_ii) * Phi_i[i];
+          // the divisions by S_ii of R/qEI.grad.R:398-412 as products with 1 / S_ii (formed once per i above)
+          const double is = inv_sii[i], is2 = is * is;
+          const double dc_a = (mdx[i] * S_ii + dm * sdx_ii) * is2, dc_b = dm * is, ds_a = sdx_ii * is2;
           double gd = 0.0, hd = 0.0;
           int r = 0;
           for (int u = 0; u < q; u++) {
             if (u == i) continue;
             const double S_ui = Sigk[u * 4 + i];
-            const double dck = -mdx[u] + (mdx[i] * S_ii + dm * sdx_ii) / (S_ii * S_ii) * S_ui - dm / S_ii * Sdx[u * 4 + i];
+            const double dck = -mdx[u] + dc_a * S_ui - dc_b * Sdx[u * 4 + i];
             gd += Gik[i][r] * dck;
             int cc = 0;
             for (int v = 0; v < q; v++) {
               if (v == i) continue;
               const double S_vi = Sigk[v * 4 + i];
-              const double dS = Sdx[u * 4 + v] + sdx_ii / (S_ii * S_ii) * S_ui * S_vi -
-                                (Sdx[u * 4 + i] * S_vi + Sdx[v * 4 + i] * S_ui) / S_ii;
+              const double dS = Sdx[u * 4 + v] + ds_a * S_ui * S_vi - (Sdx[u * 4 + i] * S_vi + Sdx[v * 4 + i] * S_ui) * is;
               hd += Hik[i][r * 4 + cc] * dS;
               cc++;
             }
