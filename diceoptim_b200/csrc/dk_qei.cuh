@@ -615,11 +615,13 @@ __device__ __noinline__ double decompo1(int q, const double* x, const double* mu
   if (q == 1) return dens;
   double x2[4], V[16];
   int r = 0;
+#pragma unroll 1
   for (int u = 0; u < q; u++) {
     if (u == i) continue;
     const double moy = mu[u] + S[u * 4 + i] / sii * (x[i] - mu[i]);
     x2[r] = x[u] - moy;
     int cc = 0;
+#pragma unroll 1
     for (int v = 0; v < q; v++) {
       if (v == i) continue;
       // 0.5 (varcov + t(varcov)) with varcov = S22 - S21 S11^-1 S12
@@ -631,8 +633,10 @@ __device__ __noinline__ double decompo1(int q, const double* x, const double* mu
     r++;
   }
   double mn = V[0];
+#pragma unroll 1
   for (int u = 1; u < q - 1; u++) mn = fmin(mn, V[u * 4 + u]);
   if (mn <= 0.0)
+#pragma unroll 1
     for (int u = 0; u < q - 1; u++) V[u * 4 + u] = (V[u * 4 + u] >= 0.0 ? V[u * 4 + u] : 0.0) + 1e-9;
   return dens * pmnorm_dev(q - 1, x2, V);
 }
@@ -647,12 +651,14 @@ __device__ __noinline__ double decompo2(int q, const double* x, const double* mu
   // S11^-1 = [[sjj, -sij], [-sij, sii]] / det
   double x2[4], V[16];
   int r = 0;
+#pragma unroll 1
   for (int u = 0; u < q; u++) {
     if (u == i || u == j) continue;
     const double a_ui = S[u * 4 + i], a_uj = S[u * 4 + j];
     const double wi = (a_ui * sjj - a_uj * sij) / det, wj = (-a_ui * sij + a_uj * sii) / det;  // S21 S11^-1 (row u)
     x2[r] = x[u] - (mu[u] + wi * di + wj * dj);
     int cc = 0;
+#pragma unroll 1
     for (int v = 0; v < q; v++) {
       if (v == i || v == j) continue;
       const double b_vi = S[v * 4 + i], b_vj = S[v * 4 + j];
@@ -665,14 +671,17 @@ __device__ __noinline__ double decompo2(int q, const double* x, const double* mu
     r++;
   }
   double mn = V[0];
+#pragma unroll 1
   for (int u = 1; u < q - 2; u++) mn = fmin(mn, V[u * 4 + u]);
   if (mn <= 0.0)
+#pragma unroll 1
     for (int u = 0; u < q - 2; u++) V[u * 4 + u] = (V[u * 4 + u] >= 0.0 ? V[u * 4 + u] : 0.0) + 1e-9;
   return dens * pmnorm_dev(q - 2, x2, V);
 }
 
 // GPhi / HPhi (R/qEI.grad.R:29-60): gradient and Hessian of the q-variate normal CDF
 __device__ __forceinline__ void gphi_dev(int q, const double* x, const double* mu, const double* S, double* g) {
+#pragma unroll 1
   for (int i = 0; i < q; i++) g[i] = decompo1(q, x, mu, S, i);
 }
 __device__ __forceinline__ void hphi_dev(int q, const double* x, const double* mu, const double* S, const double* g,
@@ -681,12 +690,18 @@ __device__ __forceinline__ void hphi_dev(int q, const double* x, const double* m
     H[0] = -(x[0] - mu[0]) / S[0] * dmnorm1(x[0], mu[0], S[0]);
     return;
   }
+#pragma unroll 1
   for (int i = 0; i < q; i++)
+#pragma unroll 1
     for (int j = 0; j < q; j++) H[i * 4 + j] = 0.0;
+#pragma unroll 1
   for (int i = 0; i < q - 1; i++)
+#pragma unroll 1
     for (int j = i + 1; j < q; j++) H[i * 4 + j] = H[j * 4 + i] = decompo2(q, x, mu, S, i, j);
+#pragma unroll 1
   for (int i = 0; i < q; i++) {
     double sr = 0.0;
+#pragma unroll 1
     for (int j = 0; j < q; j++)
       if (j != i) sr += S[i * 4 + j] * H[j * 4 + i];
     H[i * 4 + i] = -((x[i] - mu[i]) * g[i] + sr) / S[i * 4 + i];
@@ -705,48 +720,66 @@ k_qei_grad_cdf(const double* __restrict__ moments, const double* __restrict__ de
   const int mask = (int)mom[20];
   const double sgn = minimization ? 1.0 : -1.0;
   double kmean[4], kcov[16];
+#pragma unroll 1
   for (int i = 0; i < q; i++) {
     kmean[i] = sgn * mom[i];
+#pragma unroll 1
     for (int j = 0; j < q; j++) kcov[i * 4 + j] = mom[4 + i * 4 + j];
   }
   // zero matrix when any point is a duplicate (R/qEI.grad.R:293-295) or all variances vanish (:107)
   bool alltiny = true;
+#pragma unroll 1
   for (int i = 0; i < q; i++) alltiny = alltiny && (kcov[i * 4 + i] / sd2 < 1e-8);
   const bool active = valid && k < q && mask == (1 << q) - 1 && !alltiny;
 
   double G[4][DK_MAX_D];
+#pragma unroll 1
   for (int l = 0; l < 4; l++)
+#pragma unroll 1
     for (int j = 0; j < DK_MAX_D; j++) G[l][j] = 0.0;
 
   if (active) {
     // Lk = -I with column k set to one; mk = Lk kmean; Sigk = Lk kcov Lk'
     double Lk[16], mk[4], Sigk[16], bk[4], zero4[4] = {0.0, 0.0, 0.0, 0.0}, xs_[4];
+#pragma unroll 1
     for (int a = 0; a < q; a++)
+#pragma unroll 1
       for (int c = 0; c < q; c++) Lk[a * 4 + c] = (c == k) ? 1.0 : ((a == c) ? -1.0 : 0.0);
+#pragma unroll 1
     for (int a = 0; a < q; a++) {
       double s = 0.0;
+#pragma unroll 1
       for (int c = 0; c < q; c++) s += Lk[a * 4 + c] * kmean[c];
       mk[a] = s;
       bk[a] = (a == k) ? plugin : 0.0;
     }
     {
       double tmp[16];
+#pragma unroll 1
       for (int a = 0; a < q; a++)
+#pragma unroll 1
         for (int c = 0; c < q; c++) {
           double s = 0.0;
+#pragma unroll 1
           for (int e = 0; e < q; e++) s += Lk[a * 4 + e] * kcov[e * 4 + c];
           tmp[a * 4 + c] = s;
         }
       double raw[16];
+#pragma unroll 1
       for (int a = 0; a < q; a++)
+#pragma unroll 1
         for (int c = 0; c < q; c++) {
           double s = 0.0;
+#pragma unroll 1
           for (int e = 0; e < q; e++) s += tmp[a * 4 + e] * Lk[c * 4 + e];
           raw[a * 4 + c] = s;
         }
+#pragma unroll 1
       for (int a = 0; a < q; a++)
+#pragma unroll 1
         for (int c = 0; c < q; c++) Sigk[a * 4 + c] = 0.5 * (raw[a * 4 + c] + raw[c * 4 + a]);
     }
+#pragma unroll 1
     for (int a = 0; a < q; a++) xs_[a] = bk[a] - mk[a];
     const double pk = pmnorm_dev(q, xs_, Sigk);
     double gradpk[4], hesspk[16];
@@ -755,6 +788,7 @@ k_qei_grad_cdf(const double* __restrict__ moments, const double* __restrict__ de
 
     // per-i quantities of the exact term B (R/qEI.grad.R:379-396)
     double phi_i[4], dphi_dS[4], dphi_dm[4], Phi_i[4], Gik[4][4], Hik[4][16];
+#pragma unroll 1
     for (int i = 0; i < q; i++) {
       const double S_ii = Sigk[i * 4 + i], dm = bk[i] - mk[i];
       phi_i[i] = dmnorm1(bk[i], mk[i], S_ii);
@@ -762,10 +796,12 @@ k_qei_grad_cdf(const double* __restrict__ moments, const double* __restrict__ de
       dphi_dm[i] = dm / S_ii * phi_i[i];
       double ck[4], Sp[16];
       int r = 0;
+#pragma unroll 1
       for (int u = 0; u < q; u++) {
         if (u == i) continue;
         ck[r] = bk[u] - mk[u] - dm / S_ii * Sigk[u * 4 + i];
         int cc = 0;
+#pragma unroll 1
         for (int v = 0; v < q; v++) {
           if (v == i) continue;
           const double a1 = Sigk[u * 4 + v] - Sigk[u * 4 + i] * Sigk[v * 4 + i] / S_ii;
@@ -782,13 +818,19 @@ k_qei_grad_cdf(const double* __restrict__ moments, const double* __restrict__ de
 
     const double fac = plugin - kmean[k];
     double inv_sii[4];
+#pragma unroll 1
     for (int i = 0; i < q; i++) inv_sii[i] = 1.0 / Sigk[i * 4 + i];
+#pragma unroll 1
     for (int l = 0; l < q; l++) {
+#pragma unroll 1
       for (int j = 0; j < d; j++) {
         // J = symmetrised cov.jacob[l, j, , ]: row/column l carry the one-sided derivatives, (l, l) twice
         double J[16];
+#pragma unroll 1
         for (int a = 0; a < q; a++)
+#pragma unroll 1
           for (int c = 0; c < q; c++) J[a * 4 + c] = 0.0;
+#pragma unroll 1
         for (int i = 0; i < q; i++) {
           const double v = dv[(4 + l * 4 + i) * d + j];
           if (i == l) J[l * 4 + l] = 2.0 * v;
@@ -798,29 +840,39 @@ k_qei_grad_cdf(const double* __restrict__ moments, const double* __restrict__ de
         double Sdx[16], mdx[4];
         {
           double tmp[16];
+#pragma unroll 1
           for (int a = 0; a < q; a++)
+#pragma unroll 1
             for (int c = 0; c < q; c++) {
               double s = 0.0;
+#pragma unroll 1
               for (int e = 0; e < q; e++) s += Lk[a * 4 + e] * J[e * 4 + c];
               tmp[a * 4 + c] = s;
             }
+#pragma unroll 1
           for (int a = 0; a < q; a++)
+#pragma unroll 1
             for (int c = 0; c < q; c++) {
               double s = 0.0;
+#pragma unroll 1
               for (int e = 0; e < q; e++) s += tmp[a * 4 + e] * Lk[c * 4 + e];
               Sdx[a * 4 + c] = s;
             }
         }
+#pragma unroll 1
         for (int a = 0; a < q; a++) mdx[a] = Lk[a * 4 + l] * mjl;
         // A2: Dpk = 0.5 sum(hesspk * Sdx) - gradpk' mdx
         double hs = 0.0, gm = 0.0;
+#pragma unroll 1
         for (int a = 0; a < q; a++) {
           gm += gradpk[a] * mdx[a];
+#pragma unroll 1
           for (int c = 0; c < q; c++) hs += hesspk[a * 4 + c] * Sdx[a * 4 + c];
         }
         double acc = fac * (0.5 * hs - gm);
         if (l == k) acc -= mjl * pk;                 // A1
         // B1 + B2 + B3
+#pragma unroll 1
         for (int i = 0; i < q; i++) {
           const double S_ik = Sigk[i * 4 + k], S_ii = Sigk[i * 4 + i], dm = bk[i] - mk[i];
           const double sdx_ii = Sdx[i * 4 + i];
@@ -831,12 +883,14 @@ k_qei_grad_cdf(const double* __restrict__ moments, const double* __restrict__ de
           const double dc_a = (mdx[i] * S_ii + dm * sdx_ii) * is2, dc_b = dm * is, ds_a = sdx_ii * is2;
           double gd = 0.0, hd = 0.0;
           int r = 0;
+#pragma unroll 1
           for (int u = 0; u < q; u++) {
             if (u == i) continue;
             const double S_ui = Sigk[u * 4 + i];
             const double dck = -mdx[u] + dc_a * S_ui - dc_b * Sdx[u * 4 + i];
             gd += Gik[i][r] * dck;
             int cc = 0;
+#pragma unroll 1
             for (int v = 0; v < q; v++) {
               if (v == i) continue;
               const double S_vi = Sigk[v * 4 + i];
