@@ -265,7 +265,7 @@ __device__ __forceinline__ void covzk_dev(int q, const double* S, int k, double*
 
 // Four lanes per batch (one per k): the throughput version, used when there are enough batches to fill the GPU.
 #ifndef DK_CDF_MINB
-#define DK_CDF_MINB 4
+#define DK_CDF_MINB 5
 #endif
 __global__ void __launch_bounds__(128, DK_CDF_MINB)
 k_qei_cdf(const double* __restrict__ moments, int64_t B, int q, double plugin, int minimization,
