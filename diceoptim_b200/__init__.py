@@ -6,8 +6,8 @@ include/dk_b200.h), the ctypes binding, and the host-side mirror of the R interf
 DiceKriging; ``synth`` only builds km objects with FIXED hyper-parameters for tests and bench.
 """
 from .km import KM, Covariance, DeviceModel  # noqa: F401
-from .api import (AEI, AEI_grad, EQI_grad, AKG, AKG_grad, EI, EQI, EI_grad, kriging_quantile, kriging_quantile_grad, max_crit, max_qEI, predict, qEI, qEI_grad,  # noqa: F401
+from .api import (AEI, AEI_grad, EQI_grad, AKG, AKG_grad, EI, EQI, EI_grad, kriging_quantile, kriging_quantile_grad, max_crit, max_EI, max_qEI, predict, qEI, qEI_grad,  # noqa: F401
                   sampleFromEI, screen_EI)
 
 __all__ = ["AEI", "AEI_grad", "EQI", "EQI_grad", "AKG", "AKG_grad", "KM", "Covariance", "DeviceModel", "EI", "EI_grad", "kriging_quantile", "kriging_quantile_grad",
-           "max_crit", "max_qEI", "predict", "qEI", "qEI_grad", "sampleFromEI", "screen_EI"]
+           "max_crit", "max_EI", "max_qEI", "predict", "qEI", "qEI_grad", "sampleFromEI", "screen_EI"]

@@ -95,6 +95,17 @@ def EI_grad(x, model: KM, plugin=None, type="UK", minimization=True, envir=None,
     return grad[0].copy() if single else grad
 
 
+def _ei_value_and_grad(x, model: KM, plugin, type, minimization, proxy, device):
+    """EI and its gradient for every row of ``x`` from ONE launch of the gradient kernel (dk_ei_grad fills both)."""
+    x = _as_candidates(x, model.d)
+    N = x.shape[0]
+    grad = np.empty((N, model.d), order="F"); ei = np.empty(N)
+    h = model.handle(device)
+    _lib.check(_lib.load().dk_ei_grad(h.ptr, _vp(x), N, float(plugin), _type_id(type), int(bool(minimization)),
+                                      int(bool(proxy)), _vp(grad), _vp(ei)), "dk_ei_grad")
+    return ei, grad
+
+
 def kriging_quantile(x, model: KM, beta=0.1, type="UK", envir=None, device=0):
     """Kriging quantile mk + qnorm(beta) sk, R/kriging.quantile.R:92-115."""
     x = _as_candidates(x, model.d)
@@ -159,6 +170,23 @@ def max_crit(model: KM, type="UK", lower=None, upper=None, minimization=True, co
     N = int(control.get("n.ei", min(2000, 500 * d)))
     plugin = _default_plugin(model, minimization)
     rng = np.random.default_rng(seed)
+    if control.get("optimizer", "batched") == "batched":
+        # every restart's screen, then ONE batched polish of the restarts' winners (optim.py)
+        from .optim import batched_lbfgsb
+        starts = np.empty((restarts, d)); vals = np.empty(restarts)
+        for r in range(restarts):
+            x = lower + rng.random((N, d)) * (upper - lower)
+            idx, val = screen_EI(x, model, plugin=None, type=type, minimization=minimization, proxy=proxy, device=device)
+            starts[r], vals[r] = x[idx[0]], val[0]
+        if bfgs:
+            def fg(X):
+                ei, gr = _ei_value_and_grad(X, model, plugin, type, True, proxy, device)   # R/max_crit.R:119
+                return -ei, -np.asarray(gr)
+            res = batched_lbfgsb(fg, starts, lower, upper, maxit=int(control.get("maxit", 100)))
+            improved = -res["f"] >= vals
+            starts = np.where(improved[:, None], res["x"], starts); vals = np.where(improved, -res["f"], vals)
+        b = int(np.argmax(vals))
+        return {"par": starts[b].copy(), "value": float(vals[b])}
     best = None
     for _ in range(restarts):
         x = lower + rng.random((N, d)) * (upper - lower)
@@ -173,6 +201,51 @@ def max_crit(model: KM, type="UK", lower=None, upper=None, minimization=True, co
         if best is None or value > best[1]:
             best = (np.asarray(par, float), float(value))
     return {"par": best[0], "value": best[1]}
+
+
+def max_EI(model: KM, plugin=None, type="UK", lower=None, upper=None, parinit=None, minimization=True, control=None,
+           seed=None, device=0):
+    """R/max_EI.R:185-219 with the GPU engine in place of rgenoud: the reference evolves a population of
+    ``pop.size`` points for ``max.generations`` generations and hands the best to BFGS; here ``control["n.screen"]``
+    uniform candidates (default 2^17, plus ``parinit``) are scored in one launch, the ``pop.size`` best are polished
+    together by the batched L-BFGS (``control["BFGSmaxit"]`` iterations at most) and the best polished point is
+    returned as list(par, value).  Same arguments and defaults as the reference (R/max_EI.R:195-204)."""
+    from .optim import batched_lbfgsb
+    control = dict(control or {})
+    d = model.d
+    lower = np.zeros(d) if lower is None else np.asarray(lower, float)
+    upper = np.ones(d) if upper is None else np.asarray(upper, float)
+    if plugin is None:
+        plugin = float(np.min(model.y))                                   # R/max_EI.R:187 (not sign-flipped there)
+    Npop = 3 * 2 ** d if d <= 6 else 32 * d
+    pop = int(control.get("pop.size", Npop))
+    maxit = int(control.get("BFGSmaxit", Npop))
+    n_screen = int(control.get("n.screen", 1 << 17))
+    rng = np.random.default_rng(seed)
+    x = lower + rng.random((n_screen, d)) * (upper - lower)
+    if parinit is not None:
+        x[0] = np.clip(np.asarray(parinit, float), lower, upper)
+    k = min(pop, n_screen)
+    if k <= 64:                                                           # the device top-k keeps at most 64
+        idx, val = screen_EI(x, model, plugin=plugin, type=type, minimization=minimization, k=k, device=device)
+        idx = idx[idx >= 0]
+    else:
+        ei = EI(x, model, plugin=plugin, type=type, minimization=minimization, device=device)
+        ei = np.where(np.isnan(ei), -np.inf, ei)
+        idx = np.argpartition(-ei, k - 1)[:k]
+        idx = idx[np.lexsort((idx, -ei[idx]))]                            # by value, first index wins ties
+        val = ei[idx]
+    starts = x[idx]
+
+    def fg(X):
+        ei, gr = _ei_value_and_grad(X, model, plugin, type, minimization, False, device)
+        return -ei, -np.asarray(gr)
+    res = batched_lbfgsb(fg, starts, lower, upper, maxit=maxit)
+    vals = np.where(np.isfinite(res["f"]), -res["f"], -np.inf)
+    b = int(np.argmax(vals))
+    if not vals[b] >= val[0]:
+        return {"par": x[idx[0]].copy(), "value": float(val[0])}
+    return {"par": res["x"][b].copy(), "value": float(vals[b])}
 
 
 def qEI(x, model: KM, plugin=None, type="UK", minimization=True, fastCompute=True, eps=1e-5, envir=None, device=0):
@@ -295,6 +368,20 @@ def max_qEI(model: KM, npoints, lower, upper, crit="exact", minimization=True, o
     lo = np.tile(lower, npoints); up = np.tile(upper, npoints)
     plugin_v = float(np.min(model.y)) if minimization else float(np.max(model.y))
     plugin_g = float(np.min(model.y)) if minimization else -float(np.max(model.y))
+    if oc.get("optimizer", "batched") == "batched":
+        # all nStarts runs advance together: one qEI and one qEI.grad launch per evaluation (optim.py)
+        from .optim import batched_lbfgsb
+        S = start.shape[0]
+
+        def fg(X):
+            xb = X.reshape(S, npoints, d)
+            val = np.atleast_1d(qEI(xb, model, plugin=plugin_v, minimization=minimization, fastCompute=fast, device=device))
+            gr = qEI_grad(xb, model, plugin=plugin_g, minimization=minimization, fastCompute=fast, device=device)
+            return -val, -np.asarray(gr).reshape(S, npoints * d)
+        res = batched_lbfgsb(fg, start.reshape(S, npoints * d), lo, up, maxit=int(oc.get("maxit", 100)))
+        vals = np.where(np.isfinite(res["f"]), -res["f"], -np.inf)
+        b = int(np.argmax(vals))
+        return {"par": res["x"][b].reshape(npoints, d).copy(), "value": float(vals[b])}
     best = None
     for s in range(start.shape[0]):
         f = lambda t: -qEI(t.reshape(npoints, d), model, plugin=plugin_v, minimization=minimization, fastCompute=fast, device=device)

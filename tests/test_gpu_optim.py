@@ -1,0 +1,61 @@
+"""max_crit / max_EI / max_qEI with the batched polish (all restarts in one launch per iteration) against the
+one-restart-at-a-time scipy L-BFGS-B path that mirrors R's optim(); optimisers are compared on the value reached
+(1e-6 relative), not on the path."""
+import numpy as np
+import pytest
+
+from conftest import small_model
+
+pytestmark = pytest.mark.gpu
+
+
+def _projected_grad_norm(g, x, lo, up):
+    g = np.array(g, float)
+    g[(x <= lo) & (g < 0)] = 0.0      # maximisation: at the lower bound only a positive slope can be followed
+    g[(x >= up) & (g > 0)] = 0.0
+    return float(np.max(np.abs(g)))
+
+
+def test_max_crit_batched_matches_sequential_polish(gpu_lib):
+    from diceoptim_b200 import EI, EI_grad, max_crit, synth
+    km = synth.config_model("cfg1_branin2_n20")
+    lo, up = np.zeros(2), np.ones(2)
+    a = max_crit(km, lower=lo, upper=up, control={"restarts": 6, "n.ei": 1000}, seed=5)
+    b = max_crit(km, lower=lo, upper=up, control={"restarts": 6, "n.ei": 1000, "optimizer": "scipy"}, seed=5)
+    assert np.all(a["par"] >= lo) and np.all(a["par"] <= up)
+    assert a["value"] >= b["value"] * (1 - 1e-6)
+    assert abs(EI(a["par"], km)[0] - a["value"]) <= 1e-12 * abs(a["value"])
+    assert _projected_grad_norm(EI_grad(a["par"], km), a["par"], lo, up) <= 1e-4 * a["value"] + 1e-10
+    no_polish = max_crit(km, lower=lo, upper=up, control={"restarts": 6, "n.ei": 1000, "BFGS": False}, seed=5)
+    assert a["value"] >= no_polish["value"]
+    km.release()
+
+
+def test_max_ei_screen_then_polish(gpu_lib):
+    from diceoptim_b200 import EI, max_EI, screen_EI
+    km = small_model("matern5_2", "const", n=60, d=3, seed=21)
+    lo, up = np.zeros(3), np.ones(3)
+    res = max_EI(km, lower=lo, upper=up, control={"n.screen": 20000, "pop.size": 16}, seed=3)
+    x = lo + np.random.default_rng(3).random((20000, 3)) * (up - lo)
+    _, v = screen_EI(x, km)
+    assert res["value"] >= v[0] and np.all(res["par"] >= lo) and np.all(res["par"] <= up)
+    assert abs(EI(res["par"], km)[0] - res["value"]) <= 1e-12 * abs(res["value"])
+    # maximisation of the response (the reference keeps plugin = min(y) there, R/max_EI.R:187)
+    rmax = max_EI(km, lower=lo, upper=up, minimization=False, control={"n.screen": 5000, "pop.size": 8}, seed=4)
+    assert abs(EI(rmax["par"], km, plugin=float(np.min(km.y)), minimization=False)[0] - rmax["value"]) <= 1e-12 * abs(rmax["value"])
+    km.release()
+
+
+def test_max_qei_batched_matches_sequential(gpu_lib):
+    from diceoptim_b200 import max_qEI, qEI
+    km = small_model("matern5_2", "const", n=50, d=2, seed=8)
+    lo, up = np.zeros(2), np.ones(2)
+    par0 = np.random.default_rng(2).random((5, 2, 2))
+    a = max_qEI(km, 2, lo, up, optimcontrol={"parinit": par0, "maxit": 60})
+    b = max_qEI(km, 2, lo, up, optimcontrol={"parinit": par0, "maxit": 60, "optimizer": "scipy"})
+    assert a["par"].shape == (2, 2) and np.all(a["par"] >= lo) and np.all(a["par"] <= up)
+    assert a["value"] >= b["value"] * (1 - 1e-4), (a["value"], b["value"])
+    assert abs(qEI(a["par"], km) - a["value"]) <= 1e-10 * abs(a["value"]) + 1e-15
+    start_vals = qEI(par0, km)
+    assert a["value"] >= np.max(start_vals)
+    km.release()
