@@ -54,6 +54,10 @@ SIGNATURES = {
     "dk_screen_ei": (_I, [_V, _V, _I, _L, _D, _I, _I, _I, _I, _V, _V, _V]),
     "dk_sample_weights": (_I, [_V, _V, _L, _D, _I, _V]),
     "dk_sample_weights_dev": (_I, [_V, _V, _L, _D, _I, _V, _V]),
+    "dk_feas_dev": (_I, [_V, _V, _L, _I, _I, _D, _I, _V, _V]),
+    "dk_check_distance_dev": (_I, [_V, _V, _L, _I, _I, _I, _V, _V]),
+    "dk_check_predict": (_I, [_V, _I, _V, _L, _I, _I, _V]),
+    "dk_feasible_improvement": (_I, [_V, _V, _I, _V, _L, _D, _I, _I, _V, _V, _V]),
     "dk_aei": (_I, [_V, _V, _L, _D, _D, _I, _V]),
     "dk_aei_dev": (_I, [_V, _V, _L, _D, _D, _I, _V, _V]),
     "dk_eqi": (_I, [_V, _V, _L, _D, _D, _D, _I, _V]),

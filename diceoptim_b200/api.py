@@ -462,3 +462,128 @@ def EQI_grad(x, model: KM, new_noise_var=0.0, beta=0.9, q_min=None, type="UK", e
     _lib.check(_lib.load().dk_eqi_grad(h.ptr, _vp(x), x.shape[0], float(q_min), float(new_noise_var), float(ndtri(beta)),
                                        _type_id(type), _vp(g)), "dk_eqi_grad")
     return g[0].copy() if single else g
+
+
+# ---- constrained criteria over several km models (objective + constraints), SURVEY 8(f) rank 3 ----
+_DISTANCES = {"euclidean": 0, "covdist": 1, "covratio": 2}
+
+
+def _handles(models, device):
+    hs = [m.handle(device) for m in models]
+    arr = (C.c_void_p * len(hs))(*[h.ptr for h in hs])
+    return hs, arr
+
+
+def _model_list(model):
+    if isinstance(model, KM):
+        return [model]
+    out = list(model)
+    if not out or not all(isinstance(m, KM) for m in out):
+        raise TypeError("model must be a km model or a list of km models (fastfun objects are not served by the GPU engine)")
+    return out
+
+
+def test_feas_vec(cst, equality=False, tolConstraints=None):
+    """R/test_feas_vec.R:11-36: which rows of the observed constraint matrix are feasible."""
+    cst = np.asarray(cst, float)
+    if cst.ndim == 1:
+        cst = cst.reshape(1, -1)
+    nc = cst.shape[1]
+    eq = np.broadcast_to(np.asarray(equality, bool), (nc,)) if np.ndim(equality) else np.full(nc, bool(equality))
+    if tolConstraints is None:
+        eps = np.zeros(nc); eps[eq] = 0.05
+    else:
+        eps = np.broadcast_to(np.asarray(tolConstraints, float), (nc,))
+    ok = np.ones(cst.shape[0], bool)
+    if eq.any():
+        ok[np.max(cst[:, eq] + eps[eq], axis=1) < 0] = False
+    ok[np.max(cst - eps, axis=1) > 0] = False
+    return ok
+
+
+test_feas_vec.__test__ = False   # a reference function name, not a pytest case
+
+
+def checkPredict(x, model, threshold=1e-4, distance="covdist", type="UK", device=0, return_distance=False):
+    """R/checkPredict.R:18-75 for every row of ``x``: TRUE where the point is too close to the design of one of the
+    models.  ``return_distance=True`` gives the distances themselves (the reference's ``mindist``)."""
+    models = _model_list(model)
+    if distance is None:
+        distance = "covdist"
+    if threshold is None:
+        threshold = 1e-4
+    x = _as_candidates(x, models[0].d)
+    N = x.shape[0]
+    if distance == "none":
+        return np.zeros(N, bool)
+    if distance not in _DISTANCES:
+        raise ValueError(f"distance must be one of euclidean, covdist, covratio, none; got {distance!r}")
+    out = np.empty(N)
+    hs, arr = _handles(models, device)
+    _lib.check(_lib.load().dk_check_predict(arr, len(hs), _vp(x), N, _type_id(type), _DISTANCES[distance], _vp(out)),
+               "dk_check_predict")
+    return out if return_distance else out < threshold
+
+
+def Feas(model: KM, newdata, type="UK", equality=False, threshold=0.0, device=0):
+    """Probability of feasibility, R/crit_EFI.R:231-238 (the reference predicts with "UK" whatever ``type`` says)."""
+    res = predict(model, newdata, type="UK", device=device)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        hi = np.where(res["sd"] > 0, ndtr((threshold - res["mean"]) / res["sd"]), (threshold >= res["mean"]) * 1.0)
+        if not equality:
+            return hi
+        lo = np.where(res["sd"] > 0, ndtr((-threshold - res["mean"]) / res["sd"]), (-threshold >= res["mean"]) * 1.0)
+    return hi - lo
+
+
+def _constraint_setup(model_fun, model_constraint, equality, critcontrol):
+    cst = _model_list(model_constraint)
+    nc = len(cst)
+    cc = dict(critcontrol or {})
+    eqv = np.full(nc, False) if (np.ndim(equality) == 0 and not equality) else np.broadcast_to(np.asarray(equality, bool), (nc,)).copy()
+    observations = np.column_stack([m.y for m in cst])
+    feas = test_feas_vec(observations, equality=eqv if eqv.any() else False, tolConstraints=cc.get("tolConstraints"))
+    best = float(np.min(model_fun.y[feas])) if feas.any() else np.inf
+    if cc.get("tolConstraints") is None:
+        tol = np.zeros(nc); tol[eqv] = 0.05
+    else:
+        tol = np.broadcast_to(np.asarray(cc["tolConstraints"], float), (nc,)).copy()
+    return cst, cc, eqv, tol, best
+
+
+def _feasible_improvement(x, model_fun, cst, plugin, type, kind, eqv, tol, device):
+    x = _as_candidates(x, model_fun.d)
+    N = x.shape[0]
+    out = np.empty(N)
+    hf = model_fun.handle(device)
+    hs, arr = _handles(cst, device)
+    eq = np.ascontiguousarray(eqv, dtype=np.int32)
+    tl = np.ascontiguousarray(tol, dtype=np.float64)
+    _lib.check(_lib.load().dk_feasible_improvement(hf.ptr, arr, len(hs), _vp(x), N, float(plugin), _type_id(type), kind,
+                                                   _vp(eq), _vp(tl), _vp(out)), "dk_feasible_improvement")
+    return out
+
+
+def crit_EFI(x, model_fun: KM, model_constraint, equality=False, critcontrol=None, plugin=None, type="UK", device=0):
+    """Expected feasible improvement, R/crit_EFI.R:125-228, for every row of ``x``: 0 where checkPredict refuses the
+    point, else EI(x; model.fun, plugin = best feasible observation) x prod_i Feas_i(x)."""
+    if not isinstance(model_fun, KM):
+        raise TypeError("model.fun must be a km model (fastfun objectives are not served by the GPU engine)")
+    cst, cc, eqv, tol, best = _constraint_setup(model_fun, model_constraint, equality, critcontrol)
+    if plugin is None:
+        plugin = best
+    single = np.asarray(x).ndim <= 1
+    out = _feasible_improvement(x, model_fun, cst, plugin, type, 0, eqv, tol, device)
+    refuse = checkPredict(x, cst + [model_fun], threshold=cc.get("threshold"), distance=cc.get("distance"), type=type,
+                          device=device)
+    out[refuse] = 0.0
+    return float(out[0]) if single else out
+
+
+def prob_of_feasible_improvement(integration_points, model_fun: KM, model_constraint, equality=False, critcontrol=None,
+                                 type="UK", device=0):
+    """R/prob.of.feasible.improvement.R:1-81: pnorm((obj.min - mean) / sd) x prod_i Feas_i over the integration
+    points; inequality thresholds are 0, equality tolerances default to 0.05."""
+    cst, cc, eqv, tol, best = _constraint_setup(model_fun, model_constraint, equality, critcontrol)
+    thr = np.where(eqv, tol, 0.0)
+    return _feasible_improvement(integration_points, model_fun, cst, best, type, 1, eqv, thr, device)

@@ -81,13 +81,16 @@ struct DevModel {
   double theta[DK_MAX_D];
 };
 
-enum Mode { MODE_PREDICT = 0, MODE_EI = 1, MODE_QUANTILE = 2, MODE_EI_WEIGHT = 3, MODE_AEI = 4, MODE_EQI = 5 };
+enum Mode { MODE_PREDICT = 0, MODE_EI = 1, MODE_QUANTILE = 2, MODE_EI_WEIGHT = 3, MODE_AEI = 4, MODE_EQI = 5,
+            MODE_FEAS = 6, MODE_COVRATIO = 7 };
+enum Combine { COMBINE_STORE = 0, COMBINE_MUL = 1, COMBINE_MIN = 2 };
 
 struct CritParams {
   int mode, type, minimization, proxy;
   double plugin, qnorm_beta;
   double tau2;  // new.noise.var (AEI, EQI)
   double sd2;   // covariance@sd2 for the negligible-sd guards of AEI / EQI
+  int combine = COMBINE_STORE;  // how the criterion meets what out[] already holds (products / minima over several models)
 };
 
 // ---------------------------------------------------------------------------------------
@@ -143,6 +146,8 @@ struct dk_model {
   double* d_akg_scratch = nullptr;
   double* d_Kinv = nullptr;        // K^-1, n x n (AKG.grad only, built lazily on the device)
   double* d_akg_gscratch = nullptr; // per-CTA blocks of the AKG.grad contraction passes
+  double* d_delta = nullptr;        // n: noise.var or zeros (checkPredict covdist when AKG never ran)
+  double* d_knyy[2] = {nullptr, nullptr};  // sd(X_j)^2 per type (SK, UK), checkPredict covdist
   long long launches = 0;        // kernels launched through this handle
   int timing = 0;                // bracket the solve kernel with events
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;

@@ -417,6 +417,16 @@ __device__ __forceinline__ double crit_value(const CritParams& P, double mean, d
     const double xcr = (P.plugin - mq) / sq;
     return sq * (xcr * normcdf(xcr) + dnorm_std(xcr));
   }
+  if (P.mode == MODE_FEAS) {
+    // Feas (R/crit_EFI.R:231-238): pnorm(q = threshold, mean, sd), minus pnorm(-threshold, ...) for an equality
+    // constraint (P.proxy carries the flag).  sd = 0 follows R's pnorm: 1 when q >= mean, else 0.
+    const double thr = P.plugin;
+    const double hi = (sd > 0.0) ? normcdf((thr - mean) / sd) : ((thr >= mean) ? 1.0 : 0.0);
+    if (!P.proxy) return hi;
+    const double lo = (sd > 0.0) ? normcdf((-thr - mean) / sd) : ((-thr >= mean) ? 1.0 : 0.0);
+    return hi - lo;
+  }
+  if (P.mode == MODE_COVRATIO) return sd / sqrt(P.sd2);  // checkPredict "covratio" (R/checkPredict.R:43-48)
   const double km = P.minimization ? mean : -mean;
   const double diff = P.plugin - km;
   if (P.proxy) return diff;
@@ -431,7 +441,12 @@ __device__ __noinline__ void crit_epilogue(const DevModel& M, const CritParams& 
   cand_predict(M, P.type, panel, xs, s2acc, c, mean, sd, u);
   if (out_mean) out_mean[gidx] = mean;
   if (out_sd) out_sd[gidx] = sd;
-  if (out_main) out_main[gidx] = crit_value(P, mean, sd);
+  if (out_main) {
+    double v = crit_value(P, mean, sd);
+    if (P.combine == COMBINE_MUL) v *= out_main[gidx];
+    else if (P.combine == COMBINE_MIN) v = fmin(v, out_main[gidx]);  // pmin(mindist, .) of R/checkPredict.R:47
+    out_main[gidx] = v;
+  }
 }
 
 // ---------------------------------------------------------------------------------------

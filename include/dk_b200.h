@@ -202,6 +202,31 @@ int dk_mvn_cdf(int q, int64_t B, const double* h, const double* S, double* out);
 int dk_ei_dev_noalloc(dk_model* m, const double* d_x, int64_t N, double plugin, int type, int minimization,
                       int proxy, double* d_ei, double* d_mean, double* d_sd, void* stream);
 
+/* ---- Constrained criteria over several km models on one device (objective + constraints) ----
+ * dk_feas_dev replaces Feas, /root/reference/R/crit_EFI.R:231-238: pnorm(threshold, mean, sd) of every row, minus
+ * pnorm(-threshold, mean, sd) when `equality`.  multiply != 0 multiplies the result into d_out instead of storing it,
+ * so a product over constraint models needs no pass of its own. */
+int dk_feas_dev(dk_model* m, const double* d_x, int64_t N, int type, int equality, double threshold, int multiply,
+                double* d_out, void* stream);
+
+/* Distances of checkPredict, /root/reference/R/checkPredict.R:35-66. */
+enum { DK_DIST_EUCLIDEAN = 0, DK_DIST_COVDIST = 1, DK_DIST_COVRATIO = 2 };
+/* One model's distance for every row; running_min != 0 keeps pmin(d_out, distance) (lists of models, :47, :64). */
+int dk_check_distance_dev(dk_model* m, const double* d_x, int64_t N, int type, int distance, int running_min,
+                          double* d_out, void* stream);
+/* checkPredict(x, model = list(...), distance, type) for every row of x (host buffers): out_mindist[i] is the `mindist`
+ * the reference compares with `threshold` (:74); "euclidean" looks at models[0] only, as the reference does. */
+int dk_check_predict(dk_model* const* models, int n_models, const double* x, int64_t N, int type, int distance,
+                     double* out_mindist);
+
+/* crit_EFI's product (kind = DK_FI_EXPECTED; /root/reference/R/crit_EFI.R:158-191, without the checkPredict gate, which
+ * is dk_check_predict) and prob.of.feasible.improvement (kind = DK_FI_PROBABILITY;
+ * /root/reference/R/prob.of.feasible.improvement.R:39-79) for every row of x: objective model `fun`, n_cst constraint
+ * models, plugin = current feasible best (+Inf: none known), equality[n_cst] / tol[n_cst] may be NULL (all FALSE / 0). */
+enum { DK_FI_EXPECTED = 0, DK_FI_PROBABILITY = 1 };
+int dk_feasible_improvement(dk_model* fun, dk_model* const* cst, int n_cst, const double* x, int64_t N, double plugin,
+                            int type, int kind, const int* equality, const double* tol, double* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -661,3 +661,115 @@ def EQI_grad(x, model, new_noise_var=0.0, beta=0.9, q_min=None, type="UK", envir
     sq2_grad = (sk ** 2) * (2 * t2 + sk ** 2) / (t2 + sk ** 2) ** 2 * sk2_grad
     sq_grad = sq2_grad / (2.0 * sq)
     return -prob * mq_grad + dens * sq_grad
+
+
+# ---------------------------------------------------------------------------------------
+# Constrained criteria: checkPredict, test_feas_vec, Feas, crit_EFI, prob.of.feasible.improvement
+# ---------------------------------------------------------------------------------------
+def check_predict_distance(x, models, distance="covdist", type="UK"):
+    """`mindist` of R/checkPredict.R:35-66, one value per row of x (the reference is written for one row; the
+    euclidean branch recycles x against the design, so it is restated row by row)."""
+    x = np.atleast_2d(np.asarray(x, float))
+    if distance == "euclidean":
+        X = models[0].X
+        return np.array([np.min(np.sqrt(np.sum((X - xi) ** 2, axis=1))) for xi in x])          # :35-38
+    mindist = np.full(x.shape[0], np.inf)
+    for m in models:
+        sd2 = m.covariance.sd2
+        if distance == "covratio":
+            mindist = np.minimum(mindist, dk.predict_km(m, x, type, light_return=True)["sd"] / np.sqrt(sd2))  # :45-47
+            continue
+        kn_xx = dk.predict_km(m, x, type)["sd"] ** 2                                               # :54
+        kn_yy = dk.predict_km(m, m.X, type)["sd"] ** 2                                             # :55
+        kxy = dk.cov_mat1_mat2(m.covariance, x, m.X)                                               # :56
+        kyy = dk.cov_matrix(m.covariance, m.X)                                                     # :57
+        Kinv = np.linalg.inv(m.T.T @ m.T)                                                          # chol2inv(T)
+        kn_xy = kxy - kxy @ Kinv @ kyy                                                             # :58
+        val = np.sqrt(np.maximum(0.0, kn_xx - 2.0 * np.max(kn_xy - kn_yy[None, :], axis=1)) / sd2)  # :61-62
+        mindist = np.minimum(mindist, val)
+    return mindist
+
+
+def test_feas_vec(cst, equality=False, tolConstraints=None):
+    """R/test_feas_vec.R:11-36."""
+    cst = np.asarray(cst, float)
+    if cst.ndim == 1:
+        cst = cst.reshape(1, -1)
+    nc = cst.shape[1]
+    eq = np.broadcast_to(np.asarray(equality, bool), (nc,)) if np.ndim(equality) else np.full(nc, bool(equality))
+    if tolConstraints is None:
+        eps = np.zeros(nc); eps[eq] = 0.05
+    else:
+        eps = np.broadcast_to(np.asarray(tolConstraints, float), (nc,))
+    ok = np.ones(cst.shape[0], bool)
+    if eq.any():
+        ok[np.max(cst[:, eq] + eps[eq], axis=1) < 0] = False
+    ok[np.max(cst - eps, axis=1) > 0] = False
+    return ok
+
+
+test_feas_vec.__test__ = False
+
+
+def Feas(model, newdata, equality=False, threshold=0.0):
+    """R/crit_EFI.R:231-238 (predicts with "UK")."""
+    p = dk.predict_km(model, newdata, "UK", light_return=True)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        hi = np.where(p["sd"] > 0, pnorm((threshold - p["mean"]) / p["sd"]), (threshold >= p["mean"]) * 1.0)
+        if not equality:
+            return hi
+        lo = np.where(p["sd"] > 0, pnorm((-threshold - p["mean"]) / p["sd"]), (-threshold >= p["mean"]) * 1.0)
+    return hi - lo
+
+
+def _eq_tol(nc, equality, cc):
+    eqv = np.full(nc, False) if (np.ndim(equality) == 0 and not equality) else np.broadcast_to(np.asarray(equality, bool), (nc,))
+    if cc.get("tolConstraints") is None:
+        tol = np.zeros(nc); tol[eqv] = 0.05
+    else:
+        tol = np.broadcast_to(np.asarray(cc["tolConstraints"], float), (nc,))
+    return eqv, tol
+
+
+def crit_EFI(x, model_fun, model_constraint, equality=False, critcontrol=None, plugin=None, type="UK"):
+    """R/crit_EFI.R:125-228 for ONE point x."""
+    cc = dict(critcontrol or {})
+    cst = list(model_constraint)
+    nc = len(cst)
+    observations = np.column_stack([m.y for m in cst])
+    if plugin is None:
+        feas = test_feas_vec(observations, equality=equality, tolConstraints=cc.get("tolConstraints"))
+        plugin = float(np.min(model_fun.y[feas])) if feas.any() else np.inf
+    d = check_predict_distance(x, cst + [model_fun], distance=cc.get("distance") or "covdist", type=type)
+    if d[0] < (cc.get("threshold") or 1e-4):
+        return 0.0
+    Ei = 1.0 if plugin == np.inf else float(EI(x, model_fun, plugin=plugin, type=type)[0])
+    eqv, tol = _eq_tol(nc, equality, cc)
+    Pf = 1.0
+    for i in range(nc):
+        Pf *= float(Feas(cst[i], np.atleast_2d(x), equality=bool(eqv[i]), threshold=float(tol[i]))[0])
+    return Pf * Ei
+
+
+def prob_of_feasible_improvement(integration_points, model_fun, model_constraint, equality=False, critcontrol=None,
+                                 type="UK"):
+    """R/prob.of.feasible.improvement.R:1-81."""
+    cc = dict(critcontrol or {})
+    cst = list(model_constraint)
+    nc = len(cst)
+    P = np.atleast_2d(np.asarray(integration_points, float))
+    pc = [dk.predict_km(m, P, type) for m in cst]
+    po = dk.predict_km(model_fun, P, type)
+    eqv, tol = _eq_tol(nc, equality, cc)
+    observations = np.column_stack([m.y for m in cst])
+    feas = test_feas_vec(observations, equality=equality, tolConstraints=cc.get("tolConstraints"))
+    obj_min = float(np.min(model_fun.y[feas])) if feas.any() else np.inf
+    with np.errstate(divide="ignore", invalid="ignore"):
+        p_obj = pnorm((obj_min - po["mean"]) / po["sd"]) if obj_min != np.inf else np.ones(P.shape[0])
+        pf = np.ones(P.shape[0])
+        for i in range(nc):
+            if eqv[i]:
+                pf = pf * (pnorm((tol[i] - pc[i]["mean"]) / pc[i]["sd"]) - pnorm((-tol[i] - pc[i]["mean"]) / pc[i]["sd"]))
+            else:
+                pf = pf * pnorm((0.0 - pc[i]["mean"]) / pc[i]["sd"])
+    return p_obj * pf
