@@ -71,3 +71,32 @@ screen_EI <- function(x, model, plugin = NULL, type = "UK", minimization = TRUE,
   if (is.null(plugin)) plugin <- if (minimization) min(model@y) else -max(model@y)
   .Call("dkR_screen_ei", dk_handle(model), .as_rows(x, model@d), plugin, .type_id(type), minimization, proxy, as.integer(k))
 }
+## checkPredict (R/checkPredict.R:18-75), vectorised over the rows of x; fastfun members of `model` are skipped as there
+checkPredict <- function(x, model, threshold = 1e-4, distance = "covdist", type = "UK") {
+  if (is.null(distance)) distance <- "covdist"
+  if (is.null(threshold)) threshold <- 1e-4
+  kms <- Filter(function(m) is(m, "km"), model)
+  x <- .as_rows(x, kms[[1]]@d)
+  if (distance == "none") return(rep(FALSE, nrow(x)))
+  id <- match(distance, c("euclidean", "covdist", "covratio")) - 1L
+  .Call("dkR_check_predict", lapply(kms, dk_handle), x, .type_id(type), id) < threshold
+}
+## crit_EFI (R/crit_EFI.R:125-228) for every row of x: one upload of x, EI and the Feas factors multiplied on the device
+crit_EFI <- function(x, model.fun, model.constraint, equality = FALSE, critcontrol = NULL, plugin = NULL, type = "UK") {
+  if (!is(model.constraint, "list")) model.constraint <- list(model.constraint)
+  n.cst <- length(model.constraint)
+  if (is.null(plugin)) {
+    observations <- sapply(model.constraint, function(m) m@y)
+    feasibility <- test_feas_vec(cst = observations, equality = equality, tolConstraints = critcontrol$tolConstraints)
+    plugin <- if (any(feasibility)) min(model.fun@y[feasibility]) else Inf
+  }
+  equalityvec <- if (length(equality) == 1 && equality == FALSE) rep(FALSE, n.cst) else equality
+  tolvec <- critcontrol$tolConstraints
+  if (is.null(tolvec)) { tolvec <- rep(0, n.cst); tolvec[equalityvec] <- 0.05 }
+  x <- .as_rows(x, model.fun@d)
+  out <- .Call("dkR_feasible_improvement", dk_handle(model.fun), lapply(model.constraint, dk_handle), x, plugin,
+               .type_id(type), 0L, as.logical(equalityvec), as.double(tolvec))
+  out[checkPredict(x, c(model.constraint, model.fun), type = type, distance = critcontrol$distance,
+                   threshold = critcontrol$threshold)] <- 0
+  out
+}

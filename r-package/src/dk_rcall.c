@@ -145,4 +145,37 @@ SEXP dkR_sample_weights(SEXP h, SEXP x, SEXP T, SEXP minimization) {
   if (rc) Rf_error("dk_sample_weights: %s", dk_last_error());
   return w;
 }
+
+/* handles: list of external pointers (one per km model, all on one device) */
+static dk_model** handles_of(SEXP lst, int* n) {
+  *n = (int)Rf_xlength(lst);
+  dk_model** hs = (dk_model**)R_alloc(*n > 0 ? *n : 1, sizeof(dk_model*));
+  for (int i = 0; i < *n; i++) hs[i] = handle_of(VECTOR_ELT(lst, i));
+  return hs;
+}
+
+/* checkPredict's mindist for every row of x (R/checkPredict.R:35-66); distance: 0 euclidean, 1 covdist, 2 covratio */
+SEXP dkR_check_predict(SEXP handles, SEXP x, SEXP type, SEXP distance) {
+  int n = 0;
+  dk_model** hs = handles_of(handles, &n);
+  R_xlen_t N = Rf_nrows(x);
+  SEXP out = PROTECT(Rf_allocVector(REALSXP, N));
+  int rc = dk_check_predict(hs, n, REAL(x), (int64_t)N, Rf_asInteger(type), Rf_asInteger(distance), REAL(out));
+  UNPROTECT(1);
+  if (rc) Rf_error("dk_check_predict: %s", dk_last_error());
+  return out;
+}
+
+/* kind 0: EI x prod Feas (R/crit_EFI.R:158-191); kind 1: prob.of.feasible.improvement */
+SEXP dkR_feasible_improvement(SEXP hfun, SEXP hcst, SEXP x, SEXP plugin, SEXP type, SEXP kind, SEXP equality, SEXP tol) {
+  int n = 0;
+  dk_model** hs = handles_of(hcst, &n);
+  R_xlen_t N = Rf_nrows(x);
+  SEXP out = PROTECT(Rf_allocVector(REALSXP, N));
+  int rc = dk_feasible_improvement(handle_of(hfun), hs, n, REAL(x), (int64_t)N, Rf_asReal(plugin), Rf_asInteger(type),
+                                   Rf_asInteger(kind), LOGICAL(equality), opt_real(tol), REAL(out));
+  UNPROTECT(1);
+  if (rc) Rf_error("dk_feasible_improvement: %s", dk_last_error());
+  return out;
+}
 #endif /* DK_HAVE_R */

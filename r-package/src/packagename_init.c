@@ -16,6 +16,8 @@ extern SEXP dkR_akg(SEXP, SEXP, SEXP, SEXP);
 extern SEXP dkR_qei(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
 extern SEXP dkR_screen_ei(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
 extern SEXP dkR_sample_weights(SEXP, SEXP, SEXP, SEXP);
+extern SEXP dkR_check_predict(SEXP, SEXP, SEXP, SEXP);
+extern SEXP dkR_feasible_improvement(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
 
 static const R_CMethodDef CEntries[] = {{"davies", (DL_FUNC)&davies, 13}, {NULL, NULL, 0}};
 static const R_CallMethodDef CallEntries[] = {
@@ -23,6 +25,8 @@ static const R_CallMethodDef CallEntries[] = {
     {"dkR_ei_grad", (DL_FUNC)&dkR_ei_grad, 6},           {"dkR_quantile", (DL_FUNC)&dkR_quantile, 5},
     {"dkR_akg", (DL_FUNC)&dkR_akg, 4},                   {"dkR_qei", (DL_FUNC)&dkR_qei, 7},
     {"dkR_screen_ei", (DL_FUNC)&dkR_screen_ei, 7},       {"dkR_sample_weights", (DL_FUNC)&dkR_sample_weights, 4},
+    {"dkR_check_predict", (DL_FUNC)&dkR_check_predict, 4},
+    {"dkR_feasible_improvement", (DL_FUNC)&dkR_feasible_improvement, 8},
     {NULL, NULL, 0}};
 
 void R_init_DiceOptim(DllInfo* dll) {

@@ -12,7 +12,7 @@ extern double R_NaReal;
 #define NA_REAL R_NaReal
 #define REALSXP 14
 #define VECSXP 19
-double* REAL(SEXP); int* INTEGER(SEXP); const char* CHAR(SEXP);
+double* REAL(SEXP); int* INTEGER(SEXP); int* LOGICAL(SEXP); const char* CHAR(SEXP);
 SEXP STRING_ELT(SEXP, R_xlen_t); SEXP VECTOR_ELT(SEXP, R_xlen_t); SEXP SET_VECTOR_ELT(SEXP, R_xlen_t, SEXP);
 SEXP Rf_getAttrib(SEXP, SEXP); R_xlen_t Rf_xlength(SEXP); int Rf_nrows(SEXP); int Rf_ncols(SEXP);
 int Rf_asInteger(SEXP); int Rf_asLogical(SEXP); double Rf_asReal(SEXP);
