@@ -351,8 +351,12 @@ def max_qEI(model: KM, npoints, lower, upper, crit="exact", minimization=True, o
     first.  crit = "CL" (constant liar) and method = "genoud" need DiceKriging's model update / rgenoud and stay
     outside the engine."""
     from scipy.optimize import minimize
+    if crit == "CL":
+        return _max_qEI_CL(model, npoints, (optimcontrol or {}).get("L"), lower, upper,
+                           parinit=(optimcontrol or {}).get("parinit"), minimization=minimization,
+                           control=optimcontrol, seed=seed, device=device)
     if crit != "exact":
-        raise NotImplementedError("max_qEI(crit='CL') relies on DiceKriging model updates, which stay in R")
+        raise ValueError(f"'{crit}' is unknown.")
     oc = dict(optimcontrol or {})
     if oc.get("method", "BFGS") != "BFGS":
         raise NotImplementedError("only optimcontrol$method = 'BFGS' is served")
@@ -587,3 +591,46 @@ def prob_of_feasible_improvement(integration_points, model_fun: KM, model_constr
     cst, cc, eqv, tol, best = _constraint_setup(model_fun, model_constraint, equality, critcontrol)
     thr = np.where(eqv, tol, 0.0)
     return _feasible_improvement(integration_points, model_fun, cst, best, type, 1, eqv, thr, device)
+
+
+def _max_qEI_CL(model: KM, npoints, L, lower, upper, parinit=None, minimization=True, control=None, seed=None, device=0):
+    """max_qEI.CL, R/max_qEI.R:283-318: npoints rounds of max_EI, after each of which the maximiser joins the design
+    with a "lie" as response (L = NULL: min(y) or max(y); "min"; "max"; "mean" = kriging believer; or a number) and the
+    model's T, z, M are refreshed with covariance and trend coefficients kept.  The refresh is the n^2 append of
+    ``update_km`` instead of computeAuxVariables' full Cholesky."""
+    from .update import update_km
+    n1 = model.n
+    KB = False
+    if L is None:
+        liar = float(np.min(model.y)) if minimization else float(np.max(model.y))
+    elif isinstance(L, str):
+        if L == "max":
+            liar = float(np.max(model.y))
+        elif L == "min":
+            liar = float(np.min(model.y))
+        elif L == "mean":
+            KB = True
+        else:
+            raise ValueError('control$L must be NULL, "max", "min", "mean" or a scalar specifying the plugin.')
+    else:
+        liar = float(L)
+    ctrl = {k: v for k, v in dict(control or {}).items() if k in ("pop.size", "BFGSmaxit", "n.screen")}
+    parinit = None if parinit is None else np.atleast_2d(np.asarray(parinit, float))     # d x npoints as in R
+    rng = np.random.default_rng(seed)
+    cur = model
+    created = []
+    for s in range(npoints):
+        start = parinit[:, s] if (parinit is not None and s < parinit.shape[1]) else None
+        o = max_EI(cur, lower=lower, upper=upper, parinit=start, minimization=minimization, control=ctrl,
+                   seed=int(rng.integers(1 << 31)), device=device)
+        if KB:
+            liar = float(predict(cur, o["par"], device=device)["mean"][0])
+        nxt = update_km(cur, o["par"], liar, new_noise_var=0.0)
+        if cur is not model:
+            cur.release()
+        cur = nxt
+        created.append(nxt)
+    par, value = cur.X[n1:n1 + npoints].copy(), cur.y[n1:n1 + npoints].reshape(-1, 1).copy()
+    if cur is not model:
+        cur.release()
+    return {"par": par, "value": value}

@@ -59,3 +59,32 @@ def test_max_qei_batched_matches_sequential(gpu_lib):
     start_vals = qEI(par0, km)
     assert a["value"] >= np.max(start_vals)
     km.release()
+
+
+def test_max_qei_constant_liar(gpu_lib):
+    """max_qEI(crit = "CL"), R/max_qEI.R:283-318: every round's point maximises EI of the model that already holds the
+    earlier points with the lie as response; values are the lies."""
+    from diceoptim_b200 import EI, max_EI, max_qEI
+    from diceoptim_b200.update import update_km
+    km = small_model("matern5_2", "const", n=40, d=2, seed=6)
+    lo, up = np.zeros(2), np.ones(2)
+    ctl = {"n.screen": 20000, "pop.size": 12}
+    res = max_qEI(km, 3, lo, up, crit="CL", optimcontrol=ctl, seed=11)
+    assert res["par"].shape == (3, 2) and res["value"].shape == (3, 1)
+    assert np.all(res["value"] == np.min(km.y))
+    assert np.all(res["par"] >= lo) and np.all(res["par"] <= up)
+    cur = km
+    for s in range(3):
+        best = max_EI(cur, lower=lo, upper=up, control={"n.screen": 50000, "pop.size": 24}, seed=100 + s)
+        got = EI(res["par"][s], cur, plugin=float(np.min(cur.y)))[0]
+        assert got >= best["value"] * (1 - 1e-3), (s, got, best["value"])      # same optimum from an independent run
+        nxt = update_km(cur, res["par"][s], float(np.min(km.y)))
+        if cur is not km:
+            cur.release()
+        cur = nxt
+    cur.release()
+    kb = max_qEI(km, 2, lo, up, crit="CL", optimcontrol={**ctl, "L": "mean"}, seed=3)
+    assert np.all(np.isfinite(kb["value"])) and not np.all(kb["value"] == np.min(km.y))
+    with pytest.raises(ValueError):
+        max_qEI(km, 2, lo, up, crit="CL", optimcontrol={"L": "median"})
+    km.release()
