@@ -58,6 +58,7 @@ SIGNATURES = {
     "dk_check_distance_dev": (_I, [_V, _V, _L, _I, _I, _I, _V, _V]),
     "dk_check_predict": (_I, [_V, _I, _V, _L, _I, _I, _V]),
     "dk_feasible_improvement": (_I, [_V, _V, _I, _V, _L, _D, _I, _I, _V, _V, _V]),
+    "dk_crit_sur_cst": (_I, [_V, _V, _I, _V, _L, _V, _L, _V, _D, _I, _V, _V, _V]),
     "dk_aei": (_I, [_V, _V, _L, _D, _D, _I, _V]),
     "dk_aei_dev": (_I, [_V, _V, _L, _D, _D, _I, _V, _V]),
     "dk_eqi": (_I, [_V, _V, _L, _D, _D, _D, _I, _V]),

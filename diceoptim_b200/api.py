@@ -634,3 +634,40 @@ def _max_qEI_CL(model: KM, npoints, L, lower, upper, parinit=None, minimization=
     if cur is not model:
         cur.release()
     return {"par": par, "value": value}
+
+
+def crit_SUR_cst(x, model_fun: KM, model_constraint, equality=False, critcontrol=None, type="UK", device=0):
+    """Stepwise uncertainty reduction with constraints, R/crit_SUR_cst.R:120-378, for every row of ``x``.
+    ``critcontrol["integration.points"]`` (M x d) is required (integration_design_cst stays on the host side of the
+    caller); ``integration.weights`` defaults to 1 / M each.  0 where checkPredict refuses the point; NaN when there are
+    more than three constraints (the reference warns and returns NA)."""
+    if not isinstance(model_fun, KM):
+        raise TypeError("model.fun must be a km model (fastfun objectives are not served by the GPU engine)")
+    cst, cc, eqv, tol, best = _constraint_setup(model_fun, model_constraint, equality, critcontrol)
+    single = np.asarray(x).ndim <= 1
+    x = _as_candidates(x, model_fun.d)
+    N = x.shape[0]
+    if len(cst) > 3:
+        import warnings
+        warnings.warn("crit_SUR_cst does not take more than 3 constraints")
+        return float("nan") if single else np.full(N, np.nan)
+    if cc.get("integration.points") is None:
+        raise ValueError("critcontrol['integration.points'] is required")
+    P = np.asfortranarray(np.atleast_2d(np.asarray(cc["integration.points"], float)))
+    if P.shape[1] != model_fun.d:
+        raise ValueError("integration.points does not have the right size")
+    w = cc.get("integration.weights")
+    w = None if w is None else np.ascontiguousarray(w, dtype=np.float64)
+    if w is not None and w.shape != (P.shape[0],):
+        raise ValueError("integration.weights must have one entry per integration point")
+    out = np.empty(N)
+    hf = model_fun.handle(device)
+    hs, arr = _handles(cst, device)
+    eq = np.ascontiguousarray(eqv, dtype=np.int32)
+    tl = np.ascontiguousarray(tol, dtype=np.float64)
+    _lib.check(_lib.load().dk_crit_sur_cst(hf.ptr, arr, len(hs), _vp(x), N, _vp(P), P.shape[0], _vp(w), float(best),
+                                           _type_id(type), _vp(eq), _vp(tl), _vp(out)), "dk_crit_sur_cst")
+    refuse = checkPredict(x, cst + [model_fun], threshold=cc.get("threshold"), distance=cc.get("distance"), type=type,
+                          device=device)
+    out[refuse] = 0.0
+    return float(out[0]) if single else out

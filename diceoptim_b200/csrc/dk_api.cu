@@ -12,6 +12,7 @@
 #include "dk_akg.cuh"
 #include "dk_reduce.cuh"
 #include "dk_check.cuh"
+#include "dk_sur.cuh"
 
 namespace dk {
 
@@ -1336,4 +1337,106 @@ extern "C" int dk_feasible_improvement(dk_model* fun, dk_model* const* cst, int 
   }
   if ((rc = h.fetch(out, h.d_out, N))) return rc;
   return h.finish();
+}
+
+// ------------------------------------------------------------------------------------------
+// crit_SUR_cst (R/crit_SUR_cst.R:120-378) for every row of x, with precomputeUpdateData and computeQuickKrigcov2
+// (SURVEY 8(f) rank 4).  Stateless: the integration-point pass (two solves per model over M points) is repeated per call;
+// it costs M / N of the candidate pass.
+// ------------------------------------------------------------------------------------------
+namespace {
+bool g_sur_attr_done[64] = {};
+struct SurModelBufs {
+  DevBuf mn, sn, first, W, mk, sk, U, Cnew, kn;
+};
+}  // namespace
+
+extern "C" int dk_crit_sur_cst(dk_model* fun, dk_model* const* cst, int n_cst, const double* x, int64_t N,
+                               const double* integration_points, int64_t Mi, const double* integration_weights,
+                               double obj_min, int type, const int* equality, const double* tol, double* out) {
+  if (!fun) return fail(DK_ERR_ARG, "objective model is NULL");
+  if (n_cst < 1 || n_cst > 3 || !cst) return fail(DK_ERR_ARG, "crit_SUR_cst takes 1 to 3 constraint models, got %d", n_cst);
+  std::vector<dk_model*> all;
+  all.push_back(fun);
+  for (int i = 0; i < n_cst; i++) all.push_back(cst[i]);
+  int rc = check_models(all.data(), (int)all.size(), "dk_crit_sur_cst");
+  if (rc) return rc;
+  if ((rc = check_call(fun, x, N))) return rc;
+  if (!integration_points || Mi < 1) return fail(DK_ERR_ARG, "integration points missing");
+  if (!out) return fail(DK_ERR_ARG, "out is NULL");
+  if (N == 0) return DK_OK;
+  DeviceGuard guard(fun->device);
+  const int d = fun->d, nm = (int)all.size();
+  cudaStream_t st = fun->stream;
+  if (fun->device < 64 && !g_sur_attr_done[fun->device]) {
+    DK_CUDA_TRY(cudaFuncSetAttribute(k_sur_points, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
+    DK_CUDA_TRY(cudaFuncSetAttribute(k_sur_cand, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
+    g_sur_attr_done[fun->device] = true;
+  }
+  for (dk_model* m : all)
+    if ((rc = ensure_bwd(m))) return rc;
+  // candidate chunk: all per-candidate buffers of all models within ~1.5 GB
+  size_t per_cand = 0;
+  for (dk_model* m : all) per_cand += ((size_t)m->n + (size_t)Mi + m->p + 2) * 8;
+  int64_t NC = (int64_t)std::max<size_t>(64, (size_t)1500000000 / per_cand);
+  NC = std::min<int64_t>(N, NC & ~(int64_t)63);
+  if (NC < 1) NC = std::min<int64_t>(N, 64);
+
+  DevBuf d_pts, d_w, d_x, d_out;
+  std::vector<SurModelBufs> B(nm);
+#define SUR_ALLOC(buf, count)                                                                              \
+  if ((buf).alloc(count) != cudaSuccess) { cudaGetLastError(); return fail(DK_ERR_NOMEM, "cudaMalloc of %zu doubles failed", (size_t)(count)); }
+  SUR_ALLOC(d_pts, (size_t)Mi * d);
+  SUR_ALLOC(d_w, (size_t)Mi);
+  SUR_ALLOC(d_x, (size_t)NC * d);
+  SUR_ALLOC(d_out, (size_t)NC);
+  for (int k = 0; k < nm; k++) {
+    dk_model* m = all[k];
+    SUR_ALLOC(B[k].mn, (size_t)Mi); SUR_ALLOC(B[k].sn, (size_t)Mi); SUR_ALLOC(B[k].first, (size_t)Mi * m->p);
+    SUR_ALLOC(B[k].W, (size_t)m->n * Mi);
+    SUR_ALLOC(B[k].mk, (size_t)NC); SUR_ALLOC(B[k].sk, (size_t)NC); SUR_ALLOC(B[k].U, (size_t)NC * m->p);
+    SUR_ALLOC(B[k].Cnew, (size_t)m->n * NC); SUR_ALLOC(B[k].kn, (size_t)NC * Mi);
+  }
+#undef SUR_ALLOC
+  std::vector<double> hw((size_t)Mi, 1.0 / (double)Mi);   // rep(1 / n.integration.points, n.integration.points) (:150)
+  if (integration_weights) std::copy(integration_weights, integration_weights + Mi, hw.begin());
+  DK_CUDA_TRY(cudaMemcpyAsync(d_pts.p, integration_points, (size_t)Mi * d * 8, cudaMemcpyHostToDevice, st));
+  DK_CUDA_TRY(cudaMemcpyAsync(d_w.p, hw.data(), (size_t)Mi * 8, cudaMemcpyHostToDevice, st));
+  const int64_t ptiles = (Mi + BN - 1) / BN;
+  for (int k = 0; k < nm; k++) {
+    dk_model* m = all[k];
+    const int grid = (int)std::min<int64_t>(ptiles, m->grid);
+    k_sur_points<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, type, d_pts.p, Mi, ptiles, m->d_vscratch, m->d_wscratch,
+                                                        m->scratch_doubles_per_cta, B[k].mn.p, B[k].sn.p, B[k].first.p, B[k].W.p);
+    m->launches++;
+  }
+  DK_CUDA_TRY(cudaGetLastError());
+  std::vector<double> hx((size_t)NC * d);
+  for (int64_t c0 = 0; c0 < N; c0 += NC) {
+    const int64_t nc = std::min<int64_t>(NC, N - c0);
+    for (int k = 0; k < d; k++) std::copy(x + c0 + (int64_t)k * N, x + c0 + (int64_t)k * N + nc, hx.begin() + (size_t)k * nc);
+    DK_CUDA_TRY(cudaMemcpyAsync(d_x.p, hx.data(), (size_t)nc * d * 8, cudaMemcpyHostToDevice, st));
+    const int64_t ctiles = (nc + BN - 1) / BN;
+    SurParams S{};
+    S.nc = n_cst; S.any_eq = 0; S.obj_min = obj_min; S.w = d_w.p; S.Mi = Mi;
+    for (int i = 0; i < n_cst; i++) S.any_eq |= (equality && equality[i]) ? 1 : 0;
+    for (int k = 0; k < nm; k++) {
+      dk_model* m = all[k];
+      const int grid = (int)std::min<int64_t>(ctiles, m->grid);
+      k_sur_cand<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, type, d_x.p, nc, ctiles, m->d_vscratch, m->d_cscratch,
+                                                        m->scratch_doubles_per_cta, B[k].mk.p, B[k].sk.p, B[k].U.p, B[k].Cnew.p);
+      dim3 g((unsigned)((Mi + 63) / 64), (unsigned)((nc + 63) / 64));
+      k_sur_kn<<<g, 256, 0, st>>>(m->dm, d_pts.p, Mi, d_x.p, nc, B[k].W.p, B[k].Cnew.p, B[k].first.p, B[k].U.p, B[k].kn.p);
+      m->launches += 2;
+      SurModel sm{B[k].mn.p, B[k].sn.p, B[k].mk.p, B[k].sk.p, B[k].kn.p, std::sqrt(m->dm.sd2) / 1e4,
+                  (k > 0 && tol) ? tol[k - 1] : 0.0, (k > 0 && equality) ? equality[k - 1] : 0};
+      if (k == 0) S.obj = sm; else S.cst[k - 1] = sm;
+    }
+    k_sur_reduce<<<(unsigned)nc, 128, 0, st>>>(S, nc, d_out.p);
+    fun->launches++;
+    DK_CUDA_TRY(cudaGetLastError());
+    DK_CUDA_TRY(cudaMemcpyAsync(out + c0, d_out.p, (size_t)nc * 8, cudaMemcpyDeviceToHost, st));
+    DK_CUDA_TRY(cudaStreamSynchronize(st));   // hx is reused by the next chunk
+  }
+  return DK_OK;
 }

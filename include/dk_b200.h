@@ -227,6 +227,15 @@ enum { DK_FI_EXPECTED = 0, DK_FI_PROBABILITY = 1 };
 int dk_feasible_improvement(dk_model* fun, dk_model* const* cst, int n_cst, const double* x, int64_t N, double plugin,
                             int type, int kind, const int* equality, const double* tol, double* out);
 
+/* crit_SUR_cst for every row of x — replaces /root/reference/R/crit_SUR_cst.R:120-378 together with its helpers
+ * precomputeUpdateData (R/precomputeUpdateData.R:1-22) and computeQuickKrigcov2 (R/computeQuickKrigcov2.R:22-33); the
+ * checkPredict gate of :133-136 is dk_check_predict.  integration_points: Mi x d column-major (critcontrol$integration.points),
+ * integration_weights: Mi or NULL (1 / Mi each), obj_min: best feasible observation (+Inf: none), n_cst in 1..3,
+ * equality[n_cst] / tol[n_cst] may be NULL.  out[i] = mean((oldcrit - newcrit) * weights, na.rm = TRUE) of row i. */
+int dk_crit_sur_cst(dk_model* fun, dk_model* const* cst, int n_cst, const double* x, int64_t N,
+                    const double* integration_points, int64_t Mi, const double* integration_weights, double obj_min,
+                    int type, const int* equality, const double* tol, double* out);
+
 #ifdef __cplusplus
 }
 #endif

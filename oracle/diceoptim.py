@@ -773,3 +773,148 @@ def prob_of_feasible_improvement(integration_points, model_fun, model_constraint
             else:
                 pf = pf * pnorm((0.0 - pc[i]["mean"]) / pc[i]["sd"])
     return p_obj * pf
+
+
+# ---------------------------------------------------------------------------------------
+# Stepwise uncertainty reduction with constraints: precomputeUpdateData, computeQuickKrigcov2, crit_SUR_cst
+# ---------------------------------------------------------------------------------------
+def precompute_update_data(model, integration_points):
+    """R/precomputeUpdateData.R:1-22."""
+    P = np.atleast_2d(np.asarray(integration_points, float))
+    c_old = dk.cov_mat1_mat2(model.covariance, model.X, P, nugget_flag=model.covariance.nugget_flag)       # n x M
+    Tinv_c = solve_triangular(model.T, c_old, trans="T", lower=False)                                       # the big backsolve
+    Kinv_c = solve_triangular(model.T, Tinv_c, lower=False)
+    Kinv_F = solve_triangular(model.T, model.M, lower=False)
+    inv_tF_Kinv_F = np.linalg.inv(model.M.T @ model.M)                                                      # chol2inv(chol(crossprod(M)))
+    fP = dk.model_matrix(model.trend, P)
+    first_member = (fP - c_old.T @ Kinv_F) @ inv_tF_Kinv_F
+    return {"Kinv.c.olddata": Kinv_c, "Kinv.F": Kinv_F, "first.member": first_member}
+
+
+def compute_quick_krigcov2(model, integration_points, X_new, precalc, F_newdata, c_newdata):
+    """R/computeQuickKrigcov2.R:22-33: kriging covariances between X.new and the integration points (M x q)."""
+    P = np.atleast_2d(np.asarray(integration_points, float))
+    c_xnew = dk.cov_mat1_mat2(model.covariance, P, np.atleast_2d(X_new), nugget_flag=model.covariance.nugget_flag)
+    cov_std = c_xnew - precalc["Kinv.c.olddata"].T @ c_newdata
+    if F_newdata is None:
+        return cov_std
+    second = (F_newdata - c_newdata.T @ precalc["Kinv.F"]).T
+    return precalc["first.member"] @ second + cov_std
+
+
+def _pbivnorm(x, y, rho):
+    """pbivnorm::pbivnorm with the device's deterministic BVND (oracle/mvnorm.py); rho clamped to [-1, 1] where
+    rounding pushed it outside (the package would stop())."""
+    from . import mvnorm as mv
+    x, y, rho = np.broadcast_arrays(np.asarray(x, float), np.asarray(y, float), np.asarray(rho, float))
+    out = np.empty(x.shape)
+    for idx in np.ndindex(x.shape):
+        r = rho[idx]
+        out[idx] = np.nan if (np.isnan(r) or np.isnan(x[idx]) or np.isnan(y[idx])) else \
+            mv.bvn_cdf(float(x[idx]), float(y[idx]), float(min(1.0, max(-1.0, r))))
+    return out
+
+
+def crit_SUR_cst(x, model_fun, model_constraint, equality=False, critcontrol=None, type="UK"):
+    """R/crit_SUR_cst.R:120-378 for ONE point x; critcontrol$integration.points must be given
+    (integration_design_cst is outside the hot path)."""
+    cc = dict(critcontrol or {})
+    cst = list(model_constraint)
+    nc = len(cst)
+    if nc > 3:
+        return np.nan                                                                                      # :124-127
+    x = np.atleast_2d(np.asarray(x, float))
+    d = check_predict_distance(x, cst + [model_fun], distance=cc.get("distance") or "covdist", type=type)
+    if d[0] < (cc.get("threshold") or 1e-4):
+        return 0.0                                                                                         # :133-136
+    P = np.atleast_2d(np.asarray(cc["integration.points"], float))
+    Mi = P.shape[0]
+    w = cc.get("integration.weights")
+    w = np.full(Mi, 1.0 / Mi) if w is None else np.asarray(w, float)
+    pre_c, mn_c, sn_c = [], np.zeros((nc, Mi)), np.zeros((nc, Mi))
+    for i, m in enumerate(cst):                                                                            # :155-160
+        pt = dk.predict_km(m, P, type)
+        mn_c[i], sn_c[i] = pt["mean"], pt["sd"]
+        pre_c.append(precompute_update_data(m, P))
+    pt = dk.predict_km(model_fun, P, type)
+    mn_o, sn_o = pt["mean"], pt["sd"]
+    pre_o = precompute_update_data(model_fun, P)
+    obs = np.column_stack([m.y for m in cst])
+    feas = test_feas_vec(obs, equality=equality, tolConstraints=cc.get("tolConstraints"))
+    obj_min = float(np.min(model_fun.y[feas])) if feas.any() else np.inf                                   # :178-184
+    A = np.array([np.sqrt(m.covariance.sd2) / 1e4 for m in cst])[:, None]
+    keep = ~np.all(sn_c < A, axis=0)                                                                       # :192-208
+    P, mn_o, sn_o, mn_c, sn_c = P[keep], mn_o[keep], sn_o[keep], mn_c[:, keep], sn_c[:, keep]
+    if w.size > 1:
+        w = w[keep]
+    pre_o = {**pre_o, "Kinv.c.olddata": pre_o["Kinv.c.olddata"][:, keep], "first.member": pre_o["first.member"][keep]}
+    pre_c = [{**q, "Kinv.c.olddata": q["Kinv.c.olddata"][:, keep], "first.member": q["first.member"][keep]} for q in pre_c]
+    Mi = P.shape[0]
+    if Mi == 0:
+        return 0.0
+    eqv, tol = _eq_tol(nc, equality, cc)
+    any_eq = bool(np.any(eqv))
+    with np.errstate(divide="ignore", invalid="ignore"):
+        ko = dk.predict_km(model_fun, x, type)                                                             # :226-228
+        mk, sk = ko["mean"][0], ko["sd"][0]
+        kn = compute_quick_krigcov2(model_fun, P, x, pre_o, dk.model_matrix(model_fun.trend, x), ko["c"])[:, 0]
+        rho_o = kn / (sk * sn_o)
+        den = np.sqrt(sk ** 2 + sn_o ** 2 - 2 * kn)
+        eta = (mk - mn_o) / den
+        nu = (kn - sk ** 2) / sk / den
+        omt = (obj_min - mn_o) / sn_o
+        p_omt = pnorm(omt)
+        omb = (obj_min - mk) / sk
+        w1 = np.zeros(Mi); w2 = np.zeros(Mi)
+        if omb > -10:                                                                                      # :243-250
+            if omb == np.inf:
+                w1 = pnorm(eta)
+            else:
+                J = np.where(eta > -10)[0]
+                w1[J] = _pbivnorm(np.full(J.size, omb), eta[J], nu[J])
+        if -omb > -10:                                                                                     # :251-258
+            if -omb == np.inf:
+                w2 = p_omt
+            else:
+                J = np.where(omt > -10)[0]
+                w2[J] = _pbivnorm(np.full(J.size, -omb), omt[J], -rho_o[J])
+        pf_minus, pf_plus = w1 + w2, p_omt
+        Tbar = np.zeros(nc); Tbarm = np.zeros(nc); Tbarp = np.zeros(nc)
+        Tt = np.zeros((nc, Mi)); Ttm = np.zeros((nc, Mi)); Ttp = np.zeros((nc, Mi)); rho_c = np.zeros((nc, Mi))
+        for i, m in enumerate(cst):                                                                        # :274-299
+            kc = dk.predict_km(m, x, type)
+            mkc, skc = kc["mean"][0], kc["sd"][0]
+            knc = compute_quick_krigcov2(m, P, x, pre_c[i], dk.model_matrix(m.trend, x), kc["c"])[:, 0]
+            if any_eq and eqv[i]:
+                Tbarp[i] = (tol[i] - mkc) / skc; Ttp[i] = (tol[i] - mn_c[i]) / sn_c[i]
+                Tbarm[i] = (-tol[i] - mkc) / skc; Ttm[i] = (-tol[i] - mn_c[i]) / sn_c[i]
+            else:
+                Tbar[i] = (-tol[i] - mkc) / skc; Tt[i] = (-tol[i] - mn_c[i]) / sn_c[i]
+            rho_c[i] = knc / (skc * sn_c[i])
+        pf = np.ones(Mi)                                                                                   # :303-315
+        for i in range(nc):
+            pf = pf * ((pnorm(Ttp[i]) - pnorm(Ttm[i])) if (any_eq and eqv[i]) else pnorm(Tt[i]))
+        oldcrit = p_omt * pf
+        pgm = np.zeros((nc, Mi)); pgp = np.zeros((nc, Mi))
+        for i in range(nc):                                                                                # :319-348
+            if any_eq and eqv[i]:
+                pgm[i] = (_pbivnorm(Tbarp[i], Ttp[i], rho_c[i]) - _pbivnorm(Tbarp[i], Ttm[i], rho_c[i])
+                          - _pbivnorm(Tbarm[i], Ttp[i], rho_c[i]) + _pbivnorm(Tbarm[i], Ttm[i], rho_c[i]))
+                pgp[i] = pnorm(Ttp[i]) - pnorm(Ttm[i]) - pgm[i]
+            else:
+                if Tbar[i] > -10:
+                    J = np.where(Tt[i] > -10)[0]
+                    pgm[i, J] = _pbivnorm(np.full(J.size, Tbar[i]), Tt[i, J], rho_c[i, J])
+                pgp[i] = pnorm(Tt[i]) - pgm[i]
+        PT = pnorm(Tt)
+        if nc == 1:                                                                                        # :351-369
+            newcrit = pf_minus * pgm[0] + pf_plus * pgp[0]
+        elif nc == 2:
+            newcrit = pf_minus * pgm[0] * pgm[1] + pf_plus * (PT[0] * pgp[1] + PT[1] * pgp[0] - pgp[0] * pgp[1])
+        else:
+            newcrit = pf_minus * pgm[0] * pgm[1] * pgm[2] + pf_plus * (
+                PT[1] * PT[2] * pgp[0] + PT[0] * PT[2] * pgp[1] + PT[0] * PT[1] * pgp[2]
+                - PT[2] * pgp[0] * pgp[1] - PT[1] * pgp[0] * pgp[2] - PT[0] * pgp[1] * pgp[2] + pgp[0] * pgp[1] * pgp[2])
+        a = (oldcrit - newcrit) * w
+    ok = ~np.isnan(a)
+    return float(np.sum(a[ok]) / np.sum(ok)) if ok.any() else np.nan                                       # mean(., na.rm = TRUE)

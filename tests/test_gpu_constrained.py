@@ -84,3 +84,69 @@ def test_feas_single_model_and_errors(gpu_lib):
     with pytest.raises(TypeError):
         crit_EFI(x, km, [object()])
     km.release()
+
+
+def _noisy_models(n=30, d=2):
+    """Few, noisy observations: every term of the SUR criterion (bivariate CDFs included) is of order 1e-2 .. 1."""
+    from diceoptim_b200 import synth
+    X = synth.lhs(n, d, 11)
+    yo = np.sin(4.0 * X[:, 0]) + X[:, 1]
+    yc1 = X[:, 0] - 0.5 + 0.3 * np.cos(5 * X[:, 1])
+    yc2 = 0.4 - X[:, 1] + 0.2 * X[:, 0]
+    yc3 = 0.2 * np.sin(6 * X[:, 0] * X[:, 1])
+    nv = np.full(n, 0.05)
+    fun = synth.make_km(X, yo, "matern5_2", np.full(d, 0.4), float(np.var(yo)), noise_var=nv)
+    c1 = synth.make_km(X, yc1, "matern3_2", np.full(d, 0.5), float(np.var(yc1)), noise_var=nv)
+    c2 = synth.make_km(X, yc2, "gauss", np.full(d, 0.5), float(np.var(yc2)), trend="linear", noise_var=nv)
+    c3 = synth.make_km(X, yc3, "exp", np.full(d, 0.6), float(np.var(yc3)), nugget=0.01)
+    return fun, [c1, c2, c3]
+
+
+@pytest.mark.parametrize("ncst,eq", [(1, False), (2, False), (3, False), (1, [True]), (2, [False, True]), (3, [True, False, False])])
+@pytest.mark.parametrize("type", ["UK", "SK"])
+def test_crit_sur_cst_matches_oracle(gpu_lib, ncst, eq, type):
+    """crit_SUR_cst over a batch vs the oracle's restatement of R/crit_SUR_cst.R row by row; 1e-9 relative with an
+    absolute floor of 1e-13 (the criterion is a difference of probabilities times 1 / M^2)."""
+    from diceoptim_b200 import crit_SUR_cst
+    from oracle import diceoptim as do
+    fun, cst = _noisy_models()
+    cst = cst[:ncst]
+    rng = np.random.default_rng(3)
+    P = rng.random((70, 2))
+    x = rng.random((24, 2))
+    x[0] = fun.X[2]                                # on the design (noisy models: not refused, sk small)
+    cc = {"integration.points": P}
+    got = crit_SUR_cst(x, fun, cst, equality=eq, critcontrol=cc, type=type)
+    fo, co = to_oracle(fun), [to_oracle(m) for m in cst]
+    ref = np.array([do.crit_SUR_cst(xi, fo, co, equality=eq, critcontrol=cc, type=type) for xi in x])
+    assert np.max(np.abs(ref)) > 1e-7              # the case exercises the formula, not rounding noise
+    assert np.all(np.abs(got - ref) <= 1e-9 * np.abs(ref) + 1e-13), np.max(np.abs(got - ref))
+    for m in cst + [fun]:
+        m.release()
+
+
+def test_crit_sur_cst_weights_no_feasible_and_guards(gpu_lib):
+    from diceoptim_b200 import crit_SUR_cst
+    from oracle import diceoptim as do
+    fun, cst = _noisy_models()
+    rng = np.random.default_rng(8)
+    P = rng.random((50, 2)); w = rng.random(50); w /= w.sum()
+    x = rng.random((10, 2))
+    fo, co = to_oracle(fun), [to_oracle(m) for m in cst[:2]]
+    cc = {"integration.points": P, "integration.weights": w, "tolConstraints": [0.02, 0.0]}
+    got = crit_SUR_cst(x, fun, cst[:2], critcontrol=cc)
+    ref = np.array([do.crit_SUR_cst(xi, fo, co, critcontrol=cc) for xi in x])
+    assert np.all(np.abs(got - ref) <= 1e-9 * np.abs(ref) + 1e-13)
+    # no feasible observation: shift a constraint's observations up so that obj.min = Inf (:184)
+    from diceoptim_b200 import synth
+    bad = synth.make_km(cst[0].X, cst[0].y + 10.0, "matern3_2", np.full(2, 0.5), float(np.var(cst[0].y)), noise_var=np.full(30, 0.05))
+    got = crit_SUR_cst(x, fun, [bad], critcontrol={"integration.points": P})
+    ref = np.array([do.crit_SUR_cst(xi, fo, [to_oracle(bad)], critcontrol={"integration.points": P}) for xi in x])
+    assert np.all(np.abs(got - ref) <= 1e-9 * np.abs(ref) + 1e-13)
+    assert isinstance(crit_SUR_cst(x[0], fun, cst[:1], critcontrol={"integration.points": P}), float)
+    with pytest.raises(ValueError):
+        crit_SUR_cst(x, fun, cst[:1])
+    with pytest.warns(UserWarning):
+        assert np.all(np.isnan(crit_SUR_cst(x, fun, cst + [cst[0]], critcontrol={"integration.points": P})))
+    for m in cst + [fun, bad]:
+        m.release()
