@@ -671,3 +671,83 @@ def crit_SUR_cst(x, model_fun: KM, model_constraint, equality=False, critcontrol
                           device=device)
     out[refuse] = 0.0
     return float(out[0]) if single else out
+
+
+# ---- the noisy-criteria maximisers (rgenoud in the reference): screen, then batched polish of the best starts ----
+def _screen_and_polish(value, value_grad, d, lower, upper, parinit, control, seed, maximise=True):
+    """Engine replacement of the genoud calls of R/max_AEI.R:95-112, R/max_AKG.R:97-113, R/max_EQI.R:97-114 and
+    R/min_quantile.R:96-108: ``control["n.screen"]`` uniform candidates (default 2^15, plus ``parinit``) are scored in
+    one launch, the ``pop.size`` best (reference default 3 x 2^d for d <= 6, else 32 d) are polished together by the
+    batched projected L-BFGS, the best polished point wins.  Returns list(par, value) as the reference does."""
+    from .optim import batched_lbfgsb
+    control = dict(control or {})
+    lower = np.zeros(d) if lower is None else np.asarray(lower, float)
+    upper = np.ones(d) if upper is None else np.asarray(upper, float)
+    Npop = 3 * 2 ** d if d <= 6 else 32 * d
+    pop = int(control.get("pop.size", Npop))
+    maxit = int(control.get("BFGSmaxit", Npop))
+    n_screen = int(control.get("n.screen", 1 << 15))
+    rng = np.random.default_rng(seed)
+    x = lower + rng.random((n_screen, d)) * (upper - lower)
+    if parinit is not None:
+        x[0] = np.clip(np.asarray(parinit, float), lower, upper)
+    sgn = -1.0 if maximise else 1.0
+    v = sgn * np.asarray(value(x), float)
+    v = np.where(np.isnan(v), np.inf, v)
+    k = min(pop, n_screen)
+    idx = np.argpartition(v, k - 1)[:k]
+    idx = idx[np.lexsort((idx, v[idx]))]
+
+    def fg(X):
+        f, g = value_grad(X)
+        return sgn * np.asarray(f, float), sgn * np.asarray(g, float)
+    res = batched_lbfgsb(fg, x[idx], lower, upper, maxit=maxit)
+    f = np.where(np.isfinite(res["f"]), res["f"], np.inf)
+    b = int(np.argmin(f))
+    if not f[b] <= v[idx[0]]:
+        return {"par": x[idx[0]].reshape(1, -1).copy(), "value": float(sgn * v[idx[0]])}
+    return {"par": res["x"][b].reshape(1, -1).copy(), "value": float(sgn * f[b])}
+
+
+def max_AEI(model: KM, new_noise_var=0.0, y_min=None, type="UK", lower=None, upper=None, parinit=None, control=None,
+            seed=None, device=0):
+    """R/max_AEI.R:79-118."""
+    if y_min is None:
+        y_min = _default_y_min(model, type, device)
+    return _screen_and_polish(
+        lambda X: AEI(X, model, new_noise_var=new_noise_var, y_min=y_min, type=type, device=device),
+        lambda X: (AEI(X, model, new_noise_var=new_noise_var, y_min=y_min, type=type, device=device),
+                   AEI_grad(X, model, new_noise_var=new_noise_var, y_min=y_min, type=type, device=device)),
+        model.d, lower, upper, parinit, control, seed)
+
+
+def max_AKG(model: KM, new_noise_var=0.0, type="UK", lower=None, upper=None, parinit=None, control=None, seed=None,
+            device=0):
+    """R/max_AKG.R:82-120."""
+    return _screen_and_polish(
+        lambda X: AKG(X, model, new_noise_var=new_noise_var, type=type, device=device),
+        lambda X: (AKG(X, model, new_noise_var=new_noise_var, type=type, device=device),
+                   AKG_grad(X, model, new_noise_var=new_noise_var, type=type, device=device)),
+        model.d, lower, upper, parinit, control, seed)
+
+
+def max_EQI(model: KM, new_noise_var=0.0, beta=0.9, q_min=None, type="UK", lower=None, upper=None, parinit=None,
+            control=None, seed=None, device=0):
+    """R/max_EQI.R:80-120."""
+    if q_min is None:
+        p = predict(model, model.X, type=type, device=device)
+        q_min = float(np.min(p["mean"] + ndtri(beta) * p["sd"]))            # R/EQI.R:108-112
+    return _screen_and_polish(
+        lambda X: EQI(X, model, new_noise_var=new_noise_var, beta=beta, q_min=q_min, type=type, device=device),
+        lambda X: (EQI(X, model, new_noise_var=new_noise_var, beta=beta, q_min=q_min, type=type, device=device),
+                   EQI_grad(X, model, new_noise_var=new_noise_var, beta=beta, q_min=q_min, type=type, device=device)),
+        model.d, lower, upper, parinit, control, seed)
+
+
+def min_quantile(model: KM, beta=0.1, type="UK", lower=None, upper=None, parinit=None, control=None, seed=None, device=0):
+    """R/min_quantile.R:77-115 (a minimisation)."""
+    return _screen_and_polish(
+        lambda X: kriging_quantile(X, model, beta=beta, type=type, device=device),
+        lambda X: (kriging_quantile(X, model, beta=beta, type=type, device=device),
+                   kriging_quantile_grad(X, model, beta=beta, type=type, device=device)),
+        model.d, lower, upper, parinit, control, seed, maximise=False)

@@ -88,3 +88,29 @@ def test_max_qei_constant_liar(gpu_lib):
     with pytest.raises(ValueError):
         max_qEI(km, 2, lo, up, crit="CL", optimcontrol={"L": "median"})
     km.release()
+
+
+def test_noisy_criteria_maximisers(gpu_lib):
+    """max_AEI / max_AKG / max_EQI / min_quantile (R/max_AEI.R, R/max_AKG.R, R/max_EQI.R, R/min_quantile.R): the
+    returned value is the criterion at the returned point, not below the best of an independent random screen, and
+    the point is stationary up to the box."""
+    from diceoptim_b200 import (AEI, AKG, EQI, kriging_quantile, max_AEI, max_AKG, max_EQI, min_quantile)
+    km = small_model("matern5_2", "const", n=40, d=2, seed=12, noise_var=0.05)
+    lo, up = np.zeros(2), np.ones(2)
+    xs = np.random.default_rng(9).random((4000, 2))
+    ctl = {"n.screen": 4000, "pop.size": 12}
+    cases = [(max_AEI, lambda X: AEI(X, km, new_noise_var=0.05), dict(new_noise_var=0.05), True),
+             (max_AKG, lambda X: AKG(X, km, new_noise_var=0.05), dict(new_noise_var=0.05), True),
+             (max_EQI, lambda X: EQI(X, km, new_noise_var=0.05), dict(new_noise_var=0.05), True),
+             (min_quantile, lambda X: kriging_quantile(X, km, beta=0.1), dict(beta=0.1), False)]
+    for fn, crit, kw, maximise in cases:
+        res = fn(km, lower=lo, upper=up, control=ctl, seed=1, **kw)
+        assert res["par"].shape == (1, 2) and np.all(res["par"] >= lo) and np.all(res["par"] <= up)
+        at = float(np.atleast_1d(crit(res["par"]))[0])
+        assert abs(at - res["value"]) <= 1e-9 * abs(at) + 1e-14, (fn.__name__, at, res["value"])
+        scr = crit(xs)
+        if maximise:
+            assert res["value"] >= np.nanmax(scr) * (1 - 1e-9), fn.__name__
+        else:
+            assert res["value"] <= np.nanmin(scr) + 1e-9 * abs(np.nanmin(scr)), fn.__name__
+    km.release()
