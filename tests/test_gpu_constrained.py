@@ -150,3 +150,25 @@ def test_crit_sur_cst_weights_no_feasible_and_guards(gpu_lib):
         assert np.all(np.isnan(crit_SUR_cst(x, fun, cst + [cst[0]], critcontrol={"integration.points": P})))
     for m in cst + [fun, bad]:
         m.release()
+
+
+def test_constrained_batch_equals_row_by_row(gpu_lib):
+    """Position independence across ragged tiles: a row evaluated inside a batch of 131 (tiles of 64 + 64 + 3) and on
+    its own gives the same bits, for the distances, crit_EFI and crit_SUR_cst (129 integration points: ragged too)."""
+    from diceoptim_b200 import checkPredict, crit_EFI, crit_SUR_cst
+    fun, cst = _noisy_models()
+    cst = cst[:2]
+    rng = np.random.default_rng(21)
+    x = rng.random((131, 2)); P = rng.random((129, 2))
+    cc = {"integration.points": P}
+    full_d = checkPredict(x, cst + [fun], return_distance=True)
+    full_e = crit_EFI(x, fun, cst)
+    full_s = crit_SUR_cst(x, fun, cst, critcontrol=cc)
+    for i in (0, 63, 64, 127, 128, 130):
+        assert checkPredict(x[i], cst + [fun], return_distance=True)[0] == full_d[i]
+        assert crit_EFI(x[i], fun, cst) == full_e[i]
+        assert crit_SUR_cst(x[i], fun, cst, critcontrol=cc) == full_s[i]
+    again = crit_SUR_cst(x, fun, cst, critcontrol=cc)
+    assert np.array_equal(again, full_s)
+    for m in cst + [fun]:
+        m.release()
