@@ -172,3 +172,26 @@ def test_constrained_batch_equals_row_by_row(gpu_lib):
     assert np.array_equal(again, full_s)
     for m in cst + [fun]:
         m.release()
+
+
+def test_constrained_edge_inputs(gpu_lib):
+    """Empty candidate sets return empty vectors; a NaN row leaves its tile neighbours alone (and is NaN itself for crit_EFI)."""
+    from diceoptim_b200 import checkPredict, crit_EFI, crit_SUR_cst, prob_of_feasible_improvement
+    fun, cst = _noisy_models()
+    cst = cst[:2]
+    P = np.random.default_rng(2).random((40, 2))
+    cc = {"integration.points": P}
+    empty = np.empty((0, 2))
+    assert checkPredict(empty, cst + [fun]).shape == (0,)
+    assert crit_EFI(empty, fun, cst).shape == (0,)
+    assert prob_of_feasible_improvement(empty, fun, cst).shape == (0,)
+    assert crit_SUR_cst(empty, fun, cst, critcontrol=cc).shape == (0,)
+    x = np.random.default_rng(4).random((70, 2))
+    clean_e = crit_EFI(x, fun, cst); clean_s = crit_SUR_cst(x, fun, cst, critcontrol=cc)
+    xb = x.copy(); xb[5, 1] = np.nan
+    e = crit_EFI(xb, fun, cst); s = crit_SUR_cst(xb, fun, cst, critcontrol=cc)
+    keep = np.arange(70) != 5
+    assert np.isnan(e[5]) and np.array_equal(e[keep], clean_e[keep])
+    assert np.array_equal(s[keep], clean_s[keep])     # the reference stops on a NaN point (if (NA > -10)); row 5 is unspecified
+    for m in cst + [fun]:
+        m.release()
