@@ -71,6 +71,36 @@ __device__ __forceinline__ void mma_stage(double (&acc)[4][4][2], const double* 
   }
 }
 
+// Row ownership AFTER the diagonal phase of solve_block_row.  The inverse of a diagonal block is lower triangular: the
+// 16-row pair q of the block needs the k-chunks 0..q only.  With the GEMM-phase ownership (warp row wm owns pairs 2wm,
+// 2wm + 1) warp row 3 would do 15 pair-chunks and warp row 0 three; instead the diagonal phase gives warp row wm the
+// pairs wm and 7 - wm (9 pair-chunks each), the right-hand side passing through shared memory anyway.  acc[0..1] then
+// hold pair wm, acc[2..3] pair 7 - wm; everything downstream of the solve (panel store, column sums) uses solved_row.
+__device__ __forceinline__ int solved_pair(int wm, int mi) { return mi < 2 ? wm : 7 - wm; }
+__device__ __forceinline__ int solved_row(int wm, int mi, int lane) { return 16 * solved_pair(wm, mi) + 8 * (mi & 1) + (lane >> 2); }
+
+// One k-chunk of the diagonal phase: acc[0..1] += inv[pair wm] * R, acc[2..3] += inv[pair 7 - wm] * R (when needed)
+__device__ __forceinline__ void mma_stage_diag(double (&acc)[4][4][2], const double* __restrict__ As,
+                                               const double* __restrict__ Bs, int wm, int wn, int lane, bool do_lo,
+                                               bool do_hi) {
+#pragma unroll
+  for (int k4 = 0; k4 < 4; k4++) {
+    const double2 b01 = *reinterpret_cast<const double2*>(Bs + ((k4 * 4 + 2 * wn) * 32 + lane) * 2);
+    const double2 b23 = *reinterpret_cast<const double2*>(Bs + ((k4 * 4 + 2 * wn + 1) * 32 + lane) * 2);
+    const double b[4] = {b01.x, b01.y, b23.x, b23.y};
+    if (do_lo) {
+      const double2 a = *reinterpret_cast<const double2*>(As + ((wm * 4 + k4) * 32 + lane) * 2);
+#pragma unroll
+      for (int ni = 0; ni < 4; ni++) { dmma884(acc[0][ni], a.x, b[ni]); dmma884(acc[1][ni], a.y, b[ni]); }
+    }
+    if (do_hi) {
+      const double2 a = *reinterpret_cast<const double2*>(As + (((7 - wm) * 4 + k4) * 32 + lane) * 2);
+#pragma unroll
+      for (int ni = 0; ni < 4; ni++) { dmma884(acc[2][ni], a.x, b[ni]); dmma884(acc[3][ni], a.y, b[ni]); }
+    }
+  }
+}
+
 __device__ __forceinline__ void load_tile_async(double* dst, const double* __restrict__ src, int ndoubles, int tid) {
   // straight copy, 16 B per cp.async
   for (int i = tid * 2; i < ndoubles; i += NT * 2) cp_async16(dst + i, src + i);
@@ -325,15 +355,15 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
       load_tile_async(Abuf + ((j + 1) & 1) * A_TILE, Dtiles + (size_t)(j + 1) * A_TILE, A_TILE, tid);
       cp_async_commit();
     }
-    if (j < 2 * wm + 2)  // inverse is lower triangular: chunks right of this warp's rows are zero
-      mma_stage(acc, Abuf + (j & 1) * A_TILE, Rbuf + j * B_TILE, wm, wn, lane);
+    // inverse is lower triangular: pair q needs chunks 0..q (see solved_pair)
+    if (j <= 7 - wm) mma_stage_diag(acc, Abuf + (j & 1) * A_TILE, Rbuf + j * B_TILE, wm, wn, lane, j <= wm, true);
   }
 
   DK_MARK(3);
   // ---- P5: publish V_I to the panel (fragment-ordered B tiles) -----------------------------
 #pragma unroll
   for (int mi = 0; mi < 4; mi++) {
-    const int chunk = CHUNKS_PER_BLOCK * I + 2 * wm + (mi >> 1);
+    const int chunk = CHUNKS_PER_BLOCK * I + solved_pair(wm, mi);
     const int k = 8 * (mi & 1) + (lane >> 2);
 #pragma unroll
     for (int ni = 0; ni < 4; ni++)
@@ -517,7 +547,7 @@ __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __
       for (int ni = 0; ni < 4; ni++) part[ni][0] = part[ni][1] = 0.0;
 #pragma unroll
       for (int mi = 0; mi < 4; mi++) {
-        const bool live = (I * BM + 32 * wm + 8 * mi + (lane >> 2)) < M.n;
+        const bool live = (I * BM + solved_row(wm, mi, lane)) < M.n;
 #pragma unroll
         for (int ni = 0; ni < 4; ni++)
 #pragma unroll

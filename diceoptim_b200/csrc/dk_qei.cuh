@@ -131,7 +131,7 @@ __device__ __forceinline__ void qei_tile_moments(const DevModel& M, int type, in
         double part[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
 #pragma unroll
         for (int mi = 0; mi < 4; mi++) {
-          const bool live = (I * BM + 32 * wm + 8 * mi + (lane >> 2)) < n;
+          const bool live = (I * BM + solved_row(wm, mi, lane)) < n;
           const double o0 = live ? acc[mi][ni][0] : 0.0, o1 = live ? acc[mi][ni][1] : 0.0;
           const double p0 = __shfl_xor_sync(0xffffffffu, o0, 1), p1 = __shfl_xor_sync(0xffffffffu, o1, 1);
           part[0] = fma(o0, o0, part[0]);
