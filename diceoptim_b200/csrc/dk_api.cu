@@ -1183,9 +1183,9 @@ int ensure_knyy(dk_model* m, int type, cudaStream_t st) {
   const int t = type == DK_UK ? 1 : 0;
   if (m->d_knyy[t]) return DK_OK;
   const int n = m->n, d = m->d;
-  double* buf = nullptr;
-  int rc = dev_alloc(m, &buf, (size_t)n);
-  if (rc) return rc;
+  DevBuf buf;  // handed to the model only when filled (freed on every error path)
+  if (buf.alloc((size_t)n) != cudaSuccess) { cudaGetLastError(); return fail(DK_ERR_NOMEM, "cudaMalloc of %zu bytes failed", (size_t)n * 8); }
+  int rc = DK_OK;
   // candidates are n x d column-major; d_Xrm is row-major: transpose a host copy (small, once)
   std::vector<double> Xrm((size_t)n * d), Xcm((size_t)n * d);
   DK_CUDA_TRY(cudaMemcpy(Xrm.data(), m->d_Xrm, Xrm.size() * 8, cudaMemcpyDeviceToHost));
@@ -1201,8 +1201,10 @@ int ensure_knyy(dk_model* m, int type, cudaStream_t st) {
   DK_CUDA_TRY(cudaMemcpyAsync(sd.data(), d_sd, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
   DK_CUDA_TRY(cudaStreamSynchronize(st));
   for (auto& v : sd) v = v * v;
-  DK_CUDA_TRY(cudaMemcpy(buf, sd.data(), (size_t)n * 8, cudaMemcpyHostToDevice));
-  m->d_knyy[t] = buf;
+  DK_CUDA_TRY(cudaMemcpy(buf.p, sd.data(), (size_t)n * 8, cudaMemcpyHostToDevice));
+  m->d_knyy[t] = buf.p;
+  m->device_bytes += (size_t)n * 8;
+  buf.p = nullptr;
   return DK_OK;
 }
 }  // namespace
