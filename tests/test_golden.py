@@ -62,3 +62,40 @@ def test_cuda_matches_golden(gpu_lib):
     for q in (2, 3, 4):
         close(qEI(z[f"xb{q}"], km, plugin=float(z["plugin"])), z[f"qEI{q}"], 1e-9, 1e-12)
     km.release()
+
+
+def load_cst():
+    from diceoptim_b200 import KM, Covariance
+    z = np.load(os.path.join(G, "cst_branin_16.npz"))
+    models = []
+    for tag in ("o", "c1", "c2"):
+        cov = Covariance(name=str(z[f"{tag}_kernel"]), sd2=float(z[f"{tag}_sd2"]), range_val=z[f"{tag}_theta"],
+                         nugget=float(z[f"{tag}_nugget"]), nugget_flag=bool(z[f"{tag}_nugget_flag"]))
+        models.append(KM(X=z[f"{tag}_X"], y=z[f"{tag}_y"], F=z[f"{tag}_F"], trend=str(z[f"{tag}_trend"]),
+                         trend_coef=z[f"{tag}_beta"], covariance=cov, T=z[f"{tag}_T"], z=z[f"{tag}_z"], M=z[f"{tag}_M"],
+                         noise_var=z[f"{tag}_noise_var"]))
+    return z, models[0], models[1:]
+
+
+def test_oracle_reproduces_constrained_golden():
+    from oracle import diceoptim as do
+    z, fun, cst = load_cst()
+    fo, co = to_oracle(fun), [to_oracle(m) for m in cst]
+    idx = [0, 17, 40, 62, 80]
+    close(do.check_predict_distance(z["x"][idx], co + [fo], "covdist"), z["mindist"][idx], 1e-12, 1e-15)
+    close([do.crit_EFI(z["x"][i], fo, co) for i in idx], z["EFI"][idx], 1e-12, 1e-18)
+    close(do.prob_of_feasible_improvement(z["x"][idx], fo, co), z["PFI"][idx], 1e-12, 1e-18)
+    close([do.crit_SUR_cst(z["x"][i], fo, co, critcontrol={"integration.points": z["P"]}) for i in idx[:3]], z["SUR"][idx[:3]],
+          1e-12, 1e-20)
+
+
+@pytest.mark.gpu
+def test_cuda_matches_constrained_golden(gpu_lib):
+    from diceoptim_b200 import checkPredict, crit_EFI, crit_SUR_cst, prob_of_feasible_improvement
+    z, fun, cst = load_cst()
+    close(checkPredict(z["x"], cst + [fun], return_distance=True), z["mindist"], 1e-9, 1e-9)
+    close(crit_EFI(z["x"], fun, cst), z["EFI"], 1e-9, 1e-14)
+    close(prob_of_feasible_improvement(z["x"], fun, cst), z["PFI"], 1e-9, 1e-14)
+    close(crit_SUR_cst(z["x"], fun, cst, critcontrol={"integration.points": z["P"]}), z["SUR"], 1e-9, 1e-15)
+    for m in cst + [fun]:
+        m.release()
