@@ -8,8 +8,8 @@ DiceKriging; ``synth`` only builds km objects with FIXED hyper-parameters for te
 from .km import KM, Covariance, DeviceModel  # noqa: F401
 from .api import (AEI, AEI_grad, EQI_grad, AKG, AKG_grad, EI, EQI, EI_grad, kriging_quantile, kriging_quantile_grad, max_crit, max_EI, max_qEI, predict, qEI, qEI_grad,  # noqa: F401
                   sampleFromEI, screen_EI, checkPredict, crit_EFI, crit_SUR_cst, Feas, prob_of_feasible_improvement,
-                  max_AEI, max_AKG, max_EQI, min_quantile)
+                  max_AEI, max_AKG, max_EQI, min_quantile, integration_design_cst)
 
 __all__ = ["AEI", "AEI_grad", "EQI", "EQI_grad", "AKG", "AKG_grad", "KM", "Covariance", "DeviceModel", "EI", "EI_grad", "kriging_quantile", "kriging_quantile_grad",
            "max_crit", "max_EI", "max_qEI", "predict", "qEI", "qEI_grad", "sampleFromEI", "screen_EI", "checkPredict", "crit_EFI", "crit_SUR_cst", "Feas",
-           "prob_of_feasible_improvement", "max_AEI", "max_AKG", "max_EQI", "min_quantile"]
+           "prob_of_feasible_improvement", "max_AEI", "max_AKG", "max_EQI", "min_quantile", "integration_design_cst"]

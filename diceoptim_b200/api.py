@@ -638,8 +638,8 @@ def _max_qEI_CL(model: KM, npoints, L, lower, upper, parinit=None, minimization=
 
 def crit_SUR_cst(x, model_fun: KM, model_constraint, equality=False, critcontrol=None, type="UK", device=0):
     """Stepwise uncertainty reduction with constraints, R/crit_SUR_cst.R:120-378, for every row of ``x``.
-    ``critcontrol["integration.points"]`` (M x d) is required (integration_design_cst stays on the host side of the
-    caller); ``integration.weights`` defaults to 1 / M each.  0 where checkPredict refuses the point; NaN when there are
+    ``critcontrol["integration.points"]`` (M x d) or, to have them drawn by integration_design_cst, ``lower`` and
+    ``upper``; ``integration.weights`` defaults to 1 / M each.  0 where checkPredict refuses the point; NaN when there are
     more than three constraints (the reference warns and returns NA)."""
     if not isinstance(model_fun, KM):
         raise TypeError("model.fun must be a km model (fastfun objectives are not served by the GPU engine)")
@@ -652,7 +652,13 @@ def crit_SUR_cst(x, model_fun: KM, model_constraint, equality=False, critcontrol
         warnings.warn("crit_SUR_cst does not take more than 3 constraints")
         return float("nan") if single else np.full(N, np.nan)
     if cc.get("integration.points") is None:
-        raise ValueError("critcontrol['integration.points'] is required")
+        # R/crit_SUR_cst.R:139-143: integration_design_cst(integcontrol = critcontrol, lower, upper, ...)
+        if cc.get("lower") is None or cc.get("upper") is None:
+            raise ValueError("critcontrol needs 'integration.points', or 'lower' and 'upper' to draw them")
+        des = integration_design_cst(integcontrol=cc, lower=cc["lower"], upper=cc["upper"], model_fun=model_fun,
+                                     model_constraint=cst, device=device)
+        cc["integration.points"] = des["integration.points"]
+        cc["integration.weights"] = des["integration.weights"]
     P = np.asfortranarray(np.atleast_2d(np.asarray(cc["integration.points"], float)))
     if P.shape[1] != model_fun.d:
         raise ValueError("integration.points does not have the right size")
@@ -751,3 +757,50 @@ def min_quantile(model: KM, beta=0.1, type="UK", lower=None, upper=None, parinit
         lambda X: (kriging_quantile(X, model, beta=beta, type=type, device=device),
                    kriging_quantile_grad(X, model, beta=beta, type=type, device=device)),
         model.d, lower, upper, parinit, control, seed, maximise=False)
+
+
+def integration_design_cst(integcontrol=None, lower=None, upper=None, model_fun=None, model_constraint=None, equality=False,
+                           critcontrol=None, min_prob=0.001, seed=None, device=0):
+    """R/integration_design_cst.R: the integration points (and weights) of crit_SUR_cst.  No ``integration.points`` in
+    ``integcontrol`` -> 100 d uniform points; given -> passed through; otherwise ``distrib`` "MC" (uniform), "sobol"
+    (scipy's Sobol sequence in place of randtoolbox) or "SUR" (importance sampling of ``n.candidates`` uniform points
+    by prob.of.feasible.improvement, evaluated on the GPU).  Returns dict(integration.points, integration.weights)."""
+    ic = dict(integcontrol or {})
+    lower = np.asarray(lower, float); upper = np.asarray(upper, float)
+    if lower.shape != upper.shape:
+        raise ValueError("'lower' and 'upper' must have the same length")
+    d = lower.size
+    rng = np.random.default_rng(seed)
+    if ic.get("integration.points") is not None:
+        return {"integration.points": np.atleast_2d(np.asarray(ic["integration.points"], float)),
+                "integration.weights": ic.get("integration.weights")}
+    if not ic or ("n.points" not in ic and "distrib" not in ic):
+        return {"integration.points": lower + rng.random((100 * d, d)) * (upper - lower), "integration.weights": None}
+    n_points = int(ic.get("n.points", 100 * d))
+    distrib = ic.get("distrib", "MC")
+
+    def draw(kind, n):
+        if kind == "sobol":
+            from scipy.stats import qmc
+            return lower + qmc.Sobol(d, scramble=False).random(n) * (upper - lower)
+        if kind == "MC":
+            return lower + rng.random((n, d)) * (upper - lower)
+        raise ValueError(f"unknown distribution {kind!r}")
+    if distrib in ("sobol", "MC"):
+        return {"integration.points": draw(distrib, n_points), "integration.weights": None}
+    if distrib != "SUR":
+        raise ValueError(f"unknown integcontrol$distrib {distrib!r}")
+    n_cand = int(ic.get("n.candidates", 10 * n_points))
+    init = ic.get("init.distrib", "MC")
+    cand = np.atleast_2d(np.asarray(ic["init.distrib.spec"], float)) if init == "spec" else draw(init, n_cand)
+    if model_fun is None or model_constraint is None:
+        raise ValueError("for the 'SUR' importance sampling distribution model.fun and model.constraint are needed")
+    tau = prob_of_feasible_improvement(cand, model_fun, model_constraint, equality=equality, critcontrol=critcontrol,
+                                       type="UK", device=device)
+    tot = float(np.sum(tau)) or 1.0
+    prob = np.maximum(tau / tot, min_prob / n_cand)
+    prob = prob / prob.sum()
+    weight = 1.0 / (prob * n_cand * n_points)
+    cum = np.concatenate([[0.0], np.cumsum(prob)])
+    idx = np.clip(np.searchsorted(cum, rng.random(n_points), side="right") - 1, 0, n_cand - 1)   # findInterval(all.inside)
+    return {"integration.points": cand[idx], "integration.weights": weight[idx]}

@@ -178,4 +178,17 @@ SEXP dkR_feasible_improvement(SEXP hfun, SEXP hcst, SEXP x, SEXP plugin, SEXP ty
   if (rc) Rf_error("dk_feasible_improvement: %s", dk_last_error());
   return out;
 }
+
+/* crit_SUR_cst for every row of x (R/crit_SUR_cst.R:120-378); pts: M x d matrix, weights: numeric(M) or NULL */
+SEXP dkR_crit_sur_cst(SEXP hfun, SEXP hcst, SEXP x, SEXP pts, SEXP weights, SEXP obj_min, SEXP type, SEXP equality, SEXP tol) {
+  int n = 0;
+  dk_model** hs = handles_of(hcst, &n);
+  R_xlen_t N = Rf_nrows(x);
+  SEXP out = PROTECT(Rf_allocVector(REALSXP, N));
+  int rc = dk_crit_sur_cst(handle_of(hfun), hs, n, REAL(x), (int64_t)N, REAL(pts), (int64_t)Rf_nrows(pts), opt_real(weights),
+                           Rf_asReal(obj_min), Rf_asInteger(type), LOGICAL(equality), opt_real(tol), REAL(out));
+  UNPROTECT(1);
+  if (rc) Rf_error("dk_crit_sur_cst: %s", dk_last_error());
+  return out;
+}
 #endif /* DK_HAVE_R */

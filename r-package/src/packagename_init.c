@@ -18,6 +18,7 @@ extern SEXP dkR_screen_ei(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
 extern SEXP dkR_sample_weights(SEXP, SEXP, SEXP, SEXP);
 extern SEXP dkR_check_predict(SEXP, SEXP, SEXP, SEXP);
 extern SEXP dkR_feasible_improvement(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
+extern SEXP dkR_crit_sur_cst(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
 
 static const R_CMethodDef CEntries[] = {{"davies", (DL_FUNC)&davies, 13}, {NULL, NULL, 0}};
 static const R_CallMethodDef CallEntries[] = {
@@ -27,6 +28,7 @@ static const R_CallMethodDef CallEntries[] = {
     {"dkR_screen_ei", (DL_FUNC)&dkR_screen_ei, 7},       {"dkR_sample_weights", (DL_FUNC)&dkR_sample_weights, 4},
     {"dkR_check_predict", (DL_FUNC)&dkR_check_predict, 4},
     {"dkR_feasible_improvement", (DL_FUNC)&dkR_feasible_improvement, 8},
+    {"dkR_crit_sur_cst", (DL_FUNC)&dkR_crit_sur_cst, 9},
     {NULL, NULL, 0}};
 
 void R_init_DiceOptim(DllInfo* dll) {

@@ -146,6 +146,18 @@ def test_crit_sur_cst_weights_no_feasible_and_guards(gpu_lib):
     assert isinstance(crit_SUR_cst(x[0], fun, cst[:1], critcontrol={"integration.points": P}), float)
     with pytest.raises(ValueError):
         crit_SUR_cst(x, fun, cst[:1])
+    # integration points drawn by integration_design_cst (R/crit_SUR_cst.R:139-143), plain and importance-sampled
+    from diceoptim_b200 import integration_design_cst
+    v = crit_SUR_cst(x, fun, cst[:1], critcontrol={"lower": [0, 0], "upper": [1, 1]})
+    assert v.shape == (10,) and np.all(np.isfinite(v))
+    des = integration_design_cst({"n.points": 64, "distrib": "SUR", "n.candidates": 512}, [0, 0], [1, 1], fun, cst[:2], seed=1)
+    assert des["integration.points"].shape == (64, 2) and des["integration.weights"].shape == (64,)
+    assert np.all(des["integration.weights"] > 0)
+    ci = {"integration.points": des["integration.points"], "integration.weights": des["integration.weights"]}
+    got = crit_SUR_cst(x, fun, cst[:2], critcontrol=ci)
+    ref = np.array([do.crit_SUR_cst(xi, fo, co, critcontrol=ci) for xi in x])
+    assert np.all(np.abs(got - ref) <= 1e-9 * np.abs(ref) + 1e-13)
+    assert integration_design_cst({"n.points": 32, "distrib": "sobol"}, [0, 0], [2, 1])["integration.points"].max() <= 2.0
     with pytest.warns(UserWarning):
         assert np.all(np.isnan(crit_SUR_cst(x, fun, cst + [cst[0]], critcontrol={"integration.points": P})))
     for m in cst + [fun, bad]:
