@@ -1381,6 +1381,7 @@ extern "C" int dk_crit_sur_cst(dk_model* fun, dk_model* const* cst, int n_cst, c
   size_t per_cand = 0;
   for (dk_model* m : all) per_cand += ((size_t)m->n + (size_t)Mi + m->p + 2) * 8;
   int64_t NC = (int64_t)std::max<size_t>(64, (size_t)1500000000 / per_cand);
+  NC = std::min<int64_t>(NC, (int64_t)1 << 21);   // k_sur_kn's grid.y = NC / 64 stays far below 65535
   NC = std::min<int64_t>(N, NC & ~(int64_t)63);
   if (NC < 1) NC = std::min<int64_t>(N, 64);
 
