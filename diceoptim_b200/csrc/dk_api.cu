@@ -325,7 +325,7 @@ int dk_model_create(const dk_model_desc* D, dk_model** out) {
     std::vector<double> Xrm((size_t)dm.n_pad * d, 0.0);
     for (int i = 0; i < n; i++)
       for (int k = 0; k < d; k++) Xrm[(size_t)i * d + k] = D->X[(size_t)i + (size_t)k * n];
-    if ((rc = dev_alloc(m, &m->d_Xrm, 2 * Xrm.size()))) return bail(rc);
+    if ((rc = dev_alloc(m, &m->d_Xrm, 3 * Xrm.size()))) return bail(rc);
     cudaMemcpy(m->d_Xrm, Xrm.data(), Xrm.size() * 8, cudaMemcpyHostToDevice);
     dm.Xrm = m->d_Xrm;
     {
@@ -333,6 +333,13 @@ int dk_model_create(const dk_model_desc* D, dk_model** out) {
       for (size_t i = 0; i < Xrm.size(); i++) Xs[i] = Xrm[i] * dm.w[i % d];
       cudaMemcpy(m->d_Xrm + Xrm.size(), Xs.data(), Xs.size() * 8, cudaMemcpyHostToDevice);
       dm.Xrm_s = m->d_Xrm + Xrm.size();
+    }
+    {
+      // round(X, 8) once per model: the qEI kernels compare it with the rounded batch points (R/qEI.R:124-134)
+      std::vector<double> Xr(Xrm.size());
+      for (size_t i = 0; i < Xrm.size(); i++) Xr[i] = std::nearbyint(Xrm[i] * 1e8) / 1e8;
+      cudaMemcpy(m->d_Xrm + 2 * Xrm.size(), Xr.data(), Xr.size() * 8, cudaMemcpyHostToDevice);
+      dm.Xrm_r8 = m->d_Xrm + 2 * Xrm.size();
     }
 
     // ---- small candidate-independent arrays (SURVEY 8(a1) "derived once per model") ----

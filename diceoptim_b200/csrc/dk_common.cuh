@@ -63,6 +63,7 @@ struct DevModel {
   const double* tiles_bwd;  // backward (flipped T) tiles, same format; NULL until a gradient call
   const double* Xrm;        // [n_pad][d] row-major design (pad rows zero)
   const double* Xrm_s;      // the same rows scaled by w_k (cov-gen operand)
+  const double* Xrm_r8;     // the same rows rounded to 8 digits, rint(v 1e8) / 1e8 (qEI's duplicate rule)
   const double* beta;       // p
   const double* RM;         // chol(M'M) upper, p x p column-major
   const double* tuuinv;     // (M'M)^-1, p x p

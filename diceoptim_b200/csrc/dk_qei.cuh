@@ -167,9 +167,10 @@ __device__ __forceinline__ void qei_tile_moments(const DevModel& M, int type, in
     // 4 threads per candidate scan the design for a row equal after rounding to 8 digits
     const int c = tid & (BN - 1), slice = tid >> 6;
     bool dup = false;
+    const double x0 = round8(xs[c]);   // the design is rounded once per model (Xrm_r8); a row is dismissed on its first coordinate
     for (int i = slice; i < n && !dup; i += 4) {
-      bool same = true;
-      for (int k = 0; k < d && same; k++) same = (round8(__ldg(M.Xrm + (size_t)i * d + k)) == round8(xs[k * BN + c]));
+      bool same = (__ldg(M.Xrm_r8 + (size_t)i * d) == x0);
+      for (int k = 1; k < d && same; k++) same = (__ldg(M.Xrm_r8 + (size_t)i * d + k) == round8(xs[k * BN + c]));
       dup = same;
     }
     if (dup) atomicOr(&dupflag[c], 1);
