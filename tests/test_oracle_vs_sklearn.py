@@ -39,3 +39,20 @@ def test_matern_kernels_one_dimension(name, nu):
     theta, sd2 = 0.3, 0.9
     m = dk.make_km(X, y, name, np.array([theta]), sd2, noise_var=np.full(30, 1e-6))
     _check(m, ConstantKernel(sd2, "fixed") * Matern(theta, "fixed", nu=nu), rng.random((20, 1)), 1e-6)
+
+
+def test_universal_kriging_is_the_flat_prior_limit():
+    """UK with a constant trend = zero-mean GP whose kernel carries an extra constant of huge variance (flat prior on
+    beta): the GLS coefficient and the variance inflation term of predict.km(type = "UK") come out of that limit.  1e-5
+    (the 1e6 prior variance costs digits)."""
+    rng = np.random.default_rng(2)
+    X = rng.random((35, 2)); y = 2.0 + np.sin(4 * X[:, 0]) * X[:, 1]
+    theta = np.array([0.5, 0.6]); sd2 = 0.8
+    m = dk.make_km(X, y, "gauss", theta, sd2, noise_var=np.full(35, 1e-4))      # beta = GLS estimate
+    kern = ConstantKernel(sd2, "fixed") * RBF(theta, "fixed") + ConstantKernel(1e6, "fixed")
+    gp = sk.GaussianProcessRegressor(kernel=kern, alpha=1e-4, optimizer=None, normalize_y=False).fit(X, y)
+    Xn = rng.random((20, 2))
+    mean, sd = gp.predict(Xn, return_std=True)
+    got = dk.predict_km(m, Xn, "UK")
+    assert np.max(np.abs(got["mean"] - mean)) < 1e-5 * (np.max(np.abs(y)) + 1.0)
+    assert np.max(np.abs(got["sd"] ** 2 - sd ** 2)) < 1e-5 * sd2
