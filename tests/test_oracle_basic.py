@@ -85,3 +85,43 @@ def test_akg_grad_oracle_vs_finite_differences_sk():
         assert np.max(np.abs(g - fd)) <= 1e-3 * np.max(np.abs(g)) + 1e-12
         checked += 1
     assert checked >= 2
+
+
+@pytest.mark.parametrize("type", ["SK", "UK"])
+def test_akg_against_its_definition_by_monte_carlo(type):
+    """AKG(x) = E_Z[max_i (A_i + B_i Z)] - max_i A_i with A = -(kriging means at the design and at x) and
+    B = cov_n(., x) / sqrt(tau^2 + s_n(x)^2) (R/AKG.R:136-146).  Here A and B come from predict.km's own posterior
+    covariance (cov.compute branch) instead of AKG's V.X / mu.x algebra, and the expectation from 2e6 normal draws
+    instead of the envelope scan: an independent check of both."""
+    rng = np.random.default_rng(3)
+    X = rng.random((15, 2)); y = np.sin(5 * X[:, 0]) + X[:, 1] + 0.1 * rng.standard_normal(15)
+    m = dk.make_km(X, y, "matern5_2", np.array([0.4, 0.5]), float(np.var(y)), noise_var=np.full(15, 0.02))
+    tau2 = 0.03
+    for x in rng.random((3, 2)):
+        pts = np.vstack([X, x])
+        pr = dk.predict_km(m, pts, type, cov_compute=True)
+        A = -pr["mean"]
+        sk2 = pr["cov"][-1, -1]
+        B = pr["cov"][:, -1] / np.sqrt(tau2 + sk2)
+        Z = rng.standard_normal(2_000_000)
+        best = np.full(Z.size, -np.inf)
+        for a, b in zip(A, B):
+            np.maximum(best, a + b * Z, out=best)
+        mc = best.mean() - A.max(); se = best.std() / np.sqrt(Z.size)
+        got = do.AKG(x, m, new_noise_var=tau2, type=type)
+        assert abs(got - mc) < 5 * se + 1e-9, (got, mc, se)
+
+
+def test_ei_against_its_definition_by_quadrature():
+    """EI(x) = E[max(plugin - Y(x), 0)], Y(x) ~ N(mean, sd^2) (minimisation), by adaptive quadrature."""
+    from scipy.integrate import quad
+    from scipy.stats import norm
+    km = to_oracle(small_model("matern5_2", "linear", n=25, d=2, seed=5))
+    x = np.random.default_rng(1).random((6, 2))
+    pr = dk.predict_km(km, x, "UK")
+    plugin = float(np.median(km.y))
+    got = do.EI(x, km, plugin=plugin)
+    for i in range(6):
+        m, s = pr["mean"][i], pr["sd"][i]
+        ref = quad(lambda y: (plugin - y) * norm.pdf(y, m, s), m - 12 * s, plugin, epsabs=1e-14, epsrel=1e-12)[0] if plugin > m - 12 * s else 0.0
+        assert abs(got[i] - ref) <= 1e-9 * abs(ref) + 1e-13
