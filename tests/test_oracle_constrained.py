@@ -35,3 +35,46 @@ def test_covdist_identity():
         assert np.max(np.abs(kn_xy - (delta[:, None] * w).T)) < 1e-10 * m.covariance.sd2
         d = do.check_predict_distance(x, [m], "covdist")
         assert np.all(np.isfinite(d)) and np.all(d >= 0)
+
+
+def test_crit_sur_cst_against_its_definition_by_monte_carlo():
+    """One inequality constraint: the criterion is the expected drop, after observing f and g at x, of
+    mean_u w_u P(g(u) <= 0) P(f(u) <= best feasible value), where the best feasible value becomes min(obj.min, f(x))
+    when g(x) <= 0.  Here the expectation is a 3e5-draw Monte-Carlo over (f(x), g(x)) with the Gaussian conditioning
+    formulas and predict.km's own posterior covariances, instead of the pbivnorm algebra of R/crit_SUR_cst.R."""
+    from scipy.special import ndtr
+    rng = np.random.default_rng(5)
+    X = rng.random((18, 2))
+    yo = np.sin(4 * X[:, 0]) + X[:, 1] + 0.05 * rng.standard_normal(18)
+    yc = X[:, 0] - 0.45 + 0.3 * np.cos(5 * X[:, 1]) + 0.05 * rng.standard_normal(18)
+    nv = np.full(18, 0.03)
+    fun = dk.make_km(X, yo, "matern5_2", np.array([0.4, 0.5]), float(np.var(yo)), noise_var=nv)
+    cst = dk.make_km(X, yc, "matern3_2", np.array([0.5, 0.5]), float(np.var(yc)), noise_var=nv)
+    P = rng.random((25, 2)); Mi = P.shape[0]
+    feas = do.test_feas_vec(yc[:, None])
+    obj_min = float(np.min(yo[feas]))
+    S = 300_000
+    informative = 0
+    for x in rng.random((2, 2)):
+        got = do.crit_SUR_cst(x, fun, [cst], critcontrol={"integration.points": P, "distance": "covratio", "threshold": 1e-9})
+        tot = np.zeros(S)
+        parts = {}
+        for tag, m in (("f", fun), ("g", cst)):
+            pr = dk.predict_km(m, np.vstack([P, x]), "UK", cov_compute=True)
+            mn, sn2 = pr["mean"][:-1], np.diag(pr["cov"])[:-1]
+            mk, sk2, kn = pr["mean"][-1], pr["cov"][-1, -1], pr["cov"][:-1, -1]
+            ynew = mk + np.sqrt(sk2) * rng.standard_normal(S)
+            parts[tag] = (mn, sn2, mk, sk2, kn, ynew)
+        mn_f, sn2_f, mk_f, sk2_f, kn_f, yf = parts["f"]
+        mn_g, sn2_g, mk_g, sk2_g, kn_g, yg = parts["g"]
+        T = np.where(yg <= 0.0, np.minimum(obj_min, yf), obj_min)
+        for u in range(Mi):
+            old = ndtr((obj_min - mn_f[u]) / np.sqrt(sn2_f[u])) * ndtr((0.0 - mn_g[u]) / np.sqrt(sn2_g[u]))
+            mf = mn_f[u] + kn_f[u] / sk2_f * (yf - mk_f); sf = np.sqrt(max(sn2_f[u] - kn_f[u] ** 2 / sk2_f, 1e-300))
+            mg = mn_g[u] + kn_g[u] / sk2_g * (yg - mk_g); sg = np.sqrt(max(sn2_g[u] - kn_g[u] ** 2 / sk2_g, 1e-300))
+            new = ndtr((T - mf) / sf) * ndtr((0.0 - mg) / sg)
+            tot += (old - new) * (1.0 / Mi) / Mi          # mean(a * weights), weights = 1 / Mi
+        mc, se = tot.mean(), tot.std() / np.sqrt(S)
+        assert abs(got - mc) < 5 * se + 1e-12, (got, mc, se)
+        informative += got > 20 * se
+    assert informative >= 1          # at least one point where the criterion is resolved to a few percent
