@@ -125,3 +125,18 @@ def test_ei_against_its_definition_by_quadrature():
         m, s = pr["mean"][i], pr["sd"][i]
         ref = quad(lambda y: (plugin - y) * norm.pdf(y, m, s), m - 12 * s, plugin, epsabs=1e-14, epsrel=1e-12)[0] if plugin > m - 12 * s else 0.0
         assert abs(got[i] - ref) <= 1e-9 * abs(ref) + 1e-13
+
+
+@pytest.mark.parametrize("type", ["SK", "UK"])
+def test_aei_eqi_gradients_by_finite_differences(type):
+    """R/AEI.grad.R and R/EQI.grad.R restated vs central differences of the restated AEI / EQI (fixed y.min / q.min)."""
+    km = to_oracle(small_model("matern5_2", "linear", n=30, d=2, seed=8, noise_var=0.04))
+    rng = np.random.default_rng(6)
+    h = 1e-6
+    for x in rng.random((3, 2)) * 0.8 + 0.1:
+        for f, g, kw in ((do.AEI, do.AEI_grad, dict(new_noise_var=0.03, y_min=float(np.median(km.y)))),
+                         (do.EQI, do.EQI_grad, dict(new_noise_var=0.03, beta=0.9, q_min=float(np.median(km.y))))):
+            an = g(x, km, type=type, **kw)
+            fd = np.array([(float(np.ravel(f(x + h * e, km, type=type, **kw))[0]) - float(np.ravel(f(x - h * e, km, type=type, **kw))[0])) / (2 * h)
+                           for e in np.eye(2)])
+            assert np.max(np.abs(an - fd)) <= 2e-6 * np.max(np.abs(fd)) + 1e-9, (f.__name__, an, fd)
