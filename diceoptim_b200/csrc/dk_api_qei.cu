@@ -1,0 +1,145 @@
+// dk_api_qei.cu — C ABI entry points of the qEI family (include/dk_b200.h): dk_qei*, dk_qei_grad*, dk_mvn_cdf.
+#include "dk_host.h"
+#include "dk_qei.cuh"
+
+using namespace dk;
+
+
+// ------------------------------------------------------------------------------------------
+// qEI (R/qEI.R:119-261): batches of q <= DK_MAX_Q points
+// ------------------------------------------------------------------------------------------
+
+namespace {
+bool g_qei_attr_done[64] = {};
+
+int ensure_qei(dk_model* m, int64_t B) {
+  if (m->device < 64 && !g_qei_attr_done[m->device]) {
+    DK_CUDA_TRY(cudaFuncSetAttribute(k_qei_moments, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
+    g_qei_attr_done[m->device] = true;
+  }
+  if (!m->d_aux) {
+    int rc = dev_alloc(m, &m->d_aux, (size_t)m->grid * QEI_AUX_DOUBLES);
+    if (rc) return rc;
+  }
+  const size_t need = (size_t)std::max<int64_t>(B, 1) * MOM_STRIDE;
+  if (m->mom_doubles < need) {
+    if (m->d_mom) { cudaFree(m->d_mom); m->device_bytes -= m->mom_doubles * 8; m->d_mom = nullptr; m->mom_doubles = 0; }
+    int rc = dev_alloc(m, &m->d_mom, need);
+    if (rc) return rc;
+    m->mom_doubles = need;
+  }
+  return DK_OK;
+}
+
+}  // namespace
+
+extern "C" int dk_qei_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type, int minimization,
+                          double* d_out, void* stream) {
+  int rc = check_call(m, d_x, B);
+  if (rc) return rc;
+  if (q < 1 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI batch size q=%d outside 1..%d (deterministic CDFs are implemented up to dimension %d)", q, DK_MAX_Q, DK_MAX_Q);
+  if (!d_out) return fail(DK_ERR_ARG, "d_out is NULL");
+  if (B == 0) return DK_OK;
+  DeviceGuard guard(m->device);
+  if ((rc = ensure_qei(m, B))) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t ntiles = (B + QB - 1) / QB;
+  const int grid = (int)std::min<int64_t>(ntiles, m->grid);
+  if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
+  k_qei_moments<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, type, q, d_x, B, ntiles, m->d_vscratch, m->scratch_doubles_per_cta,
+                                             m->d_aux, m->d_mom);
+  DK_CUDA_TRY(cudaGetLastError());
+  static const int64_t warp_below = [] { const char* e = std::getenv("DK_QEI_WARP_BELOW"); return e ? std::atoll(e) : (int64_t)12288; }();  // measured crossover (cfg3): 2048 batches 0.64 vs 2.06 ms, 18944: 5.4 vs 5.0 ms
+  if (B < warp_below)  // few batches: a warp per batch (path-integral nodes spread over lanes) hides latency better
+    k_qei_cdf_warp<<<(unsigned)((B + 3) / 4), 128, 0, st>>>(m->d_mom, B, q, plugin, minimization, d_out);
+  else
+    k_qei_cdf<<<(unsigned)((B * 4 + 127) / 128), 128, 0, st>>>(m->d_mom, B, q, plugin, minimization, d_out);
+  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
+  m->launches += 2;
+  DK_CUDA_TRY(cudaGetLastError());
+  return DK_OK;
+}
+
+extern "C" int dk_qei(dk_model* m, const double* x, int64_t B, int q, double plugin, int type, int minimization,
+                      double* out) {
+  int rc = check_call(m, x, B);
+  if (rc) return rc;
+  if (q < 1 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI batch size q=%d outside 1..%d", q, DK_MAX_Q);
+  if (!out) return fail(DK_ERR_ARG, "out is NULL");
+  DeviceGuard guard(m->device);
+  HostCall h;
+  if ((rc = h.init(m, x, B * q, (size_t)B))) return rc;
+  if ((rc = dk_qei_dev(m, h.d_x, B, q, plugin, type, minimization, h.d_out, m->stream))) return rc;
+  if ((rc = h.fetch(out, h.d_out, B))) return rc;
+  return h.finish();
+}
+
+extern "C" int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type,
+                               int minimization, double* d_grad, void* stream) {
+  int rc = check_call(m, d_x, B);
+  if (rc) return rc;
+  if (q < 2 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI.grad batch size q=%d outside 2..%d (use dk_ei_grad for q = 1)", q, DK_MAX_Q);
+  if (!d_grad) return fail(DK_ERR_ARG, "d_grad is NULL");
+  if (B == 0) return DK_OK;
+  DeviceGuard guard(m->device);
+  if ((rc = ensure_bwd(m))) return rc;
+  if ((rc = ensure_qei(m, B))) return rc;
+  static bool attr_done[64] = {};
+  if (m->device < 64 && !attr_done[m->device]) {
+    DK_CUDA_TRY(cudaFuncSetAttribute(k_qei_grad_moments, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
+    attr_done[m->device] = true;
+  }
+  const size_t need = (size_t)B * qei_deriv_stride(m->d);
+  if (m->deriv_doubles < need) {
+    if (m->d_deriv) { cudaFree(m->d_deriv); m->device_bytes -= m->deriv_doubles * 8; m->d_deriv = nullptr; m->deriv_doubles = 0; }
+    if ((rc = dev_alloc(m, &m->d_deriv, need))) return rc;
+    m->deriv_doubles = need;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t ntiles = (B + QB - 1) / QB;
+  const int grid = (int)std::min<int64_t>(ntiles, m->grid);
+  if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
+  k_qei_grad_moments<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, type, q, d_x, B, ntiles, m->d_vscratch, m->d_wscratch,
+                                                  m->d_cscratch, m->scratch_doubles_per_cta, m->d_aux, m->d_mom, m->d_deriv);
+  DK_CUDA_TRY(cudaGetLastError());
+  const int64_t threads = B * 4;
+  k_qei_grad_cdf<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(m->d_mom, m->d_deriv, B, q, m->d, plugin, minimization,
+                                                                   m->dm.sd2, d_grad);
+  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
+  m->launches += 2;
+  DK_CUDA_TRY(cudaGetLastError());
+  return DK_OK;
+}
+
+extern "C" int dk_qei_grad(dk_model* m, const double* x, int64_t B, int q, double plugin, int type, int minimization,
+                           double* out_grad) {
+  int rc = check_call(m, x, B);
+  if (rc) return rc;
+  if (q < 2 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI.grad batch size q=%d outside 2..%d (use dk_ei_grad for q = 1)", q, DK_MAX_Q);
+  if (!out_grad) return fail(DK_ERR_ARG, "out_grad is NULL");
+  DeviceGuard guard(m->device);
+  HostCall h;
+  if ((rc = h.init(m, x, B * q, (size_t)B * q * m->d))) return rc;
+  if ((rc = dk_qei_grad_dev(m, h.d_x, B, q, plugin, type, minimization, h.d_out, m->stream))) return rc;
+  if ((rc = h.fetch(out_grad, h.d_out, (size_t)B * q * m->d))) return rc;
+  return h.finish();
+}
+
+/* Test hook: pmnorm(h_b, varcov = S_b) for B independent q-variate problems (q <= 4), host pointers,
+ * device 0.  h is B x q row-major, S is B x q x q row-major. */
+extern "C" int dk_mvn_cdf(int q, int64_t B, const double* h, const double* S, double* out) {
+  if (q < 1 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "dimension q=%d outside 1..%d", q, DK_MAX_Q);
+  if (!h || !S || !out || B < 0) return fail(DK_ERR_ARG, "dk_mvn_cdf: bad argument");
+  if (B == 0) return DK_OK;
+  DevBuf bh, bS, bo;
+  DK_CUDA_TRY(bh.alloc((size_t)B * q));
+  DK_CUDA_TRY(bS.alloc((size_t)B * q * q));
+  DK_CUDA_TRY(bo.alloc((size_t)B));
+  double *d_h = bh.p, *d_S = bS.p, *d_o = bo.p;
+  DK_CUDA_TRY(cudaMemcpy(d_h, h, B * q * 8, cudaMemcpyHostToDevice));
+  DK_CUDA_TRY(cudaMemcpy(d_S, S, B * q * q * 8, cudaMemcpyHostToDevice));
+  k_mvn_cdf_test<<<(unsigned)((B + 63) / 64), 64>>>(q, B, d_h, d_S, d_o);
+  DK_CUDA_TRY(cudaGetLastError());
+  DK_CUDA_TRY(cudaMemcpy(out, d_o, B * 8, cudaMemcpyDeviceToHost));
+  return DK_OK;
+}

@@ -29,7 +29,7 @@ __device__ __forceinline__ double rcp_nr(double x) {
 //   [0..10]  sin:  -1/3!, 1/5!, ... , -1/23!   (odd Taylor series, |x| <= pi/2, truncation below 2e-18)
 //   [11..22] exp:  1/2!, 1/3!, ... , 1/13!     (Taylor series on |r| <= ln2 / 2, truncation below 4e-18)
 //   [23..25] log2(e), ln2 high part (32 trailing zero bits), ln2 low part
-__device__ __constant__ double MVN_K[26] = {
+static __device__ __constant__ double MVN_K[26] = {
     -1.6666666666666666e-01, 8.333333333333333e-03,  -1.984126984126984e-04, 2.7557319223985893e-06,
     -2.505210838544172e-08,  1.6059043836821613e-10, -7.647163731819816e-13, 2.8114572543455206e-15,
     -8.22063524662433e-18,   1.9572941063391263e-20, -3.868170170630684e-23,
@@ -67,10 +67,10 @@ __device__ __forceinline__ double exp_path(double x) {
 
 // One out-of-line copy of Phi for the CDF kernels: the inlined erfc is ~150 instructions and the quadrature code
 // calls it from a dozen places; the hot path has to stay inside the 32 KB instruction cache.
-__device__ __noinline__ double phi_cdf(double x) { return normcdf(x); }
+static __device__ __noinline__ double phi_cdf(double x) { return normcdf(x); }
 
 // |r| >= 0.925 branch of BVND (rare for the conditional correlations met here; kept out of line)
-__device__ __noinline__ double bvnu_far(double h, double k, double r) {
+static __device__ __noinline__ double bvnu_far(double h, double k, double r) {
   double hk = h * k, bvn = 0.0;
   if (r < 0.0) { k = -k; hk = -hk; }
   if (fabs(r) < 1.0) {
@@ -110,7 +110,7 @@ __device__ __noinline__ double bvnu_far(double h, double k, double r) {
 }
 
 // P(X > dh, Y > dk), correlation r
-__device__ __noinline__ double bvnu_dev(double dh, double dk, double r) {
+static __device__ __noinline__ double bvnu_dev(double dh, double dk, double r) {
   if (dh == INFINITY || dk == INFINITY) return 0.0;
   if (dh == -INFINITY) return phi_cdf(-dk);
   if (dk == -INFINITY) return phi_cdf(-dh);
@@ -159,7 +159,7 @@ __device__ __forceinline__ double tvn_term(double h1, double hj, double hk, doub
   return e * phi_cdf((hk - mu) * rsqrt(var));
 }
 
-__device__ __noinline__ double tvn_cdf_dev(double h1, double h2, double h3, double r12, double r13, double r23) {
+static __device__ __noinline__ double tvn_cdf_dev(double h1, double h2, double h3, double r12, double r13, double r23) {
   const double base = phi_cdf(h1) * bvn_cdf_dev(h2, h3, r23);
   const double a2 = asin(r12), a3 = asin(r13);
   if (fabs(a2) + fabs(a3) == 0.0) return base;
@@ -185,7 +185,7 @@ __device__ __noinline__ double tvn_cdf_dev(double h1, double h2, double h3, doub
 // One term of the Phi_4 integrand: phi_2(h0, hj; rj) (up to 1 / (2 pi sqrt(csj))) times the bivariate CDF of the
 // two remaining variables (limits hk, hl) given the first two.  rk1, rl1: their path correlations with variable
 // 0; rkj, rlj, rkl: fixed correlations.  Out of line: one copy serves the three correlations of row 0.
-__device__ __noinline__ double qvn_pair_term(double h0, double hj, double hk, double hl, double rj, double csj,
+static __device__ __noinline__ double qvn_pair_term(double h0, double hj, double hk, double hl, double rj, double csj,
                                              double rk1, double rl1, double rkj, double rlj, double rkl) {
   const double icsj = (csj < 1e-290) ? 1.0 / csj : rcp_nr(csj);
   const double e = exp_path(-0.5 * (h0 * h0 - 2.0 * rj * h0 * hj + hj * hj) * icsj);
@@ -225,7 +225,7 @@ __device__ __forceinline__ double qvn_node(const double* h, const double* R, con
 }
 
 // h[4], R row-major 4 x 4 correlation matrix
-__device__ __noinline__ double qvn_cdf_dev(const double* h, const double* R) {
+static __device__ __noinline__ double qvn_cdf_dev(const double* h, const double* R) {
   const double base = phi_cdf(h[0]) * tvn_cdf_dev(h[1], h[2], h[3], R[1 * 4 + 2], R[1 * 4 + 3], R[2 * 4 + 3]);
   double a[3];
   for (int j = 0; j < 3; j++) a[j] = asin(R[j + 1]);
@@ -310,7 +310,7 @@ __device__ __forceinline__ double pmnorm_coop(bool active, int q, const double* 
 
 // pmnorm(x, varcov = S) for q = 1..4; S row-major with leading dimension 4.  Out of line and rolled: the callers
 // reach it from a dozen sites and the square roots / divisions expand to ~100 instructions each.
-__device__ __noinline__ double pmnorm_dev(int q, const double* x, const double* S) {
+static __device__ __noinline__ double pmnorm_dev(int q, const double* x, const double* S) {
   double sd[4], z[4], R[16];
 #pragma unroll 1
   for (int i = 0; i < q; i++) {

@@ -611,7 +611,7 @@ __device__ __forceinline__ double dmnorm2(double xi, double xj, double sii, doub
 }
 
 // decompo(x, mu, Sigma, k = {i}) (R/qEI.grad.R:1-26): density of component i times the CDF of the rest given it
-__device__ __noinline__ double decompo1(int q, const double* x, const double* mu, const double* S, int i) {
+static __device__ __noinline__ double decompo1(int q, const double* x, const double* mu, const double* S, int i) {
   const double sii = S[i * 4 + i], dens = dmnorm1(x[i], mu[i], sii);
   if (q == 1) return dens;
   double x2[4], V[16];
@@ -643,7 +643,7 @@ __device__ __noinline__ double decompo1(int q, const double* x, const double* mu
 }
 
 // decompo(x, mu, Sigma, k = {i, j}), i < j
-__device__ __noinline__ double decompo2(int q, const double* x, const double* mu, const double* S, int i, int j) {
+static __device__ __noinline__ double decompo2(int q, const double* x, const double* mu, const double* S, int i, int j) {
   const double sii = S[i * 4 + i], sij = S[i * 4 + j], sjj = S[j * 4 + j];
   const double di = x[i] - mu[i], dj = x[j] - mu[j];
   const double dens = dmnorm2(di, dj, sii, sij, sjj);
