@@ -43,6 +43,7 @@ SIGNATURES = {
     "dk_model_launches": (C.c_longlong, [_V]),
     "dk_model_set_timing": (_I, [_V, _I]),
     "dk_model_last_kernel_ms": (_D, [_V]),
+    "dk_model_last_phase_ms": (_D, [_V]),
     "dk_predict": (_I, [_V, _V, _L, _I, _V, _V]),
     "dk_predict_dev": (_I, [_V, _V, _L, _I, _V, _V, _V]),
     "dk_ei": (_I, [_V, _V, _L, _D, _I, _I, _I, _V, _V, _V]),
@@ -76,6 +77,18 @@ SIGNATURES = {
     "dk_qei_grad": (_I, [_V, _V, _L, _I, _D, _I, _I, _V]),
     "dk_qei_grad_dev": (_I, [_V, _V, _L, _I, _D, _I, _I, _V, _V]),
     "dk_mvn_cdf": (_I, [_I, _L, _V, _V, _V]),
+    "dk_multi_create": (_I, [C.POINTER(dk_model_desc), _V, _I, C.POINTER(_V)]),
+    "dk_multi_destroy": (None, [_V]),
+    "dk_multi_count": (_I, [_V]),
+    "dk_multi_model": (_V, [_V, _I]),
+    "dk_model_clone": (_I, [_V, _I, C.POINTER(_V)]),
+    "dk_multi_predict": (_I, [_V, _V, _L, _I, _V, _V]),
+    "dk_multi_ei": (_I, [_V, _V, _L, _D, _I, _I, _I, _V, _V, _V]),
+    "dk_multi_ei_grad": (_I, [_V, _V, _L, _D, _I, _I, _I, _V, _V]),
+    "dk_multi_quantile": (_I, [_V, _V, _L, _D, _I, _V, _V]),
+    "dk_multi_akg": (_I, [_V, _V, _L, _D, _I, _V]),
+    "dk_multi_qei": (_I, [_V, _V, _L, _I, _D, _I, _I, _V, _V]),
+    "dk_multi_screen_ei": (_I, [_V, _V, _L, _D, _I, _I, _I, _I, _V, _V]),
     "dk_ei_dev_noalloc": (_I, [_V, _V, _L, _D, _I, _I, _I, _V, _V, _V, _V]),
 }
 DEBUG_SIGNATURES = {

@@ -122,14 +122,28 @@ int ensure_bwd(dk_model* m) {
   } catch (const std::bad_alloc&) {
     return fail(DK_ERR_NOMEM, "host allocation for the backward tiles failed");
   }
-  int rc = dev_alloc(m, &m->d_tiles_bwd, tiles.size());
-  if (rc) return rc;
-  DK_CUDA_TRY(cudaMemcpy(m->d_tiles_bwd, tiles.data(), tiles.size() * 8, cudaMemcpyHostToDevice));
-  rc = dev_alloc(m, &m->d_wscratch, (size_t)m->grid * (m->scratch_doubles_per_cta + COEF_DOUBLES));
-  if (rc) return rc;
-  rc = dev_alloc(m, &m->d_cscratch, (size_t)m->grid * m->scratch_doubles_per_cta);  // covariance panels (gradients)
-  if (rc) return rc;
-  m->dm.tiles_bwd = m->d_tiles_bwd;
+  // allocate into locals and publish every pointer only once all steps succeeded: a failed call leaves the handle
+  // exactly as it was (a later gradient call retries instead of launching with half of the buffers)
+  double *t = nullptr, *w = nullptr, *c = nullptr;
+  const size_t wcount = (size_t)m->grid * (m->scratch_doubles_per_cta + COEF_DOUBLES);
+  const size_t ccount = (size_t)m->grid * m->scratch_doubles_per_cta;
+  int rc = dev_alloc(m, &t, tiles.size());
+  if (!rc) rc = dev_alloc(m, &w, wcount);
+  if (!rc) rc = dev_alloc(m, &c, ccount);  // covariance panels (gradients)
+  if (!rc) {
+    cudaError_t e = cudaMemcpy(t, tiles.data(), tiles.size() * 8, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) rc = fail(DK_ERR_CUDA, "upload of the backward tiles failed: %s", cudaGetErrorString(e));
+  }
+  if (rc) {
+    dev_release(m, &t, tiles.size());
+    dev_release(m, &w, wcount);
+    dev_release(m, &c, ccount);
+    return rc;
+  }
+  m->d_wscratch = w;
+  m->d_cscratch = c;
+  m->d_tiles_bwd = t;
+  m->dm.tiles_bwd = t;
   return DK_OK;
 }
 
@@ -186,7 +200,7 @@ int launch_predict(dk_model* m, const CritParams& P, const double* d_x, int64_t 
   } else
     k_predict_fused<<<grid, NT, SM_TOTAL, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->scratch_doubles_per_cta,
                                                  d_main, d_mean, d_sd);
-  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
+  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; m->ev_mid_valid = false; }
   m->launches++;
   DK_CUDA_TRY(cudaGetLastError());
   return DK_OK;
@@ -206,9 +220,118 @@ int launch_grad(dk_model* m, const CritParams& P, const double* d_x, int64_t N, 
   else
     k_grad_fused<-1><<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, P, d_x, N, ntiles, m->d_vscratch, m->d_wscratch,
                                                            m->d_cscratch, m->scratch_doubles_per_cta, d_grad, d_main);
-  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
+  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; m->ev_mid_valid = false; }
   m->launches++;
   DK_CUDA_TRY(cudaGetLastError());
+  return DK_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// chunked host <-> device pipeline (dk_host.h)
+// ------------------------------------------------------------------------------------------
+int64_t chunk_units_for(const dk_model* m, int unit, int tile_units) {
+  const int64_t wave = (int64_t)tile_units * m->grid;
+  const double bytes_per_wave = (double)wave * unit * m->d * 8.0;
+  int64_t k = (int64_t)std::llround(24.0e6 / bytes_per_wave);
+  k = std::max<int64_t>(1, std::min<int64_t>(k, 256));
+  return wave * k;
+}
+
+namespace {
+int ensure_pipeline(dk_model* m, size_t in_doubles, size_t out_doubles) {
+  if (!m->copy_in) {
+    DK_CUDA_TRY(cudaStreamCreateWithFlags(&m->copy_in, cudaStreamNonBlocking));
+    DK_CUDA_TRY(cudaStreamCreateWithFlags(&m->copy_out, cudaStreamNonBlocking));
+    for (int s = 0; s < 2; s++) {
+      DK_CUDA_TRY(cudaEventCreateWithFlags(&m->ev_h2d[s], cudaEventDisableTiming));
+      DK_CUDA_TRY(cudaEventCreateWithFlags(&m->ev_kern[s], cudaEventDisableTiming));
+      DK_CUDA_TRY(cudaEventCreateWithFlags(&m->ev_d2h[s], cudaEventDisableTiming));
+    }
+  }
+  in_doubles = (in_doubles + 31) & ~(size_t)31;
+  out_doubles = (out_doubles + 31) & ~(size_t)31;
+  if (m->stage_in_doubles >= in_doubles && m->stage_out_doubles >= out_doubles) return DK_OK;
+  in_doubles = std::max(in_doubles, m->stage_in_doubles);
+  out_doubles = std::max(out_doubles, m->stage_out_doubles);
+  if (m->h_stage) { cudaFreeHost(m->h_stage); m->h_stage = nullptr; }
+  dev_release(m, &m->d_chunk, 2 * (m->stage_in_doubles + m->stage_out_doubles));
+  m->stage_in_doubles = m->stage_out_doubles = 0;
+  const size_t total = 2 * (in_doubles + out_doubles);
+  cudaError_t e = cudaHostAlloc((void**)&m->h_stage, total * 8, cudaHostAllocDefault);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    m->h_stage = nullptr;
+    return fail(DK_ERR_NOMEM, "cudaHostAlloc of %zu bytes of pinned staging failed: %s", total * 8, cudaGetErrorString(e));
+  }
+  int rc = dev_alloc(m, &m->d_chunk, total);
+  if (rc) { cudaFreeHost(m->h_stage); m->h_stage = nullptr; return rc; }
+  m->stage_in_doubles = in_doubles;
+  m->stage_out_doubles = out_doubles;
+  return DK_OK;
+}
+}  // namespace
+
+int run_chunked(dk_model* m, const double* x, int64_t ldx, int64_t row0, int64_t nunits, int unit, int64_t chunk_units,
+                const HostOut* outs, int nouts, const ChunkLaunch& launch) {
+  if (nunits <= 0) return DK_OK;
+  if (nouts > 8) return fail(DK_ERR_ARG, "run_chunked: too many outputs");
+  const int d = m->d;
+  chunk_units = std::max<int64_t>(1, std::min(chunk_units, nunits));
+  const int64_t crows = chunk_units * unit;
+  size_t out_per_chunk = 0;
+  for (int j = 0; j < nouts; j++)
+    if (outs[j].host) out_per_chunk += (size_t)outs[j].cols * (size_t)(outs[j].per_unit ? chunk_units : crows);
+  int rc = ensure_pipeline(m, (size_t)crows * d, out_per_chunk);
+  if (rc) return rc;
+  const size_t in_sz = m->stage_in_doubles, out_sz = m->stage_out_doubles;
+  double* h_in[2] = {m->h_stage, m->h_stage + in_sz};
+  double* h_out[2] = {m->h_stage + 2 * in_sz, m->h_stage + 2 * in_sz + out_sz};
+  double* d_in[2] = {m->d_chunk, m->d_chunk + in_sz};
+  double* d_out[2] = {m->d_chunk + 2 * in_sz, m->d_chunk + 2 * in_sz + out_sz};
+  const int64_t unit_base = row0 / unit;
+  const int64_t nchunks = (nunits + chunk_units - 1) / chunk_units;
+
+  // copy a finished chunk's outputs from pinned staging into the caller's arrays
+  auto scatter = [&](int64_t ci) -> int {
+    const int s = (int)(ci & 1);
+    DK_CUDA_TRY(cudaEventSynchronize(m->ev_d2h[s]));
+    const int64_t u0 = ci * chunk_units, nu = std::min(chunk_units, nunits - u0);
+    size_t off = 0;
+    for (int j = 0; j < nouts; j++) {
+      if (!outs[j].host) continue;
+      const int64_t cnt = outs[j].per_unit ? nu : nu * unit;
+      const int64_t first = outs[j].per_unit ? unit_base + u0 : row0 + u0 * unit;
+      for (int c = 0; c < outs[j].cols; c++)
+        std::memcpy(outs[j].host + (size_t)c * outs[j].ld + first, h_out[s] + off + (size_t)c * cnt, (size_t)cnt * 8);
+      off += (size_t)outs[j].cols * cnt;
+    }
+    return DK_OK;
+  };
+
+  for (int64_t ci = 0; ci < nchunks; ci++) {
+    const int s = (int)(ci & 1);
+    if (ci >= 2 && (rc = scatter(ci - 2))) return rc;   // also: slot s of every buffer is free again
+    const int64_t u0 = ci * chunk_units, nu = std::min(chunk_units, nunits - u0), rows = nu * unit;
+    const double* src = x + row0 + u0 * unit;
+    for (int k = 0; k < d; k++) std::memcpy(h_in[s] + (size_t)k * rows, src + (size_t)k * ldx, (size_t)rows * 8);
+    DK_CUDA_TRY(cudaMemcpyAsync(d_in[s], h_in[s], (size_t)rows * d * 8, cudaMemcpyHostToDevice, m->copy_in));
+    DK_CUDA_TRY(cudaEventRecord(m->ev_h2d[s], m->copy_in));
+    DK_CUDA_TRY(cudaStreamWaitEvent(m->stream, m->ev_h2d[s], 0));
+    double* dptr[8];
+    size_t off = 0;
+    for (int j = 0; j < nouts; j++) {
+      const int64_t cnt = outs[j].per_unit ? nu : rows;
+      dptr[j] = outs[j].host ? d_out[s] + off : nullptr;
+      if (outs[j].host) off += (size_t)outs[j].cols * cnt;
+    }
+    if ((rc = launch(d_in[s], rows, dptr, u0, m->stream))) return rc;
+    DK_CUDA_TRY(cudaEventRecord(m->ev_kern[s], m->stream));
+    DK_CUDA_TRY(cudaStreamWaitEvent(m->copy_out, m->ev_kern[s], 0));
+    if (off) DK_CUDA_TRY(cudaMemcpyAsync(h_out[s], d_out[s], off * 8, cudaMemcpyDeviceToHost, m->copy_out));
+    DK_CUDA_TRY(cudaEventRecord(m->ev_d2h[s], m->copy_out));
+  }
+  for (int64_t ci = std::max<int64_t>(0, nchunks - 2); ci < nchunks; ci++)
+    if ((rc = scatter(ci))) return rc;
   return DK_OK;
 }
 
@@ -282,8 +405,12 @@ int dk_model_create(const dk_model_desc* D, dk_model** out) {
     AugFactor L{D->T, D->z, D->M, n, p, dm.n_aug};
     build_tiles(L, dm.nblk, tiles);
     if ((rc = dev_alloc(m, &m->d_tiles_fwd, tiles.size()))) return bail(rc);
-    if (cudaMemcpy(m->d_tiles_fwd, tiles.data(), tiles.size() * 8, cudaMemcpyHostToDevice) != cudaSuccess)
-      return bail(fail(DK_ERR_CUDA, "upload of the factor tiles failed: %s", cudaGetErrorString(cudaGetLastError())));
+    m->tiles_fwd_doubles = tiles.size();
+    auto upload = [&](double* dst, const double* src, size_t count, const char* what) {
+      const cudaError_t e = cudaMemcpy(dst, src, count * 8, cudaMemcpyHostToDevice);
+      return e == cudaSuccess ? DK_OK : fail(DK_ERR_CUDA, "upload of %s failed: %s", what, cudaGetErrorString(e));
+    };
+    if ((rc = upload(m->d_tiles_fwd, tiles.data(), tiles.size(), "the factor tiles"))) return bail(rc);
     dm.tiles_fwd = m->d_tiles_fwd;
     tiles.clear(); tiles.shrink_to_fit();
 
@@ -292,19 +419,20 @@ int dk_model_create(const dk_model_desc* D, dk_model** out) {
     for (int i = 0; i < n; i++)
       for (int k = 0; k < d; k++) Xrm[(size_t)i * d + k] = D->X[(size_t)i + (size_t)k * n];
     if ((rc = dev_alloc(m, &m->d_Xrm, 3 * Xrm.size()))) return bail(rc);
-    cudaMemcpy(m->d_Xrm, Xrm.data(), Xrm.size() * 8, cudaMemcpyHostToDevice);
+    m->xrm_doubles = 3 * Xrm.size();
+    if ((rc = upload(m->d_Xrm, Xrm.data(), Xrm.size(), "the design"))) return bail(rc);
     dm.Xrm = m->d_Xrm;
     {
       std::vector<double> Xs(Xrm.size());
       for (size_t i = 0; i < Xrm.size(); i++) Xs[i] = Xrm[i] * dm.w[i % d];
-      cudaMemcpy(m->d_Xrm + Xrm.size(), Xs.data(), Xs.size() * 8, cudaMemcpyHostToDevice);
+      if ((rc = upload(m->d_Xrm + Xrm.size(), Xs.data(), Xs.size(), "the scaled design"))) return bail(rc);
       dm.Xrm_s = m->d_Xrm + Xrm.size();
     }
     {
       // round(X, 8) once per model: the qEI kernels compare it with the rounded batch points (R/qEI.R:124-134)
       std::vector<double> Xr(Xrm.size());
       for (size_t i = 0; i < Xrm.size(); i++) Xr[i] = std::nearbyint(Xrm[i] * 1e8) / 1e8;
-      cudaMemcpy(m->d_Xrm + 2 * Xrm.size(), Xr.data(), Xr.size() * 8, cudaMemcpyHostToDevice);
+      if ((rc = upload(m->d_Xrm + 2 * Xrm.size(), Xr.data(), Xr.size(), "the rounded design"))) return bail(rc);
       dm.Xrm_r8 = m->d_Xrm + 2 * Xrm.size();
     }
 
@@ -369,7 +497,8 @@ int dk_model_create(const dk_model_desc* D, dk_model** out) {
     const size_t o_nv = off;
     if (D->noise_var) std::memcpy(&small[off], D->noise_var, (size_t)n * 8);
     if ((rc = dev_alloc(m, &m->d_small, small.size()))) return bail(rc);
-    cudaMemcpy(m->d_small, small.data(), small.size() * 8, cudaMemcpyHostToDevice);
+    m->small_doubles = small.size();
+    if ((rc = upload(m->d_small, small.data(), small.size(), "the trend / weight arrays"))) return bail(rc);
     dm.beta = m->d_small + o_beta; dm.RM = m->d_small + o_RM; dm.tuuinv = m->d_small + o_tu;
     dm.alpha = m->d_small + o_al; dm.KinvF = m->d_small + o_al + n;
     dm.noise_var = D->noise_var ? m->d_small + o_nv : nullptr;
@@ -411,6 +540,77 @@ int dk_model_create(const dk_model_desc* D, dk_model** out) {
   return DK_OK;
 }
 
+// A replica of `src` on another device: the three uploads (factor tiles, design, small arrays) are copied device to
+// device, nothing is re-tiled on the host; the lazily built pieces (backward tiles, AKG constants, K^-1) are rebuilt
+// per replica on first use from the host copies.
+int dk_model_clone(const dk_model* src, int device, dk_model** out) {
+  if (!src || !out) return fail(DK_ERR_ARG, "dk_model_clone: NULL argument");
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(DK_ERR_UNSUPPORTED, "no CUDA device visible");
+  if (device < 0 || device >= ndev) return fail(DK_ERR_ARG, "device %d out of range (%d visible)", device, ndev);
+  cudaDeviceProp prop;
+  DK_CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) return fail(DK_ERR_UNSUPPORTED, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+  DeviceGuard guard(device);
+  int rc = set_kernel_attrs(device);
+  if (rc) return rc;
+  dk_model* m = new (std::nothrow) dk_model();
+  if (!m) return fail(DK_ERR_NOMEM, "host allocation failed");
+  auto bail = [&](int code) { dk_model_destroy(m); return code; };
+  m->device = device;
+  m->num_sms = prop.multiProcessorCount;
+  m->n = src->n; m->d = src->d; m->p = src->p;
+  m->dm = src->dm;
+  m->dm.tiles_bwd = nullptr; m->dm.akg_a_sorted = nullptr; m->dm.akg_delta = nullptr; m->dm.akg_perm = nullptr;
+  m->tiles_fwd_doubles = src->tiles_fwd_doubles; m->xrm_doubles = src->xrm_doubles; m->small_doubles = src->small_doubles;
+  if ((rc = dev_alloc(m, &m->d_tiles_fwd, m->tiles_fwd_doubles))) return bail(rc);
+  if ((rc = dev_alloc(m, &m->d_Xrm, m->xrm_doubles))) return bail(rc);
+  if ((rc = dev_alloc(m, &m->d_small, m->small_doubles))) return bail(rc);
+  auto peer = [&](double* dst, const double* s, size_t count) {
+    const cudaError_t e = cudaMemcpyPeer(dst, device, s, src->device, count * 8);
+    return e == cudaSuccess ? DK_OK : fail(DK_ERR_CUDA, "device-to-device copy of the model failed: %s", cudaGetErrorString(e));
+  };
+  if ((rc = peer(m->d_tiles_fwd, src->d_tiles_fwd, m->tiles_fwd_doubles))) return bail(rc);
+  if ((rc = peer(m->d_Xrm, src->d_Xrm, m->xrm_doubles))) return bail(rc);
+  if ((rc = peer(m->d_small, src->d_small, m->small_doubles))) return bail(rc);
+  auto rebase = [](const double* p, const double* old_base, double* new_base) -> const double* {
+    return p ? new_base + (p - old_base) : nullptr;
+  };
+  DevModel& dm = m->dm;
+  dm.tiles_fwd = m->d_tiles_fwd;
+  dm.Xrm = rebase(src->dm.Xrm, src->d_Xrm, m->d_Xrm);
+  dm.Xrm_s = rebase(src->dm.Xrm_s, src->d_Xrm, m->d_Xrm);
+  dm.Xrm_r8 = rebase(src->dm.Xrm_r8, src->d_Xrm, m->d_Xrm);
+  dm.beta = rebase(src->dm.beta, src->d_small, m->d_small);
+  dm.RM = rebase(src->dm.RM, src->d_small, m->d_small);
+  dm.tuuinv = rebase(src->dm.tuuinv, src->d_small, m->d_small);
+  dm.alpha = rebase(src->dm.alpha, src->d_small, m->d_small);
+  dm.KinvF = rebase(src->dm.KinvF, src->d_small, m->d_small);
+  dm.Mcm = rebase(src->dm.Mcm, src->d_small, m->d_small);
+  dm.noise_var = rebase(src->dm.noise_var, src->d_small, m->d_small);
+  const size_t n = (size_t)src->n, p = (size_t)src->p;
+  auto dup = [&](const double* h, size_t count, double** dst) {
+    if (!h) return true;
+    *dst = (double*)std::malloc(count * 8);
+    if (!*dst) return false;
+    std::memcpy(*dst, h, count * 8);
+    return true;
+  };
+  if (!dup(src->h_T, n * n, &m->h_T) || !dup(src->h_zM, n * (p + 1), &m->h_zM) || !dup(src->h_y, n, &m->h_y) ||
+      !dup(src->h_nv, n, &m->h_nv))
+    return bail(fail(DK_ERR_NOMEM, "host allocation failed"));
+  m->grid = src->grid * m->num_sms / std::max(1, src->num_sms);
+  m->scratch_doubles_per_cta = src->scratch_doubles_per_cta;
+  if ((rc = dev_alloc(m, &m->d_vscratch, (size_t)m->grid * m->scratch_doubles_per_cta))) return bail(rc);
+  if (cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess)
+    return bail(fail(DK_ERR_CUDA, "cudaStreamCreate failed"));
+  if (cudaDeviceSynchronize() != cudaSuccess)
+    return bail(fail(DK_ERR_CUDA, "model replication failed: %s", cudaGetErrorString(cudaGetLastError())));
+  *out = m;
+  return DK_OK;
+}
+
 void dk_model_destroy(dk_model* m) {
   if (!m) return;
   DeviceGuard guard(m->device);
@@ -419,8 +619,18 @@ void dk_model_destroy(dk_model* m) {
   cudaFree(m->d_vscratch); cudaFree(m->d_wscratch); cudaFree(m->d_cscratch); cudaFree(m->d_io); cudaFree(m->d_red);
   cudaFree(m->d_aux); cudaFree(m->d_mom); cudaFree(m->d_deriv);
   if (m->stream) cudaStreamDestroy(m->stream);
+  if (m->copy_in) cudaStreamDestroy(m->copy_in);
+  if (m->copy_out) cudaStreamDestroy(m->copy_out);
+  for (int s = 0; s < 2; s++) {
+    if (m->ev_h2d[s]) cudaEventDestroy(m->ev_h2d[s]);
+    if (m->ev_kern[s]) cudaEventDestroy(m->ev_kern[s]);
+    if (m->ev_d2h[s]) cudaEventDestroy(m->ev_d2h[s]);
+  }
+  if (m->h_stage) cudaFreeHost(m->h_stage);
+  cudaFree(m->d_chunk); cudaFree(m->d_vec);
   if (m->ev0) cudaEventDestroy(m->ev0);
   if (m->ev1) cudaEventDestroy(m->ev1);
+  if (m->ev_mid) cudaEventDestroy(m->ev_mid);
   std::free(m->h_T);
   std::free(m->h_zM);
   std::free(m->h_y);
@@ -440,9 +650,11 @@ int dk_model_set_timing(dk_model* m, int on) {
   if (on && !m->ev0) {
     DK_CUDA_TRY(cudaEventCreate(&m->ev0));
     DK_CUDA_TRY(cudaEventCreate(&m->ev1));
+    DK_CUDA_TRY(cudaEventCreate(&m->ev_mid));
   }
   m->timing = on ? 1 : 0;
   m->ev_valid = false;
+  m->ev_mid_valid = false;
   return DK_OK;
 }
 
@@ -452,6 +664,15 @@ double dk_model_last_kernel_ms(dk_model* m) {
   if (cudaEventSynchronize(m->ev1) != cudaSuccess) return -1.0;
   float ms = -1.0f;
   if (cudaEventElapsedTime(&ms, m->ev0, m->ev1) != cudaSuccess) return -1.0;
+  return (double)ms;
+}
+
+double dk_model_last_phase_ms(dk_model* m) {
+  if (!m || !m->ev_valid || !m->ev_mid_valid) return -1.0;
+  DeviceGuard guard(m->device);
+  if (cudaEventSynchronize(m->ev_mid) != cudaSuccess) return -1.0;
+  float ms = -1.0f;
+  if (cudaEventElapsedTime(&ms, m->ev0, m->ev_mid) != cudaSuccess) return -1.0;
   return (double)ms;
 }
 
@@ -499,92 +720,77 @@ int dk_ei_grad_dev(dk_model* m, const double* d_x, int64_t N, double plugin, int
 }
 
 // ------------------------------------------------------------------------------------------
-// host-pointer entry points: H2D, launch, D2H on the handle's stream, then synchronise.
+// host-pointer entry points: chunked H2D -> kernel -> D2H pipeline (run_chunked), then synchronise.
+// The host_* forms work on rows [row0, row0 + n) of the caller's matrix and write the same rows of the caller's
+// outputs: a whole call is (0, N); the multi-GPU entry points (dk_api_multi.cu) hand every device its own range.
 // ------------------------------------------------------------------------------------------
+}  // extern "C"
 
-int dk_predict(dk_model* m, const double* x, int64_t N, int type, double* out_mean, double* out_sd) {
-  int rc = check_call(m, x, N);
-  if (rc) return rc;
-  if (!out_mean) return fail(DK_ERR_ARG, "out_mean is NULL");
+namespace dk {
+
+int host_predict(dk_model* m, const CritParams& P, const double* x, int64_t ldx, int64_t row0, int64_t n,
+                 double* out_main, double* out_mean, double* out_sd) {
   DeviceGuard guard(m->device);
-  HostCall h;
-  if ((rc = h.init(m, x, N, 2 * (size_t)N))) return rc;
-  if ((rc = dk_predict_dev(m, h.d_x, N, type, h.d_out, out_sd ? h.d_out + N : nullptr, m->stream))) return rc;
-  if ((rc = h.fetch(out_mean, h.d_out, N))) return rc;
-  if ((rc = h.fetch(out_sd, h.d_out + N, N))) return rc;
-  return h.finish();
+  const HostOut outs[3] = {{out_main, 1, ldx, false}, {out_mean, 1, ldx, false}, {out_sd, 1, ldx, false}};
+  int rc = run_chunked(m, x, ldx, row0, n, 1, chunk_units_for(m, 1, BN), outs, 3,
+                       [&](const double* d_x, int64_t rows, double* const* o, int64_t, cudaStream_t st) {
+                         return launch_predict(m, P, d_x, rows, o[0], o[1], o[2], st);
+                       });
+  if (rc) { cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
+  return rc;
 }
 
-int dk_ei(dk_model* m, const double* x, int64_t N, double plugin, int type, int minimization, int proxy,
-          double* out_ei, double* out_mean, double* out_sd) {
-  int rc = check_call(m, x, N);
-  if (rc) return rc;
-  if (!out_ei) return fail(DK_ERR_ARG, "out_ei is NULL");
+int host_grad(dk_model* m, const CritParams& P, const double* x, int64_t ldx, int64_t row0, int64_t n, double* out_grad,
+              double* out_main) {
   DeviceGuard guard(m->device);
-  HostCall h;
-  if ((rc = h.init(m, x, N, 3 * (size_t)N))) return rc;
-  double* d_ei = h.d_out;
-  double* d_mean = out_mean ? h.d_out + N : nullptr;
-  double* d_sd = out_sd ? h.d_out + 2 * N : nullptr;
-  if ((rc = dk_ei_dev(m, h.d_x, N, plugin, type, minimization, proxy, d_ei, d_mean, d_sd, m->stream))) return rc;
-  if ((rc = h.fetch(out_ei, d_ei, N))) return rc;
-  if ((rc = h.fetch(out_mean, d_mean, N))) return rc;
-  if ((rc = h.fetch(out_sd, d_sd, N))) return rc;
-  return h.finish();
+  int rc = ensure_bwd(m);
+  if (rc) return rc;
+  const HostOut outs[2] = {{out_grad, m->d, ldx, false}, {out_main, 1, ldx, false}};
+  rc = run_chunked(m, x, ldx, row0, n, 1, chunk_units_for(m, 1, BN), outs, 2,
+                   [&](const double* d_x, int64_t rows, double* const* o, int64_t, cudaStream_t st) {
+                     return launch_grad(m, P, d_x, rows, o[0], o[1], st);
+                   });
+  if (rc) { cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
+  return rc;
 }
 
-int dk_ei_grad(dk_model* m, const double* x, int64_t N, double plugin, int type, int minimization, int proxy,
-               double* out_grad, double* out_ei) {
-  int rc = check_call(m, x, N);
+namespace {
+int ensure_vec(dk_model* m, size_t doubles) {
+  if (m->vec_doubles >= doubles) return DK_OK;
+  dev_release(m, &m->d_vec, m->vec_doubles);
+  m->vec_doubles = 0;
+  int rc = dev_alloc(m, &m->d_vec, doubles);
   if (rc) return rc;
-  if (!out_grad) return fail(DK_ERR_ARG, "out_grad is NULL");
-  DeviceGuard guard(m->device);
-  HostCall h;
-  if ((rc = h.init(m, x, N, (size_t)N * (m->d + 1)))) return rc;
-  double* d_grad = h.d_out;
-  double* d_ei = h.d_out + (size_t)N * m->d;
-  if ((rc = dk_ei_grad_dev(m, h.d_x, N, plugin, type, minimization, proxy, d_grad, d_ei, m->stream))) return rc;
-  if ((rc = h.fetch(out_grad, d_grad, (size_t)N * m->d))) return rc;
-  if ((rc = h.fetch(out_ei, d_ei, N))) return rc;
-  return h.finish();
+  m->vec_doubles = doubles;
+  return DK_OK;
 }
+}  // namespace
 
-int dk_quantile(dk_model* m, const double* x, int64_t N, double qnorm_beta, int type, double* out_q, double* out_grad) {
-  int rc = check_call(m, x, N);
-  if (rc) return rc;
-  if (!out_q) return fail(DK_ERR_ARG, "out_q is NULL");
+// The screen of R/max_crit.R:104-110 over rows [row0, row0 + n): criterion P into a device vector (never copied
+// back), then the k best (value desc, index asc; indices relative to row0, -1 when fewer than k are comparable).
+int host_screen(dk_model* m, const CritParams& P, const double* x, int x_on_device, int64_t ldx, int64_t row0, int64_t n,
+                int k, int64_t* out_idx, double* out_val, cudaStream_t user_stream) {
   DeviceGuard guard(m->device);
-  HostCall h;
-  if ((rc = h.init(m, x, N, (size_t)N * (m->d + 1)))) return rc;
-  double* d_q = h.d_out;
-  double* d_grad = out_grad ? h.d_out + N + (N & 1) : nullptr;
-  if ((rc = dk_quantile_dev(m, h.d_x, N, qnorm_beta, type, d_q, d_grad, m->stream))) return rc;
-  if ((rc = h.fetch(out_q, d_q, N))) return rc;
-  if ((rc = h.fetch(out_grad, d_grad, (size_t)N * m->d))) return rc;
-  return h.finish();
-}
-
-int dk_screen_ei(dk_model* m, const double* x, int x_on_device, int64_t N, double plugin, int type, int minimization,
-                 int proxy, int k, int64_t* out_idx, double* out_val, void* stream) {
-  int rc = check_call(m, x, N);
+  int rc = ensure_vec(m, (size_t)std::max<int64_t>(n, 1));
   if (rc) return rc;
-  if (k < 1 || k > DK_TOPK_MAX) return fail(DK_ERR_ARG, "k=%d outside 1..%d", k, DK_TOPK_MAX);
-  if (!out_idx || !out_val) return fail(DK_ERR_ARG, "output pointer is NULL");
-  DeviceGuard guard(m->device);
-  cudaStream_t st = stream ? (cudaStream_t)stream : (x_on_device ? (cudaStream_t) nullptr : m->stream);
-  const size_t xin = x_on_device ? 0 : (size_t)N * m->d;
-  if ((rc = ensure_io(m, xin + (size_t)N + 16))) return rc;
-  const double* d_x = x;
-  if (!x_on_device) {
-    if (N > 0) DK_CUDA_TRY(cudaMemcpyAsync(m->d_io, x, xin * 8, cudaMemcpyHostToDevice, st));
-    d_x = m->d_io;
-  }
-  double* d_ei = m->d_io + ((xin + 1) & ~(size_t)1);
-  CritParams P{MODE_EI, type, minimization, proxy, plugin, 0.0};
-  if ((rc = launch_predict(m, P, d_x, N, d_ei, nullptr, nullptr, st))) return rc;
   if ((rc = ensure_red(m, topk_workspace_bytes(k)))) return rc;
-  if ((rc = launch_topk(d_ei, N, k, m->d_red, st))) return rc;
-  m->launches += 2;
+  cudaStream_t st = user_stream ? user_stream : (x_on_device ? (cudaStream_t) nullptr : m->stream);
+  if (x_on_device) {
+    if (ldx != n) return fail(DK_ERR_ARG, "device-resident candidates must be contiguous (ld = N)");
+    if ((rc = launch_predict(m, P, x, n, m->d_vec, nullptr, nullptr, st))) return rc;
+  } else {
+    if (user_stream) {  // the pipeline runs on the handle's streams: order it after the caller's stream
+      DK_CUDA_TRY(cudaStreamSynchronize(user_stream));
+      st = m->stream;
+    }
+    rc = run_chunked(m, x, ldx, row0, n, 1, chunk_units_for(m, 1, BN), nullptr, 0,
+                     [&](const double* d_x, int64_t rows, double* const*, int64_t u0, cudaStream_t s) {
+                       return launch_predict(m, P, d_x, rows, m->d_vec + u0, nullptr, nullptr, s);
+                     });
+    if (rc) { cudaStreamSynchronize(m->stream); return rc; }
+  }
+  if ((rc = launch_topk(m->d_vec, n, k, m->d_red, st))) return rc;
+  m->launches += k;
   std::vector<TopkEntry> host(k);
   DK_CUDA_TRY(cudaMemcpyAsync(host.data(), topk_result_ptr(m->d_red), sizeof(TopkEntry) * k, cudaMemcpyDeviceToHost, st));
   DK_CUDA_TRY(cudaStreamSynchronize(st));
@@ -593,6 +799,55 @@ int dk_screen_ei(dk_model* m, const double* x, int x_on_device, int64_t N, doubl
     out_val[i] = host[i].val;
   }
   return DK_OK;
+}
+
+}  // namespace dk
+
+extern "C" {
+
+int dk_predict(dk_model* m, const double* x, int64_t N, int type, double* out_mean, double* out_sd) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (!out_mean) return fail(DK_ERR_ARG, "out_mean is NULL");
+  CritParams P{MODE_PREDICT, type, 1, 0, 0.0, 0.0};
+  return host_predict(m, P, x, N, 0, N, nullptr, out_mean, out_sd);
+}
+
+int dk_ei(dk_model* m, const double* x, int64_t N, double plugin, int type, int minimization, int proxy,
+          double* out_ei, double* out_mean, double* out_sd) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (!out_ei) return fail(DK_ERR_ARG, "out_ei is NULL");
+  CritParams P{MODE_EI, type, minimization, proxy, plugin, 0.0};
+  return host_predict(m, P, x, N, 0, N, out_ei, out_mean, out_sd);
+}
+
+int dk_ei_grad(dk_model* m, const double* x, int64_t N, double plugin, int type, int minimization, int proxy,
+               double* out_grad, double* out_ei) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (!out_grad) return fail(DK_ERR_ARG, "out_grad is NULL");
+  CritParams P{MODE_EI, type, minimization, proxy, plugin, 0.0};
+  return host_grad(m, P, x, N, 0, N, out_grad, out_ei);
+}
+
+int dk_quantile(dk_model* m, const double* x, int64_t N, double qnorm_beta, int type, double* out_q, double* out_grad) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (!out_q) return fail(DK_ERR_ARG, "out_q is NULL");
+  CritParams P{MODE_QUANTILE, type, 1, 0, 0.0, qnorm_beta};
+  if (out_grad) return host_grad(m, P, x, N, 0, N, out_grad, out_q);
+  return host_predict(m, P, x, N, 0, N, out_q, nullptr, nullptr);
+}
+
+int dk_screen_ei(dk_model* m, const double* x, int x_on_device, int64_t N, double plugin, int type, int minimization,
+                 int proxy, int k, int64_t* out_idx, double* out_val, void* stream) {
+  int rc = check_call(m, x, N);
+  if (rc) return rc;
+  if (k < 1 || k > DK_TOPK_MAX) return fail(DK_ERR_ARG, "k=%d outside 1..%d", k, DK_TOPK_MAX);
+  if (!out_idx || !out_val) return fail(DK_ERR_ARG, "output pointer is NULL");
+  CritParams P{MODE_EI, type, minimization, proxy, plugin, 0.0};
+  return host_screen(m, P, x, x_on_device, N, 0, N, k, out_idx, out_val, (cudaStream_t)stream);
 }
 
 /* Debug aid (not part of the drop-in surface): the same criterion through the plain
@@ -708,12 +963,8 @@ extern "C" int dk_sample_weights(dk_model* m, const double* x, int64_t N, double
   int rc = check_call(m, x, N);
   if (rc) return rc;
   if (!out_w) return fail(DK_ERR_ARG, "out_w is NULL");
-  DeviceGuard guard(m->device);
-  HostCall h;
-  if ((rc = h.init(m, x, N, (size_t)N))) return rc;
-  if ((rc = dk_sample_weights_dev(m, h.d_x, N, T, minimization, h.d_out, m->stream))) return rc;
-  if ((rc = h.fetch(out_w, h.d_out, N))) return rc;
-  return h.finish();
+  CritParams P{MODE_EI_WEIGHT, DK_UK, minimization, 0, T, 0.0};  // the reference hard-codes type = "UK" here
+  return host_predict(m, P, x, N, 0, N, out_w, nullptr, nullptr);
 }
 
 #ifdef DK_PHASE_TIMING
@@ -751,24 +1002,18 @@ extern "C" int dk_aei(dk_model* m, const double* x, int64_t N, double y_min, dou
   int rc = check_call(m, x, N);
   if (rc) return rc;
   if (!out) return fail(DK_ERR_ARG, "out is NULL");
-  DeviceGuard guard(m->device);
-  HostCall h;
-  if ((rc = h.init(m, x, N, (size_t)N))) return rc;
-  if ((rc = dk_aei_dev(m, h.d_x, N, y_min, new_noise_var, type, h.d_out, m->stream))) return rc;
-  if ((rc = h.fetch(out, h.d_out, N))) return rc;
-  return h.finish();
+  if (!(new_noise_var >= 0)) return fail(DK_ERR_ARG, "new.noise.var must be >= 0");
+  CritParams P{MODE_AEI, type, 1, 0, y_min, 0.0, new_noise_var, m->dm.sd2};
+  return host_predict(m, P, x, N, 0, N, out, nullptr, nullptr);
 }
 extern "C" int dk_eqi(dk_model* m, const double* x, int64_t N, double q_min, double new_noise_var, double qnorm_beta, int type,
                       double* out) {
   int rc = check_call(m, x, N);
   if (rc) return rc;
   if (!out) return fail(DK_ERR_ARG, "out is NULL");
-  DeviceGuard guard(m->device);
-  HostCall h;
-  if ((rc = h.init(m, x, N, (size_t)N))) return rc;
-  if ((rc = dk_eqi_dev(m, h.d_x, N, q_min, new_noise_var, qnorm_beta, type, h.d_out, m->stream))) return rc;
-  if ((rc = h.fetch(out, h.d_out, N))) return rc;
-  return h.finish();
+  if (!(new_noise_var >= 0)) return fail(DK_ERR_ARG, "new.noise.var must be >= 0");
+  CritParams P{MODE_EQI, type, 1, 0, q_min, qnorm_beta, new_noise_var, m->dm.sd2};
+  return host_predict(m, P, x, N, 0, N, out, nullptr, nullptr);
 }
 
 // AEI.grad (R/AEI.grad.R:65-154) and EQI.grad (R/EQI.grad.R:66-146): the gradient kernel with other outer derivatives
@@ -797,22 +1042,16 @@ extern "C" int dk_aei_grad(dk_model* m, const double* x, int64_t N, double y_min
   int rc = check_call(m, x, N);
   if (rc) return rc;
   if (!out_grad) return fail(DK_ERR_ARG, "out_grad is NULL");
-  DeviceGuard guard(m->device);
-  HostCall h;
-  if ((rc = h.init(m, x, N, (size_t)N * (m->d + 1)))) return rc;
-  if ((rc = dk_aei_grad_dev(m, h.d_x, N, y_min, new_noise_var, type, h.d_out, h.d_out + (size_t)N * m->d, m->stream))) return rc;
-  if ((rc = h.fetch(out_grad, h.d_out, (size_t)N * m->d))) return rc;
-  return h.finish();
+  if (!(new_noise_var >= 0)) return fail(DK_ERR_ARG, "new.noise.var must be >= 0");
+  CritParams P{MODE_AEI, type, 1, 0, y_min, 0.0, new_noise_var, m->dm.sd2};
+  return host_grad(m, P, x, N, 0, N, out_grad, nullptr);
 }
 extern "C" int dk_eqi_grad(dk_model* m, const double* x, int64_t N, double q_min, double new_noise_var, double qnorm_beta,
                            int type, double* out_grad) {
   int rc = check_call(m, x, N);
   if (rc) return rc;
   if (!out_grad) return fail(DK_ERR_ARG, "out_grad is NULL");
-  DeviceGuard guard(m->device);
-  HostCall h;
-  if ((rc = h.init(m, x, N, (size_t)N * (m->d + 1)))) return rc;
-  if ((rc = dk_eqi_grad_dev(m, h.d_x, N, q_min, new_noise_var, qnorm_beta, type, h.d_out, h.d_out + (size_t)N * m->d, m->stream))) return rc;
-  if ((rc = h.fetch(out_grad, h.d_out, (size_t)N * m->d))) return rc;
-  return h.finish();
+  if (!(new_noise_var >= 0)) return fail(DK_ERR_ARG, "new.noise.var must be >= 0");
+  CritParams P{MODE_EQI, type, 1, 0, q_min, qnorm_beta, new_noise_var, m->dm.sd2};
+  return host_grad(m, P, x, N, 0, N, out_grad, nullptr);
 }

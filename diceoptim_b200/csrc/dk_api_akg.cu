@@ -35,12 +35,27 @@ int ensure_akg(dk_model* m) {
   for (int i = 0; i < n; i++) perm[i] = i;
   std::stable_sort(perm.begin(), perm.end(), [&](int u, int v) { return a[u] < a[v]; });
   for (int j = 0; j < n; j++) cst[j] = a[perm[j]];
-  int rc = dev_alloc(m, &m->d_akg_const, cst.size());
-  if (rc) return rc;
-  if ((rc = dev_alloc(m, &m->d_akg_perm, (size_t)n))) return rc;
-  DK_CUDA_TRY(cudaMemcpy(m->d_akg_const, cst.data(), cst.size() * 8, cudaMemcpyHostToDevice));
-  DK_CUDA_TRY(cudaMemcpy(m->d_akg_perm, perm.data(), (size_t)n * 4, cudaMemcpyHostToDevice));
-  if ((rc = dev_alloc(m, &m->d_akg_scratch, (size_t)m->grid * akg_scratch_doubles(n)))) return rc;
+  // locals first, published together: a failed call leaves the handle unchanged and the next call retries
+  double *d_const = nullptr, *d_scr = nullptr;
+  int* d_perm = nullptr;
+  const size_t scr_count = (size_t)m->grid * akg_scratch_doubles(n);
+  int rc = dev_alloc(m, &d_const, cst.size());
+  if (!rc) rc = dev_alloc(m, &d_perm, (size_t)n);
+  if (!rc) rc = dev_alloc(m, &d_scr, scr_count);
+  if (!rc) {
+    cudaError_t e = cudaMemcpy(d_const, cst.data(), cst.size() * 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_perm, perm.data(), (size_t)n * 4, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) rc = fail(DK_ERR_CUDA, "upload of the AKG constants failed: %s", cudaGetErrorString(e));
+  }
+  if (rc) {
+    dev_release(m, &d_const, cst.size());
+    dev_release(m, &d_perm, (size_t)n);
+    dev_release(m, &d_scr, scr_count);
+    return rc;
+  }
+  m->d_akg_perm = d_perm;
+  m->d_akg_scratch = d_scr;
+  m->d_akg_const = d_const;
   m->dm.akg_a_sorted = m->d_akg_const;
   m->dm.akg_delta = m->d_akg_const + n;
   m->dm.akg_perm = m->d_akg_perm;
@@ -67,22 +82,29 @@ extern "C" int dk_akg_dev(dk_model* m, const double* d_x, int64_t N, double new_
   k_akg_fused<false><<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, type, new_noise_var, d_x, N, ntiles, m->d_vscratch,
                                                       m->d_wscratch, m->scratch_doubles_per_cta, m->d_akg_scratch, d_out,
                                                       nullptr, nullptr, nullptr, nullptr);
-  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
+  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; m->ev_mid_valid = false; }
   m->launches++;
   DK_CUDA_TRY(cudaGetLastError());
   return DK_OK;
+}
+
+int dk::host_akg(dk_model* m, const double* x, int64_t ldx, int64_t row0, int64_t n, double new_noise_var, int type,
+                 double* out) {
+  DeviceGuard guard(m->device);
+  const HostOut outs[1] = {{out, 1, ldx, false}};
+  int rc = run_chunked(m, x, ldx, row0, n, 1, chunk_units_for(m, 1, BN), outs, 1,
+                       [&](const double* d_x, int64_t rows, double* const* o, int64_t, cudaStream_t st) {
+                         return dk_akg_dev(m, d_x, rows, new_noise_var, type, o[0], st);
+                       });
+  if (rc) { cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
+  return rc;
 }
 
 extern "C" int dk_akg(dk_model* m, const double* x, int64_t N, double new_noise_var, int type, double* out) {
   int rc = check_call(m, x, N);
   if (rc) return rc;
   if (!out) return fail(DK_ERR_ARG, "out is NULL");
-  DeviceGuard guard(m->device);
-  HostCall h;
-  if ((rc = h.init(m, x, N, (size_t)N))) return rc;
-  if ((rc = dk_akg_dev(m, h.d_x, N, new_noise_var, type, h.d_out, m->stream))) return rc;
-  if ((rc = h.fetch(out, h.d_out, N))) return rc;
-  return h.finish();
+  return host_akg(m, x, N, 0, N, new_noise_var, type, out);
 }
 
 
@@ -90,7 +112,9 @@ extern "C" int dk_akg(dk_model* m, const double* x, int64_t N, double new_noise_
 // AKG.grad (R/AKG.grad.R:65-281)
 // ------------------------------------------------------------------------------------------
 namespace {
-int ensure_akg_grad(dk_model* m) {
+// K^-1 is built on the CALLER's stream (it shares the V / W panels with whatever that stream already holds for this
+// handle, and the *_dev contract is "enqueue without synchronising"); the first call still allocates.
+int ensure_akg_grad(dk_model* m, cudaStream_t st) {
   static bool attr_done[64] = {};
   if (m->device < 64 && !attr_done[m->device]) {
     DK_CUDA_TRY(cudaFuncSetAttribute(k_akg_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
@@ -104,11 +128,10 @@ int ensure_akg_grad(dk_model* m) {
     if ((rc = dev_alloc(m, &m->d_Kinv, n * n))) return rc;
     const int64_t ntiles = ((int64_t)n + BN - 1) / BN;
     const int grid = (int)std::min<int64_t>(ntiles, m->grid);
-    k_kinv<<<grid, NT, SM_TOTAL + PIPE_SMEM, m->stream>>>(m->dm, ntiles, m->d_vscratch, m->d_wscratch,
-                                                          m->scratch_doubles_per_cta, m->d_Kinv);
+    k_kinv<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, ntiles, m->d_vscratch, m->d_wscratch,
+                                                   m->scratch_doubles_per_cta, m->d_Kinv);
     m->launches++;
     DK_CUDA_TRY(cudaGetLastError());
-    DK_CUDA_TRY(cudaStreamSynchronize(m->stream));
   }
   return DK_OK;
 }
@@ -125,15 +148,15 @@ extern "C" int dk_akg_grad_dev(dk_model* m, const double* d_x, int64_t N, double
   DeviceGuard guard(m->device);
   if ((rc = ensure_bwd(m))) return rc;
   if ((rc = ensure_akg(m))) return rc;
-  if ((rc = ensure_akg_grad(m))) return rc;
   cudaStream_t st = (cudaStream_t)stream;
+  if ((rc = ensure_akg_grad(m, st))) return rc;
   const int64_t ntiles = (N + BN - 1) / BN;
   const int grid = (int)std::min<int64_t>(ntiles, m->grid);
   if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
   k_akg_fused<true><<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, type, new_noise_var, d_x, N, ntiles, m->d_vscratch,
                                                      m->d_wscratch, m->scratch_doubles_per_cta, m->d_akg_scratch, d_akg,
                                                      m->d_cscratch, m->d_Kinv, m->d_akg_gscratch, d_grad);
-  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
+  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; m->ev_mid_valid = false; }
   m->launches++;
   DK_CUDA_TRY(cudaGetLastError());
   return DK_OK;
@@ -145,12 +168,11 @@ extern "C" int dk_akg_grad(dk_model* m, const double* x, int64_t N, double new_n
   if (rc) return rc;
   if (!out_grad) return fail(DK_ERR_ARG, "out_grad is NULL");
   DeviceGuard guard(m->device);
-  HostCall h;
-  if ((rc = h.init(m, x, N, (size_t)N * (m->d + 1)))) return rc;
-  double* d_grad = h.d_out;
-  double* d_akg = h.d_out + (size_t)N * m->d;
-  if ((rc = dk_akg_grad_dev(m, h.d_x, N, new_noise_var, type, d_grad, d_akg, m->stream))) return rc;
-  if ((rc = h.fetch(out_grad, d_grad, (size_t)N * m->d))) return rc;
-  if ((rc = h.fetch(out_akg, d_akg, N))) return rc;
-  return h.finish();
+  const HostOut outs[2] = {{out_grad, m->d, N, false}, {out_akg, 1, N, false}};
+  rc = run_chunked(m, x, N, 0, N, 1, chunk_units_for(m, 1, BN), outs, 2,
+                   [&](const double* d_x, int64_t rows, double* const* o, int64_t, cudaStream_t st) {
+                     return dk_akg_grad_dev(m, d_x, rows, new_noise_var, type, o[0], o[1], st);
+                   });
+  if (rc) { cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
+  return rc;
 }

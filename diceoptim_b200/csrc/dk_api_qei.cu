@@ -49,15 +49,33 @@ extern "C" int dk_qei_dev(dk_model* m, const double* d_x, int64_t B, int q, doub
   k_qei_moments<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, type, q, d_x, B, ntiles, m->d_vscratch, m->scratch_doubles_per_cta,
                                              m->d_aux, m->d_mom);
   DK_CUDA_TRY(cudaGetLastError());
+  if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev_mid, st));
   static const int64_t warp_below = [] { const char* e = std::getenv("DK_QEI_WARP_BELOW"); return e ? std::atoll(e) : (int64_t)12288; }();  // measured crossover (cfg3): 2048 batches 0.64 vs 2.06 ms, 18944: 5.4 vs 5.0 ms
   if (B < warp_below)  // few batches: a warp per batch (path-integral nodes spread over lanes) hides latency better
     k_qei_cdf_warp<<<(unsigned)((B + 3) / 4), 128, 0, st>>>(m->d_mom, B, q, plugin, minimization, d_out);
   else
     k_qei_cdf<<<(unsigned)((B * 4 + 127) / 128), 128, 0, st>>>(m->d_mom, B, q, plugin, minimization, d_out);
-  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
+  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; m->ev_mid_valid = true; }
   m->launches += 2;
   DK_CUDA_TRY(cudaGetLastError());
   return DK_OK;
+}
+
+// Batches [b0, b0 + nb) of the caller's (B q) x d matrix (leading dimension ldx = B q): qEI values into out[b] and / or
+// qEI.grad rows into out_grad (leading dimension ldx), through the chunked pipeline (whole tiles of QB batches).
+int dk::host_qei(dk_model* m, const double* x, int64_t ldx, int64_t b0, int64_t nb, int q, double plugin, int type,
+                 int minimization, double* out, double* out_grad) {
+  DeviceGuard guard(m->device);
+  const HostOut outs[2] = {{out, 1, ldx, true}, {out_grad, m->d, ldx, false}};
+  int rc = run_chunked(m, x, ldx, b0 * q, nb, q, chunk_units_for(m, q, QB), outs, 2,
+                       [&](const double* d_x, int64_t rows, double* const* o, int64_t, cudaStream_t st) {
+                         int r = DK_OK;
+                         if (o[0]) r = dk_qei_dev(m, d_x, rows / q, q, plugin, type, minimization, o[0], st);
+                         if (!r && o[1]) r = dk_qei_grad_dev(m, d_x, rows / q, q, plugin, type, minimization, o[1], st);
+                         return r;
+                       });
+  if (rc) { cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
+  return rc;
 }
 
 extern "C" int dk_qei(dk_model* m, const double* x, int64_t B, int q, double plugin, int type, int minimization,
@@ -66,12 +84,7 @@ extern "C" int dk_qei(dk_model* m, const double* x, int64_t B, int q, double plu
   if (rc) return rc;
   if (q < 1 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI batch size q=%d outside 1..%d", q, DK_MAX_Q);
   if (!out) return fail(DK_ERR_ARG, "out is NULL");
-  DeviceGuard guard(m->device);
-  HostCall h;
-  if ((rc = h.init(m, x, B * q, (size_t)B))) return rc;
-  if ((rc = dk_qei_dev(m, h.d_x, B, q, plugin, type, minimization, h.d_out, m->stream))) return rc;
-  if ((rc = h.fetch(out, h.d_out, B))) return rc;
-  return h.finish();
+  return host_qei(m, x, B * q, 0, B, q, plugin, type, minimization, out, nullptr);
 }
 
 extern "C" int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type,
@@ -102,10 +115,11 @@ extern "C" int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q,
   k_qei_grad_moments<<<grid, NT, SM_TOTAL + PIPE_SMEM, st>>>(m->dm, type, q, d_x, B, ntiles, m->d_vscratch, m->d_wscratch,
                                                   m->d_cscratch, m->scratch_doubles_per_cta, m->d_aux, m->d_mom, m->d_deriv);
   DK_CUDA_TRY(cudaGetLastError());
+  if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev_mid, st));
   const int64_t threads = B * 4;
   k_qei_grad_cdf<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(m->d_mom, m->d_deriv, B, q, m->d, plugin, minimization,
                                                                    m->dm.sd2, d_grad);
-  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; }
+  if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; m->ev_mid_valid = true; }
   m->launches += 2;
   DK_CUDA_TRY(cudaGetLastError());
   return DK_OK;
@@ -117,12 +131,7 @@ extern "C" int dk_qei_grad(dk_model* m, const double* x, int64_t B, int q, doubl
   if (rc) return rc;
   if (q < 2 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI.grad batch size q=%d outside 2..%d (use dk_ei_grad for q = 1)", q, DK_MAX_Q);
   if (!out_grad) return fail(DK_ERR_ARG, "out_grad is NULL");
-  DeviceGuard guard(m->device);
-  HostCall h;
-  if ((rc = h.init(m, x, B * q, (size_t)B * q * m->d))) return rc;
-  if ((rc = dk_qei_grad_dev(m, h.d_x, B, q, plugin, type, minimization, h.d_out, m->stream))) return rc;
-  if ((rc = h.fetch(out_grad, h.d_out, (size_t)B * q * m->d))) return rc;
-  return h.finish();
+  return host_qei(m, x, B * q, 0, B, q, plugin, type, minimization, nullptr, out_grad);
 }
 
 /* Test hook: pmnorm(h_b, varcov = S_b) for B independent q-variate problems (q <= 4), host pointers,

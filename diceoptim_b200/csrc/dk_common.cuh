@@ -119,6 +119,7 @@ struct dk_model {
   double* d_tiles_bwd = nullptr;
   double* d_Xrm = nullptr;
   double* d_small = nullptr;     // beta | RM | tuuinv | alpha | KinvF | noise_var
+  size_t tiles_fwd_doubles = 0, xrm_doubles = 0, small_doubles = 0;  // sizes of the three uploads (dk_model_clone)
   double* d_vscratch = nullptr;  // per-CTA V panels (forward solve), grid x n_pad x 64 doubles
   double* d_wscratch = nullptr;  // per-CTA W panels (backward solve)
   double* d_cscratch = nullptr;  // per-CTA covariance panels kept for the gradient kernels
@@ -132,6 +133,15 @@ struct dk_model {
   // grow-only staging for the host entry points
   double* d_io = nullptr;
   size_t io_doubles = 0;
+  // chunked host<->device pipeline of the host entry points (run_chunked): two slots of pinned staging and of device
+  // chunk buffers, one stream per direction
+  double* h_stage = nullptr;     // pinned, 2 x (in + out)
+  size_t stage_in_doubles = 0, stage_out_doubles = 0;
+  double* d_chunk = nullptr;     // device, 2 x (in + out)
+  cudaStream_t copy_in = nullptr, copy_out = nullptr;
+  cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_kern[2] = {nullptr, nullptr}, ev_d2h[2] = {nullptr, nullptr};
+  double* d_vec = nullptr;       // device vector of one criterion value per candidate (screens), grow-only
+  size_t vec_doubles = 0;
   void* d_red = nullptr;         // argmax partials
   size_t red_bytes = 0;
   cudaStream_t stream = nullptr;
@@ -151,6 +161,6 @@ struct dk_model {
   double* d_knyy[2] = {nullptr, nullptr};  // sd(X_j)^2 per type (SK, UK), checkPredict covdist
   long long launches = 0;        // kernels launched through this handle
   int timing = 0;                // bracket the solve kernel with events
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  bool ev_valid = false;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_mid = nullptr;  // ev_mid: between the two kernels of a two-kernel call
+  bool ev_valid = false, ev_mid_valid = false;
 };

@@ -6,6 +6,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <new>
 #include <vector>
 
@@ -64,7 +65,41 @@ int launch_predict(dk_model* m, const CritParams& P, const double* d_x, int64_t 
 int launch_grad(dk_model* m, const CritParams& P, const double* d_x, int64_t N, double* d_grad, double* d_main,
                 cudaStream_t st);
 
-// host-pointer entry points: H2D, launch, D2H on the handle's stream, then synchronise
+// ---- chunked, double-buffered host <-> device pipeline of the host entry points ----
+// The caller's matrix x is column-major with leading dimension ldx (R's N x d: ldx = N); rows [row0, row0 + nunits * unit)
+// are processed in chunks of `chunk_units` units (unit = 1 candidate, or q rows of a qEI batch).  Each chunk's rows are
+// gathered into pinned staging by the calling thread, copied to the device on the handle's copy-in stream, handed to
+// `launch` on the handle's compute stream, and the outputs come back on the copy-out stream: the copies of chunk i + 1
+// and i - 1 overlap the kernels of chunk i, the caller's memory may be pageable (an R vector is), device memory is two
+// chunks whatever N, and a shard of a larger matrix (multi-GPU split) is just another (row0, nunits).
+struct HostOut {
+  double* host;    // base of the caller's WHOLE output array (NULL: this output is not wanted)
+  int cols;        // columns (1, d, ...)
+  int64_t ld;      // leading dimension of the caller's array
+  bool per_unit;   // one row per unit (qEI value) instead of one per x row
+};
+// launch(d_x, rows, d_out[nouts], unit0, stream): d_x is rows x d column-major (ld = rows); d_out[j] is cols_j x count
+// column-major (ld = count) or NULL when outs[j].host is NULL; unit0 = index of the chunk's first unit within this call.
+using ChunkLaunch = std::function<int(const double*, int64_t, double* const*, int64_t, cudaStream_t)>;
+int run_chunked(dk_model* m, const double* x, int64_t ldx, int64_t row0, int64_t nunits, int unit, int64_t chunk_units,
+                const HostOut* outs, int nouts, const ChunkLaunch& launch);
+// chunk size (in units) for tiles of `tile_units` units: whole waves of the persistent grid, about 24 MB of input
+int64_t chunk_units_for(const dk_model* m, int unit, int tile_units);
+
+// Host-pointer forms over rows [row0, row0 + n) of the caller's column-major matrix (leading dimension ldx); outputs
+// are the caller's whole arrays, written at the same rows (gradients: n x d with leading dimension ldx).
+int host_predict(dk_model* m, const CritParams& P, const double* x, int64_t ldx, int64_t row0, int64_t n,
+                 double* out_main, double* out_mean, double* out_sd);
+int host_grad(dk_model* m, const CritParams& P, const double* x, int64_t ldx, int64_t row0, int64_t n, double* out_grad,
+              double* out_main);
+int host_screen(dk_model* m, const CritParams& P, const double* x, int x_on_device, int64_t ldx, int64_t row0, int64_t n,
+                int k, int64_t* out_idx, double* out_val, cudaStream_t user_stream);
+int host_akg(dk_model* m, const double* x, int64_t ldx, int64_t row0, int64_t n, double new_noise_var, int type,
+             double* out);                                                       // dk_api_akg.cu
+int host_qei(dk_model* m, const double* x, int64_t ldx, int64_t b0, int64_t nb, int q, double plugin, int type,
+             int minimization, double* out, double* out_grad);                    // dk_api_qei.cu
+
+// small calls (a few launches on one staged copy of x): H2D, launches, D2H on the handle's stream, then synchronise
 struct HostCall {
   dk_model* m;
   double* d_x;

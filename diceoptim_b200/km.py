@@ -72,31 +72,75 @@ def _ptr(a):
     return None if a is None else a.ctypes.data_as(_lib.c_double_p)
 
 
+def make_desc(km: "KM", device: int = 0):
+    """(dk_model_desc, keep-alive dict of the arrays it points to) for a km object."""
+    if km.covariance.name not in KERNEL_IDS:
+        raise ValueError(f"covariance kernel {km.covariance.name!r} is not a covTensorProduct kernel "
+                         f"the engine supports {sorted(KERNEL_IDS)}")
+    if km.trend not in TREND_IDS:
+        raise ValueError(f"trend {km.trend!r} not supported (const = ~1, linear = ~.)")
+    cov = km.covariance
+    keep = dict(
+        theta=_f64(np.broadcast_to(cov.range_val, (km.d,)).copy()),
+        shape=None if cov.shape_val is None else _f64(cov.shape_val),
+        noise_var=None if km.noise_var is None else _f64(km.noise_var),
+        T=_f64(km.T), z=_f64(km.z), M=_f64(np.atleast_2d(km.M).reshape(km.n, km.p)),
+        X=_f64(km.X), y=_f64(km.y), F=_f64(km.F), beta=_f64(km.trend_coef),
+    )
+    desc = _lib.dk_model_desc(
+        n=km.n, d=km.d, p=km.p, kernel=KERNEL_IDS[cov.name], trend=TREND_IDS[km.trend], sd2=float(cov.sd2),
+        theta=_ptr(keep["theta"]), shape=_ptr(keep["shape"]), nugget=float(cov.nugget),
+        nugget_flag=int(bool(cov.nugget_flag)), noise_var=_ptr(keep["noise_var"]),
+        T=_ptr(keep["T"]), z=_ptr(keep["z"]), M=_ptr(keep["M"]), X=_ptr(keep["X"]), y=_ptr(keep["y"]),
+        F=_ptr(keep["F"]), beta=_ptr(keep["beta"]), device=device)
+    return desc, keep
+
+
+class MultiDeviceModel:
+    """Owns one dk_multi* (include/dk_b200.h): the model replicated on several GPUs of this process.
+    ``devices``: list of CUDA ordinals, or an int = the first that many visible devices (0: all)."""
+
+    def __init__(self, km: "KM", devices=0):
+        lib = _lib.load()
+        desc, keep = make_desc(km)
+        out = C.c_void_p()
+        if isinstance(devices, int):
+            rc = lib.dk_multi_create(C.byref(desc), None, devices, C.byref(out))
+        else:
+            arr = (C.c_int * len(devices))(*devices)
+            rc = lib.dk_multi_create(C.byref(desc), arr, len(devices), C.byref(out))
+        _lib.check(rc, "dk_multi_create")
+        self._h, self._lib = out, lib
+        self.n, self.d, self.p = km.n, km.d, km.p
+
+    @property
+    def ptr(self):
+        if self._h is None:
+            raise _lib.DkError("multi-device model already destroyed")
+        return self._h
+
+    def count(self) -> int:
+        return int(self._lib.dk_multi_count(self.ptr))
+
+    def close(self):
+        if self._h is not None:
+            self._lib.dk_multi_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class DeviceModel:
     """Owns one dk_model* (include/dk_b200.h).  Not thread-safe; calls on it must not overlap."""
 
     def __init__(self, km: KM, device: int = 0):
         lib = _lib.load()
-        if km.covariance.name not in KERNEL_IDS:
-            raise ValueError(f"covariance kernel {km.covariance.name!r} is not a covTensorProduct kernel "
-                             f"the engine supports {sorted(KERNEL_IDS)}")
-        if km.trend not in TREND_IDS:
-            raise ValueError(f"trend {km.trend!r} not supported (const = ~1, linear = ~.)")
         self.n, self.d, self.p, self.device = km.n, km.d, km.p, device
-        cov = km.covariance
-        keep = dict(
-            theta=_f64(np.broadcast_to(cov.range_val, (km.d,)).copy()),
-            shape=None if cov.shape_val is None else _f64(cov.shape_val),
-            noise_var=None if km.noise_var is None else _f64(km.noise_var),
-            T=_f64(km.T), z=_f64(km.z), M=_f64(np.atleast_2d(km.M).reshape(km.n, km.p)),
-            X=_f64(km.X), y=_f64(km.y), F=_f64(km.F), beta=_f64(km.trend_coef),
-        )
-        desc = _lib.dk_model_desc(
-            n=km.n, d=km.d, p=km.p, kernel=KERNEL_IDS[cov.name], trend=TREND_IDS[km.trend], sd2=float(cov.sd2),
-            theta=_ptr(keep["theta"]), shape=_ptr(keep["shape"]), nugget=float(cov.nugget),
-            nugget_flag=int(bool(cov.nugget_flag)), noise_var=_ptr(keep["noise_var"]),
-            T=_ptr(keep["T"]), z=_ptr(keep["z"]), M=_ptr(keep["M"]), X=_ptr(keep["X"]), y=_ptr(keep["y"]),
-            F=_ptr(keep["F"]), beta=_ptr(keep["beta"]), device=device)
+        desc, keep = make_desc(km, device)
         out = C.c_void_p()
         _lib.check(lib.dk_model_create(C.byref(desc), C.byref(out)), "dk_model_create")
         self._h = out

@@ -8,7 +8,8 @@
  *
  * Conventions (R's): all matrices are COLUMN-MAJOR doubles.  Candidates `x` are N x d
  * (coordinate k of candidate j at x[j + k*N]); gradients are N x d likewise.
- * Host entry points take HOST pointers and do the host<->device copies themselves;
+ * Host entry points take HOST pointers (pageable memory is fine) and stream the candidates through the device in
+ * chunks: the host<->device copies overlap the kernels and the device holds two chunks whatever N;
  * the *_dev entry points take DEVICE pointers on the model's device and enqueue on `stream`
  * (a cudaStream_t passed as void*; NULL = the default stream) without synchronising.
  * One model handle is bound to one CUDA device; calls on one handle must not overlap
@@ -87,6 +88,9 @@ long long dk_model_launches(const dk_model* m);
  * dk_model_last_kernel_ms returns the device time of the most recent completed one, < 0 if none. */
 int dk_model_set_timing(dk_model* m, int on);
 double dk_model_last_kernel_ms(dk_model* m);
+/* For calls made of two kernels (dk_qei_dev: moments, then CDFs): device time of the FIRST kernel of the most recent
+ * timed call, < 0 if that call had a single kernel. */
+double dk_model_last_phase_ms(dk_model* m);
 
 /* predict.km(light.return=TRUE): mean and sd — replaces the DiceKriging call at
  * /root/reference/R/EI.R:112-116 and R/sampleFromEI.R:109.  out_sd may be NULL. */
@@ -235,6 +239,39 @@ int dk_feasible_improvement(dk_model* fun, dk_model* const* cst, int n_cst, cons
 int dk_crit_sur_cst(dk_model* fun, dk_model* const* cst, int n_cst, const double* x, int64_t N,
                     const double* integration_points, int64_t Mi, const double* integration_weights, double obj_min,
                     int type, const int* equality, const double* tol, double* out);
+
+/* ---- One model on several GPUs of this process (SURVEY 8(b) "copies ... to every selected GPU", 8(e)) ----
+ * R cannot fork CUDA contexts, so the reference's only parallelism (mclapply over restarts,
+ * /root/reference/R/max_crit.R:125) is replaced by a split INSIDE the library: candidates (qEI: batches) are cut into
+ * contiguous ranges, one per device (sizes differ by at most one), one host thread per device streams its range of the
+ * caller's arrays through that device and writes the same range of the caller's outputs.  Results are bit-identical
+ * to the single-device entry points (every candidate is evaluated by the same kernel; the top-k merge keeps the lower
+ * index on ties, i.e. which.max's first maximum).  The model is tiled once on the host and copied device to device. */
+typedef struct dk_multi dk_multi;
+/* devices: ndev CUDA ordinals, or NULL for the first ndev visible devices (all of them when ndev <= 0);
+ * desc->device is ignored.  An ordinal may appear more than once (the replicas then share that device: no speed-up,
+ * but the split and merge run as they would on separate GPUs, which is how the single-GPU tests cover them). */
+int dk_multi_create(const dk_model_desc* desc, const int* devices, int ndev, dk_multi** out);
+void dk_multi_destroy(dk_multi* mm);
+int dk_multi_count(const dk_multi* mm);
+/* The single-device handle of replica i (owned by mm), e.g. for the *_dev entry points. */
+dk_model* dk_multi_model(dk_multi* mm, int i);
+/* A replica of an existing handle on another device (device-to-device copy of the tiled model). */
+int dk_model_clone(const dk_model* src, int device, dk_model** out);
+/* Host-pointer criteria, same arguments and results as dk_predict / dk_ei / dk_ei_grad / dk_quantile / dk_akg / dk_qei
+ * (+ dk_qei_grad: out or out_grad may be NULL) / dk_screen_ei. */
+int dk_multi_predict(dk_multi* mm, const double* x, int64_t N, int type, double* out_mean, double* out_sd);
+int dk_multi_ei(dk_multi* mm, const double* x, int64_t N, double plugin, int type, int minimization, int proxy,
+                double* out_ei, double* out_mean, double* out_sd);
+int dk_multi_ei_grad(dk_multi* mm, const double* x, int64_t N, double plugin, int type, int minimization, int proxy,
+                     double* out_grad, double* out_ei);
+int dk_multi_quantile(dk_multi* mm, const double* x, int64_t N, double qnorm_beta, int type, double* out_q,
+                      double* out_grad);
+int dk_multi_akg(dk_multi* mm, const double* x, int64_t N, double new_noise_var, int type, double* out);
+int dk_multi_qei(dk_multi* mm, const double* x, int64_t B, int q, double plugin, int type, int minimization,
+                 double* out, double* out_grad);
+int dk_multi_screen_ei(dk_multi* mm, const double* x, int64_t N, double plugin, int type, int minimization, int proxy,
+                       int k, int64_t* out_idx, double* out_val);
 
 #ifdef __cplusplus
 }

@@ -128,8 +128,10 @@ def kriging_quantile_grad(x, model, beta=0.1, type="UK", envir=None):
     return mk_grad + qnorm(beta) * sk_grad
 
 
-def AKG(x, model, new_noise_var=0.0, type="UK", envir=None):
-    """R/AKG.R:93-229 at ONE point (approximate knowledge gradient, written for maximisation)."""
+def AKG(x, model, new_noise_var=0.0, type="UK", envir=None, predX=None):
+    """R/AKG.R:93-229 at ONE point (approximate knowledge gradient, written for maximisation).
+    predX: optional cache of predict_km(model, model.X, type), the candidate-independent prediction of :121 that the
+    reference recomputes on every call; passing it changes no arithmetic (used by tests at n = 5000)."""
     x = np.asarray(x, float).ravel()
     if x.size != model.d:
         raise ValueError("x does not have the right size")
@@ -142,7 +144,8 @@ def AKG(x, model, new_noise_var=0.0, type="UK", envir=None):
     sd2 = model.covariance.sd2
     if sk_x < np.sqrt(sd2) / 1e6 or sd2 < 1e-20:           # :115
         return 0.0
-    predX = dk.predict_km(model, model.X, type=type)       # :121 (candidate independent)
+    if predX is None:
+        predX = dk.predict_km(model, model.X, type=type)   # :121 (candidate independent)
     mk_X = predX["mean"]; V_X = predX["Tinv.c"]
     F_X = model.F
     m_min = min(np.min(mk_X), mk_x)

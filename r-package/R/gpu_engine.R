@@ -2,30 +2,49 @@
 ## Signatures are the reference's (R/EI.R:80, R/EI.grad.R:97, R/qEI.R:119, R/qEI.grad.R:267, R/AKG.R:93,
 ## R/kriging.quantile.R:92); only the bodies change.  Untested here: the build image has no R.
 
+## Handle cache.  The key hashes everything the device handle depends on (design, response, z, M, trend and covariance
+## parameters, diag(T): dkR_model_key, O(n d) per call), so two km objects on the same design with different y / z /
+## trend.coef never share a handle.  At most getOption("DiceOptim.gpu.cache", 4) handles are kept; the least recently
+## used one is released (device memory freed at once, not at the next gc()).  dk_release() empties the cache.
+## Devices: getOption("DiceOptim.gpu.devices", 0L): an integer vector of CUDA ordinals, or NA for every visible GPU;
+## with several devices every criterion call splits its rows over them inside the library.
 .dk_cache <- new.env(parent = emptyenv())
+.dk_cache$handles <- list()     # key -> external pointer, most recently used LAST
 
-dk_handle <- function(model, device = 0L) {
-  key <- paste0(digest_T(model@T), "@", device)
-  h <- .dk_cache[[key]]
+.dk_slots <- function(model) {
+  cov <- model@covariance
+  kern <- match(cov@name, c("gauss", "exp", "matern3_2", "matern5_2", "powexp")) - 1L
+  if (is.na(kern)) stop("covariance kernel not supported by the GPU engine: ", cov@name)
+  trend <- if (model@trend.formula == ~1) 0L else if (ncol(model@F) == model@d + 1L) 1L else
+    stop("only trend formulas ~1 and ~. are supported by the GPU engine")
+  list(T = model@T, z = as.numeric(model@z), M = as.matrix(model@M), X = as.matrix(model@X),
+       y = as.numeric(model@y), F = as.matrix(model@F), trend.coef = as.numeric(model@trend.coef),
+       range.val = as.numeric(cov@range.val),
+       shape.val = if (cov@name == "powexp") as.numeric(cov@shape.val) else numeric(0),
+       noise.var = if (model@noise.flag) as.numeric(model@noise.var) else numeric(0),
+       n = model@n, d = model@d, p = ncol(model@F), kernel = kern, trend = trend, sd2 = cov@sd2,
+       nugget = if (cov@nugget.flag) cov@nugget else 0, nugget.flag = cov@nugget.flag)
+}
+
+dk_handle <- function(model, devices = getOption("DiceOptim.gpu.devices", 0L)) {
+  slots <- .dk_slots(model)
+  key <- paste0(.Call("dkR_model_key", slots), "@", paste(devices, collapse = ","))
+  hs <- .dk_cache$handles
+  h <- hs[[key]]
   if (is.null(h)) {
-    cov <- model@covariance
-    kern <- match(cov@name, c("gauss", "exp", "matern3_2", "matern5_2", "powexp")) - 1L
-    if (is.na(kern)) stop("covariance kernel not supported by the GPU engine: ", cov@name)
-    trend <- if (model@trend.formula == ~1) 0L else if (ncol(model@F) == model@d + 1L) 1L else
-      stop("only trend formulas ~1 and ~. are supported by the GPU engine")
-    slots <- list(T = model@T, z = as.numeric(model@z), M = as.matrix(model@M), X = as.matrix(model@X),
-                  y = as.numeric(model@y), F = as.matrix(model@F), trend.coef = as.numeric(model@trend.coef),
-                  range.val = as.numeric(cov@range.val),
-                  shape.val = if (cov@name == "powexp") as.numeric(cov@shape.val) else numeric(0),
-                  noise.var = if (model@noise.flag) as.numeric(model@noise.var) else numeric(0),
-                  n = model@n, d = model@d, p = ncol(model@F), kernel = kern, trend = trend, sd2 = cov@sd2,
-                  nugget = if (cov@nugget.flag) cov@nugget else 0, nugget.flag = cov@nugget.flag)
-    h <- .Call("dkR_model_create", slots, as.integer(device))
-    .dk_cache[[key]] <- h
-  }
+    keep <- max(1L, as.integer(getOption("DiceOptim.gpu.cache", 4L)))
+    while (length(hs) >= keep) { .Call("dkR_release", hs[[1]]); hs[[1]] <- NULL }
+    h <- .Call("dkR_model_create", slots, as.integer(devices))
+  } else hs[[key]] <- NULL
+  hs[[key]] <- h                 # (re)insert at the end: most recently used
+  .dk_cache$handles <- hs
   h
 }
-digest_T <- function(T) paste(dim(T)[1], format(sum(T), digits = 17), format(T[length(T)], digits = 17))
+dk_release <- function() {
+  for (h in .dk_cache$handles) .Call("dkR_release", h)
+  .dk_cache$handles <- list()
+  invisible(NULL)
+}
 .type_id <- function(type) c(SK = 0L, UK = 1L)[[type]]
 .as_rows <- function(x, d) { if (is.null(dim(x))) x <- matrix(as.numeric(x), nrow = 1)
   if (ncol(x) != d) stop("x does not have the right size"); storage.mode(x) <- "double"; as.matrix(x) }
@@ -99,4 +118,100 @@ crit_EFI <- function(x, model.fun, model.constraint, equality = FALSE, critcontr
   out[checkPredict(x, c(model.constraint, model.fun), type = type, distance = critcontrol$distance,
                    threshold = critcontrol$threshold)] <- 0
   out
+}
+
+## ---- the rest of the noisy-criteria family (R/AKG.grad.R:65, R/AEI.R:105, R/AEI.grad.R:65, R/EQI.R:100, R/EQI.grad.R:66) ----
+AKG.grad <- function(x, model, new.noise.var = 0, type = "UK", envir = NULL) {
+  g <- .Call("dkR_akg_grad", dk_handle(model), .as_rows(x, model@d), new.noise.var, .type_id(type))[[1]]
+  if (is.null(dim(x))) as.numeric(g) else g
+}
+.dk_predict <- function(model, newdata, type = "UK") {
+  r <- .Call("dkR_predict", dk_handle(model), .as_rows(newdata, model@d), .type_id(type))
+  list(mean = r[[1]], sd = r[[2]])
+}
+.default_y_min <- function(model, type) {          # R/AEI.R:113-118: mk at the design point minimising mk + qnorm(0.75) sk
+  pred <- .dk_predict(model, model@X, type)
+  pred$mean[which.min(pred$mean + qnorm(0.75) * pred$sd)]
+}
+AEI <- function(x, model, new.noise.var = 0, y.min = NULL, type = "UK", envir = NULL) {
+  if (is.null(y.min)) y.min <- .default_y_min(model, type)
+  .Call("dkR_aei", dk_handle(model), .as_rows(x, model@d), y.min, new.noise.var, .type_id(type), FALSE)
+}
+AEI.grad <- function(x, model, new.noise.var = 0, y.min = NULL, type = "UK", envir = NULL) {
+  if (is.null(y.min)) y.min <- .default_y_min(model, type)
+  g <- .Call("dkR_aei", dk_handle(model), .as_rows(x, model@d), y.min, new.noise.var, .type_id(type), TRUE)
+  if (is.null(dim(x))) as.numeric(g) else g
+}
+.default_q_min <- function(model, beta, type) {    # R/EQI.R:108-112: min over the design of mk + qnorm(beta) sk
+  pred <- .dk_predict(model, model@X, type)
+  min(pred$mean + qnorm(beta) * pred$sd)
+}
+EQI <- function(x, model, new.noise.var = 0, beta = 0.9, q.min = NULL, type = "UK", envir = NULL) {
+  if (is.null(q.min)) q.min <- .default_q_min(model, beta, type)
+  .Call("dkR_eqi", dk_handle(model), .as_rows(x, model@d), q.min, new.noise.var, qnorm(beta), .type_id(type), FALSE)
+}
+EQI.grad <- function(x, model, new.noise.var = 0, beta = 0.9, q.min = NULL, type = "UK", envir = NULL) {
+  if (is.null(q.min)) q.min <- .default_q_min(model, beta, type)
+  g <- .Call("dkR_eqi", dk_handle(model), .as_rows(x, model@d), q.min, new.noise.var, qnorm(beta), .type_id(type), TRUE)
+  if (is.null(dim(x))) as.numeric(g) else g
+}
+
+## ---- max_crit (R/max_crit.R:64-130): the random search of EVERY restart goes to the device as ONE matrix ----
+## Same arguments and return value.  n.cores is ignored: the forked workers of the reference (mclapply, :125) cannot carry
+## a CUDA context; the restarts' candidates are screened in one call (rows r N + 1 .. (r + 1) N belong to restart r) and
+## the devices listed in options(DiceOptim.gpu.devices) split the rows.  The L-BFGS-B polish is the reference's optim()
+## call on the GPU-backed EI / EI.grad.
+max_crit <- function(model, type = "UK", lower, upper, minimization = TRUE, control = NULL, proxy = FALSE, trcontrol = NULL,
+                     n.cores = 1) {
+  if (is.null(trcontrol$sigma)) trcontrol$sigma <- (upper - lower) / 2
+  if (is.null(trcontrol$x0)) trcontrol$x0 <- model@X[which.min(model@y), ]
+  if (is.null(trcontrol$crit)) trcontrol$crit <- "EI"
+  if (is.null(trcontrol$inTR)) trcontrol$inTR <- FALSE
+  if (trcontrol$inTR) {
+    lower <- pmax(trcontrol$x0 - trcontrol$sigma, lower)
+    upper <- pmin(trcontrol$x0 + trcontrol$sigma, upper)
+    if (trcontrol$crit != "EI") proxy <- TRUE
+  }
+  d <- ncol(model@X)
+  if (is.null(control$restarts)) control$restarts <- min(10, d)
+  if (is.null(control$BFGS)) control$BFGS <- TRUE
+  N <- if (!is.null(control$n.ei)) control$n.ei else min(2e3, 500 * d)
+  plugin <- if (minimization) min(model@y) else -max(model@y)
+  R <- control$restarts
+  x <- matrix(rep(lower, N * R), byrow = TRUE, ncol = d) +
+    matrix(runif(d * N * R), ncol = d) * matrix(rep(upper - lower, N * R), byrow = TRUE, ncol = d)
+  EI.vect <- EI(x, model, plugin = NULL, type = type, minimization = minimization, envir = NULL, proxy = proxy)
+  oo <- lapply(seq_len(R), function(r) {
+    rows <- ((r - 1) * N + 1):(r * N)
+    I <- which.max(EI.vect[rows])
+    o <- list(val = EI.vect[rows][I], par = x[rows[I], , drop = FALSE])
+    if (control$BFGS)
+      o <- optim(o$par, fn = EI, gr = EI.grad, plugin = plugin, model = model, type = type, minimization = TRUE,
+                 envir = NULL, proxy = proxy, method = "L-BFGS-B", lower = lower, upper = upper,
+                 control = list(maxit = 100, fnscale = -1, trace = 0), hessian = FALSE)
+    o
+  })
+  allval <- sapply(oo, function(o) if (is.null(o$val)) o$value else o$val)
+  I <- which.max(allval)
+  list(par = as.numeric(oo[[I]]$par), value = allval[I])
+}
+
+## ---- sampleFromEI (R/sampleFromEI.R:77-141): the 1000 d-point screen on the device, the weighted draw by sample() ----
+sampleFromEI <- function(model, minimization = TRUE, n = 1, initdistrib = NULL, lower = rep(0, model@d),
+                         upper = rep(1, model@d), T = NULL) {
+  if (is.null(model)) { message("Error in samplefromEI. A km object needs to be given"); return(NULL) }
+  d <- model@d
+  if (length(lower) != length(upper)) { message("Error in samplefromEI : lower and upper must have the same length"); return(NULL) }
+  initial.points <- if (is.null(initdistrib)) t(lower + t(randLHS(n = d * 1000, k = d)) * (upper - lower)) else initdistrib
+  if (d == 1) initial.points <- matrix(initial.points, ncol = 1)
+  if (is.null(T)) T <- if (minimization) min(model@y) else max(model@y)
+  ei <- .Call("dkR_sample_weights", dk_handle(model), .as_rows(initial.points, d), T, minimization)
+  if (sum(ei != 0) < n) {
+    maxEI <- max(ei)
+    ei <- if (maxEI > 0) ei / maxEI + 1 / (1000 * d) else rep(1, 1000 * d)
+  }
+  my.points <- initial.points[sample(1:(1000 * d), n, replace = FALSE, prob = ei), ]
+  if (d == 1) my.points <- matrix(my.points, ncol = 1)
+  if (n == 1) my.points <- matrix(my.points, ncol = d)
+  my.points
 }

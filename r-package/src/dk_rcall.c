@@ -12,20 +12,25 @@
 #include <R.h>
 #include <Rinternals.h>
 #include <R_ext/Rdynload.h>
+#include <stdio.h>
 #include <string.h>
 
 #include "dk_b200.h"
 
+/* The R-side handle is ALWAYS a multi-device handle, on one or several devices: R is a single process that cannot fork CUDA
+ * contexts (the reference's mclapply, /root/reference/R/max_crit.R:125), so the split over GPUs happens inside the
+ * library.  multi_of() gives the multi-GPU handle, handle_of() replica 0 for the single-device-only entry points. */
 static void dkR_finalize(SEXP ptr) {
-  dk_model* m = (dk_model*)R_ExternalPtrAddr(ptr);
-  if (m) dk_model_destroy(m);
+  dk_multi* mm = (dk_multi*)R_ExternalPtrAddr(ptr);
+  if (mm) dk_multi_destroy(mm);
   R_ClearExternalPtr(ptr);
 }
-static dk_model* handle_of(SEXP h) {
-  dk_model* m = (dk_model*)R_ExternalPtrAddr(h);
-  if (!m) Rf_error("dk_b200: model handle is NULL (released or restored from a saved workspace)");
-  return m;
+static dk_multi* multi_of(SEXP h) {
+  dk_multi* mm = (dk_multi*)R_ExternalPtrAddr(h);
+  if (!mm) Rf_error("dk_b200: model handle is NULL (released or restored from a saved workspace)");
+  return mm;
 }
+static dk_model* handle_of(SEXP h) { return dk_multi_model(multi_of(h), 0); }
 static SEXP el(SEXP list, const char* name) {
   SEXP names = Rf_getAttrib(list, R_NamesSymbol);
   for (R_xlen_t i = 0; i < Rf_xlength(list); i++)
@@ -35,7 +40,7 @@ static SEXP el(SEXP list, const char* name) {
 static const double* opt_real(SEXP x) { return (x == R_NilValue || Rf_xlength(x) == 0) ? NULL : REAL(x); }
 
 /* slots: list(T, z, M, X, y, F, trend.coef, range.val, shape.val, noise.var, n, d, p, kernel, trend, sd2, nugget, nugget.flag) */
-SEXP dkR_model_create(SEXP slots, SEXP device) {
+SEXP dkR_model_create(SEXP slots, SEXP devices) {
   dk_model_desc D;
   memset(&D, 0, sizeof D);
   D.n = Rf_asInteger(el(slots, "n")); D.d = Rf_asInteger(el(slots, "d")); D.p = Rf_asInteger(el(slots, "p"));
@@ -46,9 +51,12 @@ SEXP dkR_model_create(SEXP slots, SEXP device) {
   D.noise_var = opt_real(el(slots, "noise.var"));
   D.T = REAL(el(slots, "T")); D.z = REAL(el(slots, "z")); D.M = REAL(el(slots, "M")); D.X = REAL(el(slots, "X"));
   D.y = REAL(el(slots, "y")); D.F = REAL(el(slots, "F")); D.beta = REAL(el(slots, "trend.coef"));
-  D.device = Rf_asInteger(device);
-  dk_model* m = NULL;
-  if (dk_model_create(&D, &m)) Rf_error("dk_model_create: %s", dk_last_error());
+  /* devices: integer vector of CUDA ordinals; a single NA / negative value = every visible device */
+  int ndev = (int)Rf_xlength(devices);
+  const int* dev = INTEGER(devices);
+  int all = (ndev == 1 && (dev[0] == NA_INTEGER || dev[0] < 0));
+  dk_multi* m = NULL;
+  if (dk_multi_create(&D, all ? NULL : dev, all ? 0 : ndev, &m)) Rf_error("dk_multi_create: %s", dk_last_error());
   SEXP ptr = PROTECT(R_MakeExternalPtr(m, R_NilValue, R_NilValue));
   R_RegisterCFinalizerEx(ptr, dkR_finalize, TRUE);
   UNPROTECT(1);
@@ -56,14 +64,14 @@ SEXP dkR_model_create(SEXP slots, SEXP device) {
 }
 
 SEXP dkR_ei(SEXP h, SEXP x, SEXP plugin, SEXP type, SEXP minimization, SEXP proxy, SEXP want_envir) {
-  dk_model* m = handle_of(h);
+  dk_multi* m = multi_of(h);
   R_xlen_t N = Rf_nrows(x);
   int env = Rf_asLogical(want_envir);
   SEXP out = PROTECT(Rf_allocVector(VECSXP, 3));
   SEXP ei = PROTECT(Rf_allocVector(REALSXP, N));
   SEXP mean = PROTECT(Rf_allocVector(REALSXP, env ? N : 0));
   SEXP sd = PROTECT(Rf_allocVector(REALSXP, env ? N : 0));
-  int rc = dk_ei(m, REAL(x), (int64_t)N, Rf_asReal(plugin), Rf_asInteger(type), Rf_asLogical(minimization),
+  int rc = dk_multi_ei(m, REAL(x), (int64_t)N, Rf_asReal(plugin), Rf_asInteger(type), Rf_asLogical(minimization),
                  Rf_asLogical(proxy), REAL(ei), env ? REAL(mean) : NULL, env ? REAL(sd) : NULL);
   SET_VECTOR_ELT(out, 0, ei); SET_VECTOR_ELT(out, 1, mean); SET_VECTOR_ELT(out, 2, sd);
   UNPROTECT(4);
@@ -72,10 +80,10 @@ SEXP dkR_ei(SEXP h, SEXP x, SEXP plugin, SEXP type, SEXP minimization, SEXP prox
 }
 
 SEXP dkR_ei_grad(SEXP h, SEXP x, SEXP plugin, SEXP type, SEXP minimization, SEXP proxy) {
-  dk_model* m = handle_of(h);
+  dk_multi* m = multi_of(h);
   R_xlen_t N = Rf_nrows(x), d = Rf_ncols(x);
   SEXP g = PROTECT(Rf_allocMatrix(REALSXP, N, d));
-  int rc = dk_ei_grad(m, REAL(x), (int64_t)N, Rf_asReal(plugin), Rf_asInteger(type), Rf_asLogical(minimization),
+  int rc = dk_multi_ei_grad(m, REAL(x), (int64_t)N, Rf_asReal(plugin), Rf_asInteger(type), Rf_asLogical(minimization),
                       Rf_asLogical(proxy), REAL(g), NULL);
   UNPROTECT(1);
   if (rc) Rf_error("dk_ei_grad: %s", dk_last_error());
@@ -83,13 +91,13 @@ SEXP dkR_ei_grad(SEXP h, SEXP x, SEXP plugin, SEXP type, SEXP minimization, SEXP
 }
 
 SEXP dkR_quantile(SEXP h, SEXP x, SEXP qnorm_beta, SEXP type, SEXP want_grad) {
-  dk_model* m = handle_of(h);
+  dk_multi* m = multi_of(h);
   R_xlen_t N = Rf_nrows(x), d = Rf_ncols(x);
   int wg = Rf_asLogical(want_grad);
   SEXP out = PROTECT(Rf_allocVector(VECSXP, 2));
   SEXP q = PROTECT(Rf_allocVector(REALSXP, N));
   SEXP g = PROTECT(wg ? Rf_allocMatrix(REALSXP, N, d) : Rf_allocVector(REALSXP, 0));
-  int rc = dk_quantile(m, REAL(x), (int64_t)N, Rf_asReal(qnorm_beta), Rf_asInteger(type), REAL(q), wg ? REAL(g) : NULL);
+  int rc = dk_multi_quantile(m, REAL(x), (int64_t)N, Rf_asReal(qnorm_beta), Rf_asInteger(type), REAL(q), wg ? REAL(g) : NULL);
   SET_VECTOR_ELT(out, 0, q); SET_VECTOR_ELT(out, 1, g);
   UNPROTECT(3);
   if (rc) Rf_error("dk_quantile: %s", dk_last_error());
@@ -97,10 +105,10 @@ SEXP dkR_quantile(SEXP h, SEXP x, SEXP qnorm_beta, SEXP type, SEXP want_grad) {
 }
 
 SEXP dkR_akg(SEXP h, SEXP x, SEXP new_noise_var, SEXP type) {
-  dk_model* m = handle_of(h);
+  dk_multi* m = multi_of(h);
   R_xlen_t N = Rf_nrows(x);
   SEXP out = PROTECT(Rf_allocVector(REALSXP, N));
-  int rc = dk_akg(m, REAL(x), (int64_t)N, Rf_asReal(new_noise_var), Rf_asInteger(type), REAL(out));
+  int rc = dk_multi_akg(m, REAL(x), (int64_t)N, Rf_asReal(new_noise_var), Rf_asInteger(type), REAL(out));
   UNPROTECT(1);
   if (rc) Rf_error("dk_akg: %s", dk_last_error());
   return out;
@@ -108,27 +116,27 @@ SEXP dkR_akg(SEXP h, SEXP x, SEXP new_noise_var, SEXP type) {
 
 /* x: (B*q) x d matrix, rows b*q .. b*q+q-1 = batch b */
 SEXP dkR_qei(SEXP h, SEXP x, SEXP q, SEXP plugin, SEXP type, SEXP minimization, SEXP want_grad) {
-  dk_model* m = handle_of(h);
+  dk_multi* m = multi_of(h);
   int qq = Rf_asInteger(q), wg = Rf_asLogical(want_grad);
   R_xlen_t rows = Rf_nrows(x), d = Rf_ncols(x), B = rows / qq;
   SEXP out = PROTECT(wg ? Rf_allocMatrix(REALSXP, rows, d) : Rf_allocVector(REALSXP, B));
-  int rc = wg ? dk_qei_grad(m, REAL(x), (int64_t)B, qq, Rf_asReal(plugin), Rf_asInteger(type), Rf_asLogical(minimization), REAL(out))
-              : dk_qei(m, REAL(x), (int64_t)B, qq, Rf_asReal(plugin), Rf_asInteger(type), Rf_asLogical(minimization), REAL(out));
+  int rc = dk_multi_qei(m, REAL(x), (int64_t)B, qq, Rf_asReal(plugin), Rf_asInteger(type), Rf_asLogical(minimization),
+                        wg ? NULL : REAL(out), wg ? REAL(out) : NULL);
   UNPROTECT(1);
   if (rc) Rf_error("dk_qei: %s", dk_last_error());
   return out;
 }
 
 SEXP dkR_screen_ei(SEXP h, SEXP x, SEXP plugin, SEXP type, SEXP minimization, SEXP proxy, SEXP k) {
-  dk_model* m = handle_of(h);
+  dk_multi* m = multi_of(h);
   int kk = Rf_asInteger(k);
   R_xlen_t N = Rf_nrows(x);
   SEXP out = PROTECT(Rf_allocVector(VECSXP, 2));
   SEXP idx = PROTECT(Rf_allocVector(REALSXP, kk));
   SEXP val = PROTECT(Rf_allocVector(REALSXP, kk));
   int64_t* tmp = (int64_t*)R_alloc(kk, sizeof(int64_t));
-  int rc = dk_screen_ei(m, REAL(x), 0, (int64_t)N, Rf_asReal(plugin), Rf_asInteger(type), Rf_asLogical(minimization),
-                        Rf_asLogical(proxy), kk, tmp, REAL(val), NULL);
+  int rc = dk_multi_screen_ei(m, REAL(x), (int64_t)N, Rf_asReal(plugin), Rf_asInteger(type), Rf_asLogical(minimization),
+                              Rf_asLogical(proxy), kk, tmp, REAL(val));
   for (int i = 0; i < kk; i++) REAL(idx)[i] = tmp[i] < 0 ? NA_REAL : (double)(tmp[i] + 1); /* 1-based like which.max */
   SET_VECTOR_ELT(out, 0, idx); SET_VECTOR_ELT(out, 1, val);
   UNPROTECT(3);
@@ -189,6 +197,90 @@ SEXP dkR_crit_sur_cst(SEXP hfun, SEXP hcst, SEXP x, SEXP pts, SEXP weights, SEXP
                            Rf_asReal(obj_min), Rf_asInteger(type), LOGICAL(equality), opt_real(tol), REAL(out));
   UNPROTECT(1);
   if (rc) Rf_error("dk_crit_sur_cst: %s", dk_last_error());
+  return out;
+}
+/* Explicit release (the cache in gpu_engine.R evicts with it); the finalizer then finds a cleared pointer. */
+SEXP dkR_release(SEXP h) {
+  dkR_finalize(h);
+  return R_NilValue;
+}
+
+/* Cache key of a km object: FNV-1a over the bytes of every array that, with the scalars, determines the model
+ * (X, y, z, trend.coef, range.val, shape.val, noise.var, diag(T)) and over the scalars themselves.  O(n d), not
+ * O(n^2): T itself is a function of X and the covariance parameters. */
+static unsigned long long fnv(unsigned long long hsh, const void* p, size_t bytes) {
+  const unsigned char* c = (const unsigned char*)p;
+  for (size_t i = 0; i < bytes; i++) { hsh ^= c[i]; hsh *= 1099511628211ULL; }
+  return hsh;
+}
+SEXP dkR_model_key(SEXP slots) {
+  unsigned long long hsh = 1469598103934665603ULL;
+  const char* arrays[] = {"X", "y", "z", "M", "trend.coef", "range.val", "shape.val", "noise.var"};
+  for (int i = 0; i < 8; i++) {
+    SEXP a = el(slots, arrays[i]);
+    R_xlen_t len = a == R_NilValue ? 0 : Rf_xlength(a);
+    hsh = fnv(hsh, &len, sizeof len);
+    if (len) hsh = fnv(hsh, REAL(a), (size_t)len * sizeof(double));
+  }
+  SEXP T = el(slots, "T");
+  int n = Rf_asInteger(el(slots, "n"));
+  for (int i = 0; i < n; i++) hsh = fnv(hsh, REAL(T) + (size_t)i * n + i, sizeof(double));
+  const char* scalars[] = {"n", "d", "p", "kernel", "trend", "sd2", "nugget", "nugget.flag"};
+  for (int i = 0; i < 8; i++) { double v = Rf_asReal(el(slots, scalars[i])); hsh = fnv(hsh, &v, sizeof v); }
+  char buf[32];
+  snprintf(buf, sizeof buf, "%016llx", hsh);
+  return Rf_mkString(buf);
+}
+
+/* predict.km(light.return = TRUE): list(mean, sd) */
+SEXP dkR_predict(SEXP h, SEXP x, SEXP type) {
+  R_xlen_t N = Rf_nrows(x);
+  SEXP out = PROTECT(Rf_allocVector(VECSXP, 2));
+  SEXP mean = PROTECT(Rf_allocVector(REALSXP, N));
+  SEXP sd = PROTECT(Rf_allocVector(REALSXP, N));
+  int rc = dk_multi_predict(multi_of(h), REAL(x), (int64_t)N, Rf_asInteger(type), REAL(mean), REAL(sd));
+  SET_VECTOR_ELT(out, 0, mean); SET_VECTOR_ELT(out, 1, sd);
+  UNPROTECT(3);
+  if (rc) Rf_error("dk_predict: %s", dk_last_error());
+  return out;
+}
+
+/* AKG.grad for every row of x: list(grad N x d, akg N) */
+SEXP dkR_akg_grad(SEXP h, SEXP x, SEXP new_noise_var, SEXP type) {
+  R_xlen_t N = Rf_nrows(x), d = Rf_ncols(x);
+  SEXP out = PROTECT(Rf_allocVector(VECSXP, 2));
+  SEXP g = PROTECT(Rf_allocMatrix(REALSXP, N, d));
+  SEXP v = PROTECT(Rf_allocVector(REALSXP, N));
+  int rc = dk_akg_grad(handle_of(h), REAL(x), (int64_t)N, Rf_asReal(new_noise_var), Rf_asInteger(type), REAL(g), REAL(v));
+  SET_VECTOR_ELT(out, 0, g); SET_VECTOR_ELT(out, 1, v);
+  UNPROTECT(3);
+  if (rc) Rf_error("dk_akg_grad: %s", dk_last_error());
+  return out;
+}
+
+/* AEI / AEI.grad (want_grad) for every row of x; ref = y.min */
+SEXP dkR_aei(SEXP h, SEXP x, SEXP y_min, SEXP new_noise_var, SEXP type, SEXP want_grad) {
+  R_xlen_t N = Rf_nrows(x), d = Rf_ncols(x);
+  int wg = Rf_asLogical(want_grad);
+  SEXP out = PROTECT(wg ? Rf_allocMatrix(REALSXP, N, d) : Rf_allocVector(REALSXP, N));
+  int rc = wg ? dk_aei_grad(handle_of(h), REAL(x), (int64_t)N, Rf_asReal(y_min), Rf_asReal(new_noise_var), Rf_asInteger(type), REAL(out))
+              : dk_aei(handle_of(h), REAL(x), (int64_t)N, Rf_asReal(y_min), Rf_asReal(new_noise_var), Rf_asInteger(type), REAL(out));
+  UNPROTECT(1);
+  if (rc) Rf_error("dk_aei: %s", dk_last_error());
+  return out;
+}
+
+/* EQI / EQI.grad (want_grad) for every row of x; ref = q.min, qnorm_beta = qnorm(beta) */
+SEXP dkR_eqi(SEXP h, SEXP x, SEXP q_min, SEXP new_noise_var, SEXP qnorm_beta, SEXP type, SEXP want_grad) {
+  R_xlen_t N = Rf_nrows(x), d = Rf_ncols(x);
+  int wg = Rf_asLogical(want_grad);
+  SEXP out = PROTECT(wg ? Rf_allocMatrix(REALSXP, N, d) : Rf_allocVector(REALSXP, N));
+  int rc = wg ? dk_eqi_grad(handle_of(h), REAL(x), (int64_t)N, Rf_asReal(q_min), Rf_asReal(new_noise_var), Rf_asReal(qnorm_beta),
+                            Rf_asInteger(type), REAL(out))
+              : dk_eqi(handle_of(h), REAL(x), (int64_t)N, Rf_asReal(q_min), Rf_asReal(new_noise_var), Rf_asReal(qnorm_beta),
+                       Rf_asInteger(type), REAL(out));
+  UNPROTECT(1);
+  if (rc) Rf_error("dk_eqi: %s", dk_last_error());
   return out;
 }
 #endif /* DK_HAVE_R */

@@ -19,6 +19,12 @@ extern SEXP dkR_sample_weights(SEXP, SEXP, SEXP, SEXP);
 extern SEXP dkR_check_predict(SEXP, SEXP, SEXP, SEXP);
 extern SEXP dkR_feasible_improvement(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
 extern SEXP dkR_crit_sur_cst(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
+extern SEXP dkR_release(SEXP);
+extern SEXP dkR_model_key(SEXP);
+extern SEXP dkR_predict(SEXP, SEXP, SEXP);
+extern SEXP dkR_akg_grad(SEXP, SEXP, SEXP, SEXP);
+extern SEXP dkR_aei(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
+extern SEXP dkR_eqi(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
 
 static const R_CMethodDef CEntries[] = {{"davies", (DL_FUNC)&davies, 13}, {NULL, NULL, 0}};
 static const R_CallMethodDef CallEntries[] = {
@@ -29,6 +35,9 @@ static const R_CallMethodDef CallEntries[] = {
     {"dkR_check_predict", (DL_FUNC)&dkR_check_predict, 4},
     {"dkR_feasible_improvement", (DL_FUNC)&dkR_feasible_improvement, 8},
     {"dkR_crit_sur_cst", (DL_FUNC)&dkR_crit_sur_cst, 9},
+    {"dkR_release", (DL_FUNC)&dkR_release, 1},           {"dkR_model_key", (DL_FUNC)&dkR_model_key, 1},
+    {"dkR_predict", (DL_FUNC)&dkR_predict, 3},           {"dkR_akg_grad", (DL_FUNC)&dkR_akg_grad, 4},
+    {"dkR_aei", (DL_FUNC)&dkR_aei, 6},                   {"dkR_eqi", (DL_FUNC)&dkR_eqi, 7},
     {NULL, NULL, 0}};
 
 void R_init_DiceOptim(DllInfo* dll) {

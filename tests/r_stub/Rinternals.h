@@ -9,7 +9,9 @@ typedef enum { FALSE = 0, TRUE } Rboolean;
 typedef void (*R_CFinalizer_t)(SEXP);
 extern SEXP R_NilValue, R_NamesSymbol;
 extern double R_NaReal;
+extern int R_NaInt;
 #define NA_REAL R_NaReal
+#define NA_INTEGER R_NaInt
 #define REALSXP 14
 #define VECSXP 19
 double* REAL(SEXP); int* INTEGER(SEXP); int* LOGICAL(SEXP); const char* CHAR(SEXP);
@@ -24,4 +26,5 @@ void Rf_error(const char*, ...);
 void* R_ExternalPtrAddr(SEXP); void R_ClearExternalPtr(SEXP); SEXP R_MakeExternalPtr(void*, SEXP, SEXP);
 void R_RegisterCFinalizerEx(SEXP, R_CFinalizer_t, Rboolean);
 char* R_alloc(size_t, int);
+SEXP Rf_mkString(const char*);
 #endif
