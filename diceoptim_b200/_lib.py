@@ -32,6 +32,15 @@ class dk_model_desc(C.Structure):
     ]
 
 
+class dk_uniform_spec(C.Structure):
+    _fields_ = [("seed", C.c_ulonglong), ("lower", c_double_p), ("upper", c_double_p)]
+
+
+class dk_crit_spec(C.Structure):
+    _fields_ = [("criterion", C.c_int), ("type", C.c_int), ("minimization", C.c_int), ("proxy", C.c_int),
+                ("plugin", C.c_double), ("qnorm_beta", C.c_double), ("new_noise_var", C.c_double)]
+
+
 # every symbol include/dk_b200.h declares: name -> (restype, argtypes)
 _I, _L, _D, _P, _V = C.c_int, C.c_int64, C.c_double, c_double_p, C.c_void_p
 SIGNATURES = {
@@ -53,6 +62,8 @@ SIGNATURES = {
     "dk_quantile": (_I, [_V, _V, _L, _D, _I, _V, _V]),
     "dk_quantile_dev": (_I, [_V, _V, _L, _D, _I, _V, _V, _V]),
     "dk_screen_ei": (_I, [_V, _V, _I, _L, _D, _I, _I, _I, _I, _V, _V, _V]),
+    "dk_screen": (_I, [_V, _V, _I, C.POINTER(dk_uniform_spec), _L, C.POINTER(dk_crit_spec), _I, _V, _V, _V, _V]),
+    "dk_multi_screen": (_I, [_V, _V, C.POINTER(dk_uniform_spec), _L, C.POINTER(dk_crit_spec), _I, _V, _V, _V]),
     "dk_sample_weights": (_I, [_V, _V, _L, _D, _I, _V]),
     "dk_sample_weights_dev": (_I, [_V, _V, _L, _D, _I, _V, _V]),
     "dk_feas_dev": (_I, [_V, _V, _L, _I, _I, _D, _I, _V, _V]),

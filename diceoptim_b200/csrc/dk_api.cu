@@ -627,7 +627,7 @@ void dk_model_destroy(dk_model* m) {
     if (m->ev_d2h[s]) cudaEventDestroy(m->ev_d2h[s]);
   }
   if (m->h_stage) cudaFreeHost(m->h_stage);
-  cudaFree(m->d_chunk); cudaFree(m->d_vec);
+  cudaFree(m->d_chunk); cudaFree(m->d_vec); cudaFree(m->d_gen);
   if (m->ev0) cudaEventDestroy(m->ev0);
   if (m->ev1) cudaEventDestroy(m->ev1);
   if (m->ev_mid) cudaEventDestroy(m->ev_mid);
@@ -766,18 +766,57 @@ int ensure_vec(dk_model* m, size_t doubles) {
 }
 }  // namespace
 
-// The screen of R/max_crit.R:104-110 over rows [row0, row0 + n): criterion P into a device vector (never copied
-// back), then the k best (value desc, index asc; indices relative to row0, -1 when fewer than k are comparable).
-int host_screen(dk_model* m, const CritParams& P, const double* x, int x_on_device, int64_t ldx, int64_t row0, int64_t n,
-                int k, int64_t* out_idx, double* out_val, cudaStream_t user_stream) {
+namespace {
+int ensure_gen(dk_model* m, size_t doubles) {
+  if (m->gen_doubles >= doubles) return DK_OK;
+  dev_release(m, &m->d_gen, m->gen_doubles);
+  m->gen_doubles = 0;
+  int rc = dev_alloc(m, &m->d_gen, doubles);
+  if (rc) return rc;
+  m->gen_doubles = doubles;
+  return DK_OK;
+}
+
+// one criterion over device-resident rows
+int crit_launch(dk_model* m, const ScreenSpec& S, const double* d_x, int64_t rows, double* d_out, cudaStream_t st) {
+  if (S.criterion == DK_CRIT_AKG) return dk_akg_dev(m, d_x, rows, S.tau2, S.P.type, d_out, st);
+  return launch_predict(m, S.P, d_x, rows, d_out, nullptr, nullptr, st);
+}
+}  // namespace
+
+// The screen of R/max_crit.R:104-110 over rows [row0, row0 + n): the criterion into a device vector (never copied
+// back), then the k best (EI, AKG: largest; kriging.quantile: smallest; ties to the lower index; indices relative to
+// row0, -1 when fewer than k are comparable).  Candidates: the caller's host matrix (chunked pipeline), a device matrix,
+// or rows [row0, row0 + n) of the counter-based generator `gen` (generated chunk by chunk on the device, never uploaded).
+int host_screen(dk_model* m, const ScreenSpec& S, const double* x, int x_on_device, const dk_uniform_spec* gen, int64_t ldx,
+                int64_t row0, int64_t n, int k, int64_t* out_idx, double* out_val, cudaStream_t user_stream) {
   DeviceGuard guard(m->device);
   int rc = ensure_vec(m, (size_t)std::max<int64_t>(n, 1));
   if (rc) return rc;
   if ((rc = ensure_red(m, topk_workspace_bytes(k)))) return rc;
-  cudaStream_t st = user_stream ? user_stream : (x_on_device ? (cudaStream_t) nullptr : m->stream);
-  if (x_on_device) {
+  cudaStream_t st = user_stream ? user_stream : ((x && x_on_device) ? (cudaStream_t) nullptr : m->stream);
+  if (!x) {
+    if (!gen) return fail(DK_ERR_ARG, "neither candidates nor a generator were given");
+    GenSpec G;
+    G.seed = gen->seed;
+    for (int c = 0; c < m->d; c++) {
+      const double lo = gen->lower ? gen->lower[c] : 0.0, up = gen->upper ? gen->upper[c] : 1.0;
+      if (!(up >= lo)) return fail(DK_ERR_ARG, "generator bounds: upper[%d] < lower[%d]", c, c);
+      G.lower[c] = lo;
+      G.width[c] = up - lo;
+    }
+    const int64_t chunk = std::min<int64_t>(std::max<int64_t>(n, 1), chunk_units_for(m, 1, BN));
+    if ((rc = ensure_gen(m, (size_t)chunk * m->d))) return rc;
+    for (int64_t c0 = 0; c0 < n; c0 += chunk) {
+      const int64_t rows = std::min(chunk, n - c0);
+      k_gen_uniform<<<(unsigned)std::min<int64_t>((rows * m->d + 255) / 256, 4 * 148), 256, 0, st>>>(G, m->d, row0 + c0, rows, m->d_gen);
+      m->launches++;
+      DK_CUDA_TRY(cudaGetLastError());
+      if ((rc = crit_launch(m, S, m->d_gen, rows, m->d_vec + c0, st))) return rc;
+    }
+  } else if (x_on_device) {
     if (ldx != n) return fail(DK_ERR_ARG, "device-resident candidates must be contiguous (ld = N)");
-    if ((rc = launch_predict(m, P, x, n, m->d_vec, nullptr, nullptr, st))) return rc;
+    if ((rc = crit_launch(m, S, x, n, m->d_vec, st))) return rc;
   } else {
     if (user_stream) {  // the pipeline runs on the handle's streams: order it after the caller's stream
       DK_CUDA_TRY(cudaStreamSynchronize(user_stream));
@@ -785,20 +824,52 @@ int host_screen(dk_model* m, const CritParams& P, const double* x, int x_on_devi
     }
     rc = run_chunked(m, x, ldx, row0, n, 1, chunk_units_for(m, 1, BN), nullptr, 0,
                      [&](const double* d_x, int64_t rows, double* const*, int64_t u0, cudaStream_t s) {
-                       return launch_predict(m, P, d_x, rows, m->d_vec + u0, nullptr, nullptr, s);
+                       return crit_launch(m, S, d_x, rows, m->d_vec + u0, s);
                      });
     if (rc) { cudaStreamSynchronize(m->stream); return rc; }
   }
-  if ((rc = launch_topk(m->d_vec, n, k, m->d_red, st))) return rc;
+  const double sign = S.criterion == DK_CRIT_QUANTILE ? -1.0 : 1.0;
+  if ((rc = launch_topk(m->d_vec, n, k, m->d_red, st, sign))) return rc;
   m->launches += k;
   std::vector<TopkEntry> host(k);
   DK_CUDA_TRY(cudaMemcpyAsync(host.data(), topk_result_ptr(m->d_red), sizeof(TopkEntry) * k, cudaMemcpyDeviceToHost, st));
   DK_CUDA_TRY(cudaStreamSynchronize(st));
   for (int i = 0; i < k; i++) {
     out_idx[i] = host[i].idx;
-    out_val[i] = host[i].val;
+    out_val[i] = host[i].idx >= 0 ? sign * host[i].val : 0.0;
   }
   return DK_OK;
+}
+
+// ScreenSpec of the public dk_crit_spec (argument checks included)
+int make_screen_spec(const dk_model* m, const dk_crit_spec* c, ScreenSpec* S) {
+  if (!c) return fail(DK_ERR_ARG, "criterion spec is NULL");
+  S->criterion = c->criterion;
+  S->tau2 = c->new_noise_var;
+  switch (c->criterion) {
+    case DK_CRIT_EI: S->P = CritParams{MODE_EI, c->type, c->minimization, c->proxy, c->plugin, 0.0}; break;
+    case DK_CRIT_QUANTILE: S->P = CritParams{MODE_QUANTILE, c->type, 1, 0, 0.0, c->qnorm_beta}; break;
+    case DK_CRIT_AKG:
+      S->P = CritParams{MODE_PREDICT, c->type, 1, 0, 0.0, 0.0};
+      if (!(c->new_noise_var >= 0)) return fail(DK_ERR_ARG, "new.noise.var must be >= 0");
+      break;
+    default: return fail(DK_ERR_ARG, "criterion %d is not one of DK_CRIT_EI / DK_CRIT_QUANTILE / DK_CRIT_AKG", c->criterion);
+  }
+  (void)m;
+  return DK_OK;
+}
+
+// coordinates of generated candidates idx[0..k) (host arithmetic: the generator is a pure function of (seed, j, k))
+void generated_rows(const dk_uniform_spec* gen, int d, const int64_t* idx, int k, double* out_x) {
+  GenSpec G;
+  G.seed = gen->seed;
+  for (int c = 0; c < d; c++) {
+    G.lower[c] = gen->lower ? gen->lower[c] : 0.0;
+    G.width[c] = (gen->upper ? gen->upper[c] : 1.0) - G.lower[c];
+  }
+  for (int i = 0; i < k; i++)
+    for (int c = 0; c < d; c++)
+      out_x[i + (size_t)c * k] = idx[i] >= 0 ? gen_coordinate(G, idx[i], c) : std::nan("");
 }
 
 }  // namespace dk
@@ -846,8 +917,24 @@ int dk_screen_ei(dk_model* m, const double* x, int x_on_device, int64_t N, doubl
   if (rc) return rc;
   if (k < 1 || k > DK_TOPK_MAX) return fail(DK_ERR_ARG, "k=%d outside 1..%d", k, DK_TOPK_MAX);
   if (!out_idx || !out_val) return fail(DK_ERR_ARG, "output pointer is NULL");
-  CritParams P{MODE_EI, type, minimization, proxy, plugin, 0.0};
-  return host_screen(m, P, x, x_on_device, N, 0, N, k, out_idx, out_val, (cudaStream_t)stream);
+  ScreenSpec S{DK_CRIT_EI, CritParams{MODE_EI, type, minimization, proxy, plugin, 0.0}, 0.0};
+  return host_screen(m, S, x, x_on_device, nullptr, N, 0, N, k, out_idx, out_val, (cudaStream_t)stream);
+}
+
+int dk_screen(dk_model* m, const double* x, int x_on_device, const dk_uniform_spec* gen, int64_t N, const dk_crit_spec* crit,
+              int k, int64_t* out_idx, double* out_val, double* out_x, void* stream) {
+  if (!m) return fail(DK_ERR_ARG, "model handle is NULL");
+  if (!x && !gen) return fail(DK_ERR_ARG, "neither candidates nor a generator were given");
+  if (N < 0) return fail(DK_ERR_ARG, "N = %lld is negative", (long long)N);
+  if (k < 1 || k > DK_TOPK_MAX) return fail(DK_ERR_ARG, "k=%d outside 1..%d", k, DK_TOPK_MAX);
+  if (!out_idx || !out_val) return fail(DK_ERR_ARG, "output pointer is NULL");
+  if (out_x && x) return fail(DK_ERR_ARG, "out_x is for generated candidates (the caller already holds x)");
+  ScreenSpec S;
+  int rc = make_screen_spec(m, crit, &S);
+  if (rc) return rc;
+  if ((rc = host_screen(m, S, x, x_on_device, x ? nullptr : gen, N, 0, N, k, out_idx, out_val, (cudaStream_t)stream))) return rc;
+  if (out_x) generated_rows(gen, m->d, out_idx, k, out_x);
+  return DK_OK;
 }
 
 /* Debug aid (not part of the drop-in surface): the same criterion through the plain

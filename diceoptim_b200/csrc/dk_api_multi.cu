@@ -199,32 +199,29 @@ int dk_multi_qei(dk_multi* mm, const double* x, int64_t B, int q, double plugin,
   });
 }
 
-int dk_multi_screen_ei(dk_multi* mm, const double* x, int64_t N, double plugin, int type, int minimization, int proxy,
-                       int k, int64_t* out_idx, double* out_val) {
-  int rc = check_multi(mm, x, N);
-  if (rc) return rc;
-  if (k < 1 || k > 64) return fail(DK_ERR_ARG, "k=%d outside 1..64", k);
-  if (!out_idx || !out_val) return fail(DK_ERR_ARG, "output pointer is NULL");
+namespace {
+int multi_screen(dk_multi* mm, const ScreenSpec& S, const double* x, const dk_uniform_spec* gen, int64_t N, int k,
+                 int64_t* out_idx, double* out_val) {
   const int G = (int)mm->models.size();
   std::vector<int64_t> idx((size_t)G * k, -1);
   std::vector<double> val((size_t)G * k, 0.0);
-  CritParams P{MODE_EI, type, minimization, proxy, plugin, 0.0};
-  rc = on_every_device(mm, [&](int g) {
+  int rc = on_every_device(mm, [&](int g) {
     int64_t lo, hi;
     shard_range(N, g, G, &lo, &hi);
-    int r = host_screen(mm->models[g], P, x, 0, N, lo, hi - lo, k, &idx[(size_t)g * k], &val[(size_t)g * k], nullptr);
+    int r = host_screen(mm->models[g], S, x, 0, gen, N, lo, hi - lo, k, &idx[(size_t)g * k], &val[(size_t)g * k], nullptr);
     if (!r)
       for (int i = 0; i < k; i++)
         if (idx[(size_t)g * k + i] >= 0) idx[(size_t)g * k + i] += lo;   // shard-local -> global row
     return r;
   });
   if (rc) return rc;
-  // merge: value descending, then index ascending (which.max keeps the first maximum); -1 = nothing comparable
+  // merge: best first (EI, AKG: larger; quantile: smaller), then index ascending (which.max keeps the first maximum)
+  const double sign = S.criterion == DK_CRIT_QUANTILE ? -1.0 : 1.0;
   std::vector<int> order;
   for (int i = 0; i < G * k; i++)
     if (idx[i] >= 0) order.push_back(i);
   std::sort(order.begin(), order.end(), [&](int a, int b) {
-    if (val[a] != val[b]) return val[a] > val[b];
+    if (val[a] != val[b]) return sign * val[a] > sign * val[b];
     return idx[a] < idx[b];
   });
   for (int i = 0; i < k; i++) {
@@ -232,6 +229,33 @@ int dk_multi_screen_ei(dk_multi* mm, const double* x, int64_t N, double plugin, 
     out_idx[i] = have ? idx[order[i]] : -1;
     out_val[i] = have ? val[order[i]] : 0.0;
   }
+  return DK_OK;
+}
+}  // namespace
+
+int dk_multi_screen_ei(dk_multi* mm, const double* x, int64_t N, double plugin, int type, int minimization, int proxy,
+                       int k, int64_t* out_idx, double* out_val) {
+  int rc = check_multi(mm, x, N);
+  if (rc) return rc;
+  if (k < 1 || k > 64) return fail(DK_ERR_ARG, "k=%d outside 1..64", k);
+  if (!out_idx || !out_val) return fail(DK_ERR_ARG, "output pointer is NULL");
+  ScreenSpec S{DK_CRIT_EI, CritParams{MODE_EI, type, minimization, proxy, plugin, 0.0}, 0.0};
+  return multi_screen(mm, S, x, nullptr, N, k, out_idx, out_val);
+}
+
+int dk_multi_screen(dk_multi* mm, const double* x, const dk_uniform_spec* gen, int64_t N, const dk_crit_spec* crit, int k,
+                    int64_t* out_idx, double* out_val, double* out_x) {
+  if (!mm || mm->models.empty()) return fail(DK_ERR_ARG, "multi-GPU handle is NULL");
+  if (!x && !gen) return fail(DK_ERR_ARG, "neither candidates nor a generator were given");
+  if (N < 0) return fail(DK_ERR_ARG, "N = %lld is negative", (long long)N);
+  if (k < 1 || k > 64) return fail(DK_ERR_ARG, "k=%d outside 1..64", k);
+  if (!out_idx || !out_val) return fail(DK_ERR_ARG, "output pointer is NULL");
+  if (out_x && x) return fail(DK_ERR_ARG, "out_x is for generated candidates (the caller already holds x)");
+  ScreenSpec S;
+  int rc = make_screen_spec(mm->models[0], crit, &S);
+  if (rc) return rc;
+  if ((rc = multi_screen(mm, S, x, x ? nullptr : gen, N, k, out_idx, out_val))) return rc;
+  if (out_x) generated_rows(gen, mm->models[0]->d, out_idx, k, out_x);
   return DK_OK;
 }
 

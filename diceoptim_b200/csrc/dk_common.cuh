@@ -142,6 +142,8 @@ struct dk_model {
   cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_kern[2] = {nullptr, nullptr}, ev_d2h[2] = {nullptr, nullptr};
   double* d_vec = nullptr;       // device vector of one criterion value per candidate (screens), grow-only
   size_t vec_doubles = 0;
+  double* d_gen = nullptr;       // one chunk of generated candidates (dk_screen with a generator), grow-only
+  size_t gen_doubles = 0;
   void* d_red = nullptr;         // argmax partials
   size_t red_bytes = 0;
   cudaStream_t stream = nullptr;

@@ -92,8 +92,15 @@ int host_predict(dk_model* m, const CritParams& P, const double* x, int64_t ldx,
                  double* out_main, double* out_mean, double* out_sd);
 int host_grad(dk_model* m, const CritParams& P, const double* x, int64_t ldx, int64_t row0, int64_t n, double* out_grad,
               double* out_main);
-int host_screen(dk_model* m, const CritParams& P, const double* x, int x_on_device, int64_t ldx, int64_t row0, int64_t n,
-                int k, int64_t* out_idx, double* out_val, cudaStream_t user_stream);
+struct ScreenSpec {   // the criterion a screen ranks by
+  int criterion;      // DK_CRIT_EI / DK_CRIT_QUANTILE / DK_CRIT_AKG
+  CritParams P;       // EI / quantile parameters (type for all three)
+  double tau2;        // AKG: new.noise.var
+};
+int make_screen_spec(const dk_model* m, const dk_crit_spec* c, ScreenSpec* S);
+int host_screen(dk_model* m, const ScreenSpec& S, const double* x, int x_on_device, const dk_uniform_spec* gen, int64_t ldx,
+                int64_t row0, int64_t n, int k, int64_t* out_idx, double* out_val, cudaStream_t user_stream);
+void generated_rows(const dk_uniform_spec* gen, int d, const int64_t* idx, int k, double* out_x);
 int host_akg(dk_model* m, const double* x, int64_t ldx, int64_t row0, int64_t n, double new_noise_var, int type,
              double* out);                                                       // dk_api_akg.cu
 int host_qei(dk_model* m, const double* x, int64_t ldx, int64_t b0, int64_t nb, int q, double plugin, int type,

@@ -31,7 +31,7 @@ enum { DK_GAUSS = 0, DK_EXP = 1, DK_MATERN3_2 = 2, DK_MATERN5_2 = 3, DK_POWEXP =
 enum { DK_TREND_CONST = 0, DK_TREND_LINEAR = 1 };
 /* predict type */
 enum { DK_SK = 0, DK_UK = 1 };
-/* criteria for dk_screen */
+/* criteria of dk_screen: EI and AKG rank by the LARGEST value, kriging.quantile by the SMALLEST */
 enum { DK_CRIT_EI = 0, DK_CRIT_QUANTILE = 1, DK_CRIT_AKG = 2 };
 
 enum {
@@ -127,6 +127,32 @@ int dk_quantile_dev(dk_model* m, const double* d_x, int64_t N, double qnorm_beta
  * pointer according to x_on_device. */
 int dk_screen_ei(dk_model* m, const double* x, int x_on_device, int64_t N, double plugin, int type,
                  int minimization, int proxy, int k, int64_t* out_idx, double* out_val, void* stream);
+
+/* The same screen for any criterion, over given candidates OR over candidates generated on the device (SURVEY 8(b)
+ * "dk_screen(model, x_or_generator_spec, N, criterion, k, ...)"): the random search of R/max_crit.R:104 is
+ * `lower + runif(d N) (upper - lower)`, which the device can draw itself, so the N x d matrix (800 MB at cfg4) is never
+ * built on the host nor uploaded.  The generator is counter-based (Philox4x32-10): coordinate c of candidate j is a pure
+ * function of (seed, j, c) (counter = (j lo, j hi, c / 2, 0), key = seed; 53-bit uniform u in [0, 1), value =
+ * fma(u, upper - lower, lower)), so any GPU generates any range and the result does not depend on the device count.
+ * It is NOT R's Mersenne-Twister stream: a caller that needs runif()'s exact draws passes x instead.
+ * x == NULL selects the generator.  out_x (k x d column-major, generated candidates only, may be NULL) receives the
+ * coordinates of the k winners. */
+typedef struct {
+  unsigned long long seed;
+  const double* lower; /* d, NULL = 0 */
+  const double* upper; /* d, NULL = 1 */
+} dk_uniform_spec;
+typedef struct {
+  int criterion;        /* DK_CRIT_EI | DK_CRIT_QUANTILE | DK_CRIT_AKG */
+  int type;             /* DK_SK | DK_UK */
+  int minimization;     /* EI */
+  int proxy;            /* EI */
+  double plugin;        /* EI */
+  double qnorm_beta;    /* kriging.quantile: qnorm(beta) */
+  double new_noise_var; /* AKG */
+} dk_crit_spec;
+int dk_screen(dk_model* m, const double* x, int x_on_device, const dk_uniform_spec* gen, int64_t N, const dk_crit_spec* crit,
+              int k, int64_t* out_idx, double* out_val, double* out_x, void* stream);
 
 /* The candidate screen of sampleFromEI — replaces /root/reference/R/sampleFromEI.R:109-125: the
  * EI-proportional sampling weight sn (u Phi(u) + phi(u)) of every row (type "UK" as in the reference,
@@ -272,6 +298,8 @@ int dk_multi_qei(dk_multi* mm, const double* x, int64_t B, int q, double plugin,
                  double* out, double* out_grad);
 int dk_multi_screen_ei(dk_multi* mm, const double* x, int64_t N, double plugin, int type, int minimization, int proxy,
                        int k, int64_t* out_idx, double* out_val);
+int dk_multi_screen(dk_multi* mm, const double* x, const dk_uniform_spec* gen, int64_t N, const dk_crit_spec* crit, int k,
+                    int64_t* out_idx, double* out_val, double* out_x);
 
 #ifdef __cplusplus
 }

@@ -4,9 +4,10 @@ and, on a subset of points, both against the extended-precision restatement (ora
 Shared by tests/test_gpu_configs.py (asserts) and tools/parity_table.py (profiles/parity_r02.md).  Every case returns
 rows  (config, quantity, points, err GPU-vs-oracle, err GPU-vs-hiprec, err oracle-vs-hiprec)  with the error measure
 
-    relerr(a, ref) = max_i |a_i - ref_i| / max(|ref_i|, 1e-12 max_j |ref_j|)
-
-(gradients: per candidate, max over the d components divided by the largest component of that candidate's gradient).
+    relerr(a, ref) = max_i |a_i - ref_i| / max(|ref_i|, 1e-12 max_j |ref_j|)      EI, sd, qEI, AKG (positive quantities)
+    scalederr      = max_i |a_i - ref_i| / (max|y| + sqrt(sd2))                  mean, kriging.quantile: signed
+                     quantities that cross zero, measured against the response scale as the round-1 tests do
+    grad_relerr    = per candidate, max over the d components divided by the largest component of that gradient.
 """
 from __future__ import annotations
 
@@ -32,6 +33,11 @@ def relerr(a, ref, floor_frac=1e-12):
     den = np.maximum(np.abs(ref[ok]), floor_frac * np.max(np.abs(ref[ok])))
     den = np.where(den == 0, 1.0, den)
     return float(np.max(np.abs(a[ok] - ref[ok]) / den))
+
+
+def scalederr(a, ref, scale):
+    a = np.asarray(a, dtype=np.longdouble); ref = np.asarray(ref, dtype=np.longdouble)
+    return float(np.max(np.abs(a - ref)) / scale)
 
 
 def grad_relerr(g, ref):
@@ -66,13 +72,16 @@ def ei_family(cfg, N, n_hi, n_grad_hi, full_grid=False, seed_rank=7):
     ref = dk.predict_km(ko, x, light_return=True)
     hi_idx = np.linspace(0, N - 1, n_hi).astype(int)
     hi = hp.predict_km(ko, x[hi_idx])
-    for key in ("mean", "sd"):
-        rows.append(_row(cfg, key, N, relerr(got[key], ref[key]), relerr(got[key][hi_idx], hi[key]), relerr(ref[key][hi_idx], hi[key])))
+    scale = float(np.max(np.abs(km.y)) + np.sqrt(km.covariance.sd2))
+    rows.append(_row(cfg, "mean (/ response scale)", N, scalederr(got["mean"], ref["mean"], scale),
+                     scalederr(got["mean"][hi_idx], hi["mean"], scale), scalederr(ref["mean"][hi_idx], hi["mean"], scale)))
+    rows.append(_row(cfg, "sd", N, relerr(got["sd"], ref["sd"]), relerr(got["sd"][hi_idx], hi["sd"]), relerr(ref["sd"][hi_idx], hi["sd"])))
     ei = EI(x, km); ei_ref = do.EI(x, ko); ei_hi = hp.EI(x[hi_idx], ko, pred=hi)
     rows.append(_row(cfg, "EI", N, relerr(ei, ei_ref), relerr(ei[hi_idx], ei_hi), relerr(ei_ref[hi_idx], ei_hi)))
     q = kriging_quantile(x, km, beta=0.1); q_ref = do.kriging_quantile(x, ko, beta=0.1)
     q_hi = hp.kriging_quantile(x[hi_idx], ko, QN01, pred=hi)
-    rows.append(_row(cfg, "kriging.quantile", N, relerr(q, q_ref), relerr(q[hi_idx], q_hi), relerr(q_ref[hi_idx], q_hi)))
+    rows.append(_row(cfg, "kriging.quantile (/ response scale)", N, scalederr(q, q_ref, scale), scalederr(q[hi_idx], q_hi, scale),
+                     scalederr(q_ref[hi_idx], q_hi, scale)))
     g = EI_grad(x, km)
     g_ref = np.stack([do.EI_grad(x[i], ko) for i in range(N)])
     gi = hi_idx[:n_grad_hi]
@@ -151,15 +160,19 @@ def akg_family(cfg="cfg5_noisy20_n5000", noise_kind="noise_var", N=256, n_hi=32,
     got = predict(km, x); ref = dk.predict_km(ko, x, light_return=True)
     hi_idx = np.linspace(0, N - 1, n_hi).astype(int)
     hi = hp.predict_km(ko, x[hi_idx])
-    for key in ("mean", "sd"):
-        rows.append(_row(tag, key, N, relerr(got[key], ref[key]), relerr(got[key][hi_idx], hi[key]), relerr(ref[key][hi_idx], hi[key])))
+    scale = float(np.max(np.abs(km.y)) + np.sqrt(km.covariance.sd2))
+    rows.append(_row(tag, "mean (/ response scale)", N, scalederr(got["mean"], ref["mean"], scale),
+                     scalederr(got["mean"][hi_idx], hi["mean"], scale), scalederr(ref["mean"][hi_idx], hi["mean"], scale)))
+    rows.append(_row(tag, "sd", N, relerr(got["sd"], ref["sd"]), relerr(got["sd"][hi_idx], hi["sd"]), relerr(ref["sd"][hi_idx], hi["sd"])))
     qv = kriging_quantile(x, km, beta=0.1); q_ref = do.kriging_quantile(x, ko, beta=0.1)
     q_hi = hp.kriging_quantile(x[hi_idx], ko, QN01, pred=hi)
-    rows.append(_row(tag, "kriging.quantile", N, relerr(qv, q_ref), relerr(qv[hi_idx], q_hi), relerr(q_ref[hi_idx], q_hi)))
+    rows.append(_row(tag, "kriging.quantile (/ response scale)", N, scalederr(qv, q_ref, scale), scalederr(qv[hi_idx], q_hi, scale),
+                     scalederr(q_ref[hi_idx], q_hi, scale)))
     a = AKG(x, km, new_noise_var=tau2)
     predX = oracle_predX(ko)
     a_ref = np.array([do.AKG(x[i], ko, new_noise_var=tau2, predX=predX) for i in range(N)])
     rows.append(_row(tag, "AKG", N, relerr(a, a_ref), None, None))
+    rows.append(_row(tag, "AKG (/ response scale)", N, scalederr(a, a_ref, scale), None, None))
     km.release()
     return rows, {"akg_max": float(np.max(a_ref)), "akg_min": float(np.min(a_ref)), "akg": a, "akg_ref": a_ref}
 
@@ -179,4 +192,8 @@ def akg_hiprec(cfg="cfg5_noisy20_n5000", n=300, N=32):
     predX_hi = hp.predict_km(ko, ko.X)
     a_hi = np.array([hp.AKG(x[i], ko, tau2, predX=predX_hi) for i in range(N)])
     km.release()
-    return [_row(f"{cfg} at n={n} (noise.var)", "AKG", N, relerr(a, a_ref), relerr(a, a_hi), relerr(a_ref, a_hi))], {}
+    scale = float(np.max(np.abs(km.y)) + np.sqrt(km.covariance.sd2))
+    tag = f"{cfg} at n={n} (noise.var)"
+    return [_row(tag, "AKG", N, relerr(a, a_ref), relerr(a, a_hi), relerr(a_ref, a_hi)),
+            _row(tag, "AKG (/ response scale)", N, scalederr(a, a_ref, scale), scalederr(a, a_hi, scale), scalederr(a_ref, a_hi, scale))], \
+        {"akg_max": float(np.max(a_ref))}

@@ -113,8 +113,8 @@ def test_aei_and_eqi_match_oracle(gpu_lib):
         e = EQI(x, km, new_noise_var=0.03, beta=0.9, type=type)
         ra = np.array([do.AEI(xi, ko, new_noise_var=0.03, type=type) for xi in x])
         re = np.array([do.EQI(xi, ko, new_noise_var=0.03, beta=0.9, type=type) for xi in x])
-        assert np.all(np.abs(a - ra) <= 1e-9 * np.abs(ra) + 1e-12 * ra.max())
-        assert np.all(np.abs(e - re) <= 1e-9 * np.abs(re) + 1e-12 * re.max())
+        assert np.all(np.abs(a - ra) <= 1e-10 * np.abs(ra) + 1e-12 * ra.max())
+        assert np.all(np.abs(e - re) <= 1e-10 * np.abs(re) + 1e-12 * re.max())
         assert isinstance(AEI(x[0], km, new_noise_var=0.03, type=type), float)
         km.release()
 
@@ -132,6 +132,6 @@ def test_aei_grad_and_eqi_grad_match_oracle(gpu_lib, trend, type):
     for j in range(x.shape[0]):
         ra = do.AEI_grad(x[j], ko, new_noise_var=0.03, type=type)
         re = do.EQI_grad(x[j], ko, new_noise_var=0.03, beta=0.9, type=type)
-        assert np.max(np.abs(ga[j] - ra)) <= 1e-8 * np.max(np.abs(ra)) + 1e-14
-        assert np.max(np.abs(ge[j] - re)) <= 1e-8 * np.max(np.abs(re)) + 1e-14
+        assert np.max(np.abs(ga[j] - ra)) <= 1e-10 * np.max(np.abs(ra)) + 1e-14
+        assert np.max(np.abs(ge[j] - re)) <= 1e-10 * np.max(np.abs(re)) + 1e-14
     km.release()

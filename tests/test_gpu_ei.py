@@ -1,6 +1,7 @@
 """GPU parity tests: the CUDA path (through the C ABI / ctypes host mirror) against the CPU oracle
 on the same seeded inputs.  Tolerances (FP64): mean 1e-10 relative to the response scale,
-variance 1e-10 of sd2 (sd itself is ill-conditioned where sd2 - ||v||^2 cancels), EI 1e-9 relative
+variance 1e-10 of sd2 and sd itself 1e-10 relative wherever sd^2 > 1e-4 sd2 (next to a design point sd2 - ||v||^2
+cancels and only the variance is meaningful), EI and gradients 1e-10 relative (the north_star's tolerance)
 with an absolute floor of 1e-12 x the largest EI of the batch, argmax bit-exact."""
 import ctypes as C
 
@@ -23,10 +24,12 @@ def check_predict(km, x, type="UK", rtol=1e-10):
     assert np.max(np.abs(got["mean"] - ref["mean"])) <= rtol * scale
     tot = km.covariance.sd2 + (km.covariance.nugget if km.covariance.nugget_flag else 0.0)
     assert np.max(np.abs(got["sd"] ** 2 - ref["sd"] ** 2)) <= rtol * tot
+    far = ref["sd"] ** 2 > 1e-4 * tot
+    assert np.all(np.abs(got["sd"][far] - ref["sd"][far]) <= rtol * ref["sd"][far])
     return got, ref
 
 
-def check_ei(km, x, rtol=1e-9, atol=0.0, **kw):
+def check_ei(km, x, rtol=1e-10, atol=0.0, **kw):
     from diceoptim_b200 import EI
     from oracle import diceoptim as do
     got = EI(x, km, **kw)
@@ -83,7 +86,7 @@ def test_fused_matches_plain_substitution_kernel(gpu_lib):
     pr = predict(km, x)
     assert np.max(np.abs(pr["mean"] - out[1])) < 1e-10
     assert np.max(np.abs(pr["sd"] ** 2 - out[2] ** 2)) < 1e-10 * km.covariance.sd2
-    assert np.allclose(ei, out[0], rtol=1e-9, atol=1e-14)
+    assert np.allclose(ei, out[0], rtol=1e-10, atol=1e-14)
     km.release()
 
 
@@ -164,15 +167,15 @@ def test_ei_grad_and_quantile_grad(gpu_lib, name, trend, type):
     gq = kriging_quantile_grad(x, km, beta=0.2, type=type)
     for j in range(0, 70, 7):
         ref = do.EI_grad(x[j], ko, type=type)
-        assert np.max(np.abs(g[j] - ref)) <= 1e-8 * np.max(np.abs(ref)) + 1e-14
+        assert np.max(np.abs(g[j] - ref)) <= 1e-10 * np.max(np.abs(ref)) + 1e-14
         refq = do.kriging_quantile_grad(x[j], ko, beta=0.2, type=type)
-        assert np.max(np.abs(gq[j] - refq)) <= 1e-8 * np.max(np.abs(refq)) + 1e-14
+        assert np.max(np.abs(gq[j] - refq)) <= 1e-10 * np.max(np.abs(refq)) + 1e-14
     # single-point contract of the reference + maximisation / proxy variants
     assert np.allclose(EI_grad(x[3], km, type=type), g[3], rtol=1e-12, atol=1e-300)
     for kw in (dict(minimization=False), dict(proxy=True)):
         got = EI_grad(x[5], km, type=type, **kw)
         ref = do.EI_grad(x[5], ko, type=type, **kw)
-        assert np.max(np.abs(got - ref)) <= 1e-8 * np.max(np.abs(ref)) + 1e-14
+        assert np.max(np.abs(got - ref)) <= 1e-10 * np.max(np.abs(ref)) + 1e-14
     # zero-gradient guard at a design point (R/EI.grad.R:153)
     assert np.all(EI_grad(km.X[0], km, type=type) == 0.0)
     km.release()
@@ -204,7 +207,7 @@ def test_sample_from_ei_weights_and_draw(gpu_lib):
         with np.errstate(all="ignore"):
             ref = do.sample_from_EI_weights(pts, to_oracle(km), minimization=minimization, T=T)
         assert np.all(w >= 0) and not np.isnan(w).any()
-        assert np.all(np.abs(w - ref) <= 1e-9 * np.abs(ref) + 1e-12 * np.max(ref))
+        assert np.all(np.abs(w - ref) <= 1e-10 * np.abs(ref) + 1e-12 * np.max(ref))
     out = sampleFromEI(km, n=7, seed=3)
     assert out.shape == (7, 3) and np.all((out >= 0) & (out <= 1))
     assert sampleFromEI(km, n=1, seed=3, initdistrib=pts).shape == (1, 3)
@@ -227,7 +230,7 @@ def test_cfg2_full_size_properties(gpu_lib):
     assert ei.min() >= -1e-14 * ei.max(), (ei.min(), int((ei < 0).sum()))   # (m - mean) Phi(u) + sd phi(u) rounds around 0 in the far tail
     sub = np.random.default_rng(0).choice(N, 1500, replace=False)
     ref = do.EI(x[sub], to_oracle(km))
-    assert np.all(np.abs(ei[sub] - ref) <= 1e-9 * np.abs(ref) + 1e-12 * ref.max())
+    assert np.all(np.abs(ei[sub] - ref) <= 1e-10 * np.abs(ref) + 1e-12 * ref.max())
     idx, val = screen_EI(x, km, k=3)
     order = np.lexsort((np.arange(N), -ei))[:3]
     assert list(idx) == list(order) and np.array_equal(val, ei[order])
