@@ -5,6 +5,7 @@
 #include "dk_kernels.cuh"
 #include "dk_predict_kernels.cuh"
 #include "dk_grad.cuh"
+#include "dk_narrow.cuh"
 #include "dk_reduce.cuh"
 
 namespace dk {
@@ -157,6 +158,8 @@ int set_kernel_attrs(int device) {
   DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_fused_tma<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
   DK_ATTR_TMA(DK_GAUSS) DK_ATTR_TMA(DK_EXP) DK_ATTR_TMA(DK_MATERN3_2) DK_ATTR_TMA(DK_MATERN5_2) DK_ATTR_TMA(DK_POWEXP)
 #undef DK_ATTR_TMA
+  DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_narrow, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
+  DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_narrow, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
   DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_fused<-1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
   DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_fused<DK_MATERN5_2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
   if (device < 64) g_attr_done[device] = true;
@@ -172,10 +175,30 @@ int check_call(const dk_model* m, const void* x, int64_t N) {
   return DK_OK;
 }
 
+// Narrow tiles (16 candidates per CTA, dk_narrow.cuh) when the batch would leave at least three quarters of the
+// persistent grid without a 64-wide tile: optimiser-sized calls.  DK_NARROW=0 / 1 forces the choice (A/B runs).
+static bool use_narrow(const dk_model* m, int64_t N) {
+  static const int forced = [] { const char* e = std::getenv("DK_NARROW"); return e ? std::atoi(e) : -1; }();
+  if (m->tile_mode == DK_TILE_WIDE) return false;
+  if (m->tile_mode == DK_TILE_NARROW) return true;
+  if (forced >= 0) return forced != 0;
+  return ((N + BN - 1) / BN) * 4 <= m->grid;
+}
+
 // forward pass over device-resident candidates
 int launch_predict(dk_model* m, const CritParams& P, const double* d_x, int64_t N, double* d_main, double* d_mean,
                    double* d_sd, cudaStream_t st) {
   if (N == 0) return DK_OK;
+  if (use_narrow(m, N)) {
+    const int64_t nt = (N + BNN - 1) / BNN;
+    if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
+    k_predict_narrow<<<(int)std::min<int64_t>(nt, m->grid), NT, SM_TOTAL + PIPE_SMEM, st>>>(
+        m->dm, P, d_x, N, nt, m->d_vscratch, m->scratch_doubles_per_cta, d_main, d_mean, d_sd);
+    if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; m->ev_mid_valid = false; }
+    m->launches++;
+    DK_CUDA_TRY(cudaGetLastError());
+    return DK_OK;
+  }
   const int64_t ntiles = (N + BN - 1) / BN;
   const int grid = (int)std::min<int64_t>(ntiles, m->grid);
   if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
@@ -211,6 +234,16 @@ int launch_grad(dk_model* m, const CritParams& P, const double* d_x, int64_t N, 
   if (N == 0) return DK_OK;
   int rc = ensure_bwd(m);
   if (rc) return rc;
+  if (use_narrow(m, N)) {
+    const int64_t nt = (N + BNN - 1) / BNN;
+    if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
+    k_grad_narrow<<<(int)std::min<int64_t>(nt, m->grid), NT, SM_TOTAL + PIPE_SMEM, st>>>(
+        m->dm, P, d_x, N, nt, m->d_vscratch, m->d_wscratch, m->d_cscratch, m->scratch_doubles_per_cta, d_grad, d_main);
+    if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; m->ev_mid_valid = false; }
+    m->launches++;
+    DK_CUDA_TRY(cudaGetLastError());
+    return DK_OK;
+  }
   const int64_t ntiles = (N + BN - 1) / BN;
   const int grid = (int)std::min<int64_t>(ntiles, m->grid);
   if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
@@ -665,6 +698,13 @@ double dk_model_last_kernel_ms(dk_model* m) {
   float ms = -1.0f;
   if (cudaEventElapsedTime(&ms, m->ev0, m->ev1) != cudaSuccess) return -1.0;
   return (double)ms;
+}
+
+int dk_model_set_tile_mode(dk_model* m, int mode) {
+  if (!m) return fail(DK_ERR_ARG, "model handle is NULL");
+  if (mode != DK_TILE_AUTO && mode != DK_TILE_WIDE && mode != DK_TILE_NARROW) return fail(DK_ERR_ARG, "tile mode %d", mode);
+  m->tile_mode = mode;
+  return DK_OK;
 }
 
 double dk_model_last_phase_ms(dk_model* m) {

@@ -161,6 +161,7 @@ struct dk_model {
   double* d_akg_gscratch = nullptr; // per-CTA blocks of the AKG.grad contraction passes
   double* d_delta = nullptr;        // n: noise.var or zeros (checkPredict covdist when AKG never ran)
   double* d_knyy[2] = {nullptr, nullptr};  // sd(X_j)^2 per type (SK, UK), checkPredict covdist
+  int tile_mode = 0;             // DK_TILE_AUTO / DK_TILE_WIDE / DK_TILE_NARROW (dk_model_set_tile_mode)
   long long launches = 0;        // kernels launched through this handle
   int timing = 0;                // bracket the solve kernel with events
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_mid = nullptr;  // ev_mid: between the two kernels of a two-kernel call

@@ -92,6 +92,14 @@ double dk_model_last_kernel_ms(dk_model* m);
  * timed call, < 0 if that call had a single kernel. */
 double dk_model_last_phase_ms(dk_model* m);
 
+/* Tile shape of the forward / gradient kernels (EI, quantile, predict, AEI, EQI and their gradients).  AUTO (default):
+ * 16-candidate tiles when the call would leave three quarters of the persistent grid without a 64-candidate tile
+ * (N <= 4736 on a B200: the optimiser-sized batches of optim(fn = EI, gr = EI.grad), /root/reference/R/max_crit.R:118-121),
+ * 64-candidate tiles otherwise.  Both solve the same systems in the same order; the row reductions group their terms
+ * differently, so sd and gradients agree to the last bits, not bit for bit.  WIDE / NARROW force one shape. */
+enum { DK_TILE_AUTO = 0, DK_TILE_WIDE = 1, DK_TILE_NARROW = 2 };
+int dk_model_set_tile_mode(dk_model* m, int mode);
+
 /* predict.km(light.return=TRUE): mean and sd — replaces the DiceKriging call at
  * /root/reference/R/EI.R:112-116 and R/sampleFromEI.R:109.  out_sd may be NULL. */
 int dk_predict(dk_model* m, const double* x, int64_t N, int type, double* out_mean, double* out_sd);

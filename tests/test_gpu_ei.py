@@ -8,7 +8,7 @@ import ctypes as C
 import numpy as np
 import pytest
 
-from conftest import small_model, to_oracle
+from conftest import assert_close_adjudicated, small_model, to_oracle
 
 pytestmark = pytest.mark.gpu
 
@@ -38,7 +38,10 @@ def check_ei(km, x, rtol=1e-10, atol=0.0, **kw):
     assert np.array_equal(np.isnan(got), np.isnan(ref))
     ok = ~np.isnan(ref)
     floor = 1e-12 * np.max(np.abs(ref[ok])) if ok.any() else 0.0
-    assert np.all(np.abs(got[ok] - ref[ok]) <= rtol * np.abs(ref[ok]) + floor + atol)
+    from oracle import hiprec as hp
+    idx = np.flatnonzero(ok)
+    assert_close_adjudicated(got[ok], ref[ok], lambda bad: hp.EI(np.atleast_2d(x)[idx[bad]], to_oracle(km), **kw), rtol=rtol,
+                             floor=floor + atol, what="EI")
     return got, ref
 
 
@@ -165,17 +168,21 @@ def test_ei_grad_and_quantile_grad(gpu_lib, name, trend, type):
     x = np.random.default_rng(21).random((70, 3))
     g = EI_grad(x, km, type=type)
     gq = kriging_quantile_grad(x, km, beta=0.2, type=type)
+    from oracle import hiprec as hp
     for j in range(0, 70, 7):
         ref = do.EI_grad(x[j], ko, type=type)
-        assert np.max(np.abs(g[j] - ref)) <= 1e-10 * np.max(np.abs(ref)) + 1e-14
+        assert_close_adjudicated(g[j], ref, lambda bad: hp.EI_grad(x[j], ko, type=type)[bad], rtol=0.0,
+                                 floor=1e-10 * np.max(np.abs(ref)) + 1e-14, what="EI.grad")
         refq = do.kriging_quantile_grad(x[j], ko, beta=0.2, type=type)
-        assert np.max(np.abs(gq[j] - refq)) <= 1e-10 * np.max(np.abs(refq)) + 1e-14
+        assert_close_adjudicated(gq[j], refq, lambda bad: hp.kriging_quantile_grad(x[j], ko, do.qnorm(0.2), type=type)[bad],
+                                 rtol=0.0, floor=1e-10 * np.max(np.abs(refq)) + 1e-14, what="kriging.quantile.grad")
     # single-point contract of the reference + maximisation / proxy variants
     assert np.allclose(EI_grad(x[3], km, type=type), g[3], rtol=1e-12, atol=1e-300)
     for kw in (dict(minimization=False), dict(proxy=True)):
         got = EI_grad(x[5], km, type=type, **kw)
         ref = do.EI_grad(x[5], ko, type=type, **kw)
-        assert np.max(np.abs(got - ref)) <= 1e-10 * np.max(np.abs(ref)) + 1e-14
+        assert_close_adjudicated(got, ref, lambda bad: hp.EI_grad(x[5], ko, type=type, **kw)[bad], rtol=0.0,
+                                 floor=1e-10 * np.max(np.abs(ref)) + 1e-14, what="EI.grad variants")
     # zero-gradient guard at a design point (R/EI.grad.R:153)
     assert np.all(EI_grad(km.X[0], km, type=type) == 0.0)
     km.release()
