@@ -1,6 +1,6 @@
 // dk_api_qei.cu — C ABI entry points of the qEI family (include/dk_b200.h): dk_qei*, dk_qei_grad*, dk_mvn_cdf.
 #include "dk_host.h"
-#include "dk_qei.cuh"
+#include "dk_qei_gen.cuh"
 
 using namespace dk;
 
@@ -12,6 +12,8 @@ using namespace dk;
 namespace {
 bool g_qei_attr_done[64] = {};
 
+int ensure_mom(dk_model* m, size_t need);
+
 int ensure_qei(dk_model* m, int64_t B) {
   if (m->device < 64 && !g_qei_attr_done[m->device]) {
     DK_CUDA_TRY(cudaFuncSetAttribute(k_qei_moments, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
@@ -21,7 +23,10 @@ int ensure_qei(dk_model* m, int64_t B) {
     int rc = dev_alloc(m, &m->d_aux, (size_t)m->grid * QEI_AUX_DOUBLES);
     if (rc) return rc;
   }
-  const size_t need = (size_t)std::max<int64_t>(B, 1) * MOM_STRIDE;
+  return ensure_mom(m, (size_t)std::max<int64_t>(B, 1) * MOM_STRIDE);
+}
+
+int ensure_mom(dk_model* m, size_t need) {
   if (m->mom_doubles < need) {
     if (m->d_mom) { cudaFree(m->d_mom); m->device_bytes -= m->mom_doubles * 8; m->d_mom = nullptr; m->mom_doubles = 0; }
     int rc = dev_alloc(m, &m->d_mom, need);
@@ -37,10 +42,33 @@ extern "C" int dk_qei_dev(dk_model* m, const double* d_x, int64_t B, int q, doub
                           double* d_out, void* stream) {
   int rc = check_call(m, d_x, B);
   if (rc) return rc;
-  if (q < 1 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI batch size q=%d outside 1..%d (deterministic CDFs are implemented up to dimension %d)", q, DK_MAX_Q, DK_MAX_Q);
+  if (q < 1 || q > DK_MAX_Q_LATTICE) return fail(DK_ERR_ARG, "qEI batch size q=%d outside 1..%d", q, DK_MAX_Q_LATTICE);
   if (!d_out) return fail(DK_ERR_ARG, "d_out is NULL");
   if (B == 0) return DK_OK;
   DeviceGuard guard(m->device);
+  if (q > DK_MAX_Q) {
+    // 5 .. 10 points per batch: general-q moments + one CTA per batch for the lattice CDFs (dk_qei_gen.cuh)
+    static bool gen_attr_done[64] = {};
+    if (m->device < 64 && !gen_attr_done[m->device]) {
+      DK_CUDA_TRY(cudaFuncSetAttribute(k_qei_moments_gen, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
+      gen_attr_done[m->device] = true;
+    }
+    if ((rc = ensure_mom(m, (size_t)B * gen_mom_stride(q)))) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int nb = BN / q;
+    const int64_t ntiles = (B + nb - 1) / nb;
+    if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
+    k_qei_moments_gen<<<(int)std::min<int64_t>(ntiles, m->grid), NT, SM_TOTAL + PIPE_SMEM, st>>>(
+        m->dm, type, q, d_x, B, ntiles, m->d_vscratch, m->scratch_doubles_per_cta, m->d_mom);
+    DK_CUDA_TRY(cudaGetLastError());
+    if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev_mid, st));
+    k_qei_cdf_gen<<<(unsigned)std::min<int64_t>(B, 8 * (int64_t)m->num_sms), CDF_THREADS, 0, st>>>(m->d_mom, B, q, plugin,
+                                                                                                minimization, d_out);
+    if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; m->ev_mid_valid = true; }
+    m->launches += 2;
+    DK_CUDA_TRY(cudaGetLastError());
+    return DK_OK;
+  }
   if ((rc = ensure_qei(m, B))) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t ntiles = (B + QB - 1) / QB;
@@ -67,7 +95,7 @@ int dk::host_qei(dk_model* m, const double* x, int64_t ldx, int64_t b0, int64_t 
                  int minimization, double* out, double* out_grad) {
   DeviceGuard guard(m->device);
   const HostOut outs[2] = {{out, 1, ldx, true}, {out_grad, m->d, ldx, false}};
-  int rc = run_chunked(m, x, ldx, b0 * q, nb, q, chunk_units_for(m, q, QB), outs, 2,
+  int rc = run_chunked(m, x, ldx, b0 * q, nb, q, chunk_units_for(m, q, q > DK_MAX_Q ? BN / q : QB), outs, 2,
                        [&](const double* d_x, int64_t rows, double* const* o, int64_t, cudaStream_t st) {
                          int r = DK_OK;
                          if (o[0]) r = dk_qei_dev(m, d_x, rows / q, q, plugin, type, minimization, o[0], st);
@@ -82,7 +110,7 @@ extern "C" int dk_qei(dk_model* m, const double* x, int64_t B, int q, double plu
                       double* out) {
   int rc = check_call(m, x, B);
   if (rc) return rc;
-  if (q < 1 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI batch size q=%d outside 1..%d", q, DK_MAX_Q);
+  if (q < 1 || q > DK_MAX_Q_LATTICE) return fail(DK_ERR_ARG, "qEI batch size q=%d outside 1..%d", q, DK_MAX_Q_LATTICE);
   if (!out) return fail(DK_ERR_ARG, "out is NULL");
   return host_qei(m, x, B * q, 0, B, q, plugin, type, minimization, out, nullptr);
 }
@@ -137,7 +165,7 @@ extern "C" int dk_qei_grad(dk_model* m, const double* x, int64_t B, int q, doubl
 /* Test hook: pmnorm(h_b, varcov = S_b) for B independent q-variate problems (q <= 4), host pointers,
  * device 0.  h is B x q row-major, S is B x q x q row-major. */
 extern "C" int dk_mvn_cdf(int q, int64_t B, const double* h, const double* S, double* out) {
-  if (q < 1 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "dimension q=%d outside 1..%d", q, DK_MAX_Q);
+  if (q < 1 || q > DK_MAX_Q_LATTICE) return fail(DK_ERR_ARG, "dimension q=%d outside 1..%d", q, DK_MAX_Q_LATTICE);
   if (!h || !S || !out || B < 0) return fail(DK_ERR_ARG, "dk_mvn_cdf: bad argument");
   if (B == 0) return DK_OK;
   DevBuf bh, bS, bo;
@@ -147,7 +175,8 @@ extern "C" int dk_mvn_cdf(int q, int64_t B, const double* h, const double* S, do
   double *d_h = bh.p, *d_S = bS.p, *d_o = bo.p;
   DK_CUDA_TRY(cudaMemcpy(d_h, h, B * q * 8, cudaMemcpyHostToDevice));
   DK_CUDA_TRY(cudaMemcpy(d_S, S, B * q * q * 8, cudaMemcpyHostToDevice));
-  k_mvn_cdf_test<<<(unsigned)((B + 63) / 64), 64>>>(q, B, d_h, d_S, d_o);
+  if (q > DK_MAX_Q) k_mvn_lattice_test<<<(unsigned)std::min<int64_t>(B, 1184), CDF_THREADS>>>(q, B, d_h, d_S, d_o);
+  else k_mvn_cdf_test<<<(unsigned)((B + 63) / 64), 64>>>(q, B, d_h, d_S, d_o);
   DK_CUDA_TRY(cudaGetLastError());
   DK_CUDA_TRY(cudaMemcpy(out, d_o, B * 8, cudaMemcpyDeviceToHost));
   return DK_OK;

@@ -488,7 +488,8 @@ static __device__ __noinline__ void crit_epilogue(const DevModel& M, const CritP
 // kernels (covVector.dx needs c again: dc = c .* dlogk).
 // KSEL >= 0 fixes the covariance kernel (and NUGSEL the nugget path) at compile time, so the instantiation carries
 // only the code it runs (the generic version inlines all five kernels: 240 KB of SASS).
-template <bool TMA = false, int KSEL = -1, bool NUGSEL = false>
+// STAGED: the caller has already written the candidate tile xs[k][64] (qEI's general-q kernel lays its batches out itself).
+template <bool TMA = false, int KSEL = -1, bool NUGSEL = false, bool STAGED = false>
 __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __restrict__ x, int64_t N, int64_t c0,
                                              double* __restrict__ panel, unsigned char* smem, int tid,
                                              unsigned* stage_base = nullptr, double* __restrict__ cpanel = nullptr) {
@@ -499,11 +500,12 @@ __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __
   double* s2acc = reinterpret_cast<double*>(smem + SM_S2_OFF);
   const int d = M.d;
   // candidate tile: xs[k][j], coalesced along j (R's column-major N x d is already SoA)
-  for (int i = tid; i < d * BN; i += NT) {
-    const int k = i / BN, j = i % BN;
-    const int64_t g = c0 + j;
-    xs[i] = (g < N) ? x[g + (int64_t)k * N] : x[(N - 1) + (int64_t)k * N];
-  }
+  if constexpr (!STAGED)
+    for (int i = tid; i < d * BN; i += NT) {
+      const int k = i / BN, j = i % BN;
+      const int64_t g = c0 + j;
+      xs[i] = (g < N) ? x[g + (int64_t)k * N] : x[(N - 1) + (int64_t)k * N];
+    }
   if (tid < 4 * BN) s2acc[tid] = 0.0;
 
   DK_MARK_INIT;

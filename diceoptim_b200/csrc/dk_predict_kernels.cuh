@@ -21,6 +21,12 @@ k_predict_fused_tma(const DevModel M, const CritParams P, const double* __restri
   double* panel = vscratch + (size_t)blockIdx.x * panel_doubles;
   pipeline_init(smem, tid);
   unsigned stage_base = 0;
+#ifdef DK_X_STAGGER_NS  // what-if build: the second resident CTA of each SM starts late, so the pair is out of phase
+  if (blockIdx.x >= gridDim.x / 2) {
+    const long long t_end = clock64() + (long long)(DK_X_STAGGER_NS * 1.965);
+    while (clock64() < t_end) __nanosleep(1000);
+  }
+#endif
 #pragma unroll 1
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t c0 = tile * BN;

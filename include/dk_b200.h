@@ -44,7 +44,8 @@ enum {
 
 #define DK_MAX_D 24   /* input dimension limit of the fused kernels */
 #define DK_MAX_P 25   /* trend columns (1 for ~1, d+1 for ~.) */
-#define DK_MAX_Q 4    /* qEI batch size served by the deterministic CDF kernels */
+#define DK_MAX_Q 4    /* qEI / qEI.grad batch size served by the deterministic CDF kernels */
+#define DK_MAX_Q_LATTICE 10 /* qEI batch size served by the fixed-lattice Genz CDF (5 .. 10 points, values only) */
 
 typedef struct dk_model dk_model;
 
@@ -218,7 +219,7 @@ int dk_qei_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, 
 int dk_qei_grad(dk_model* m, const double* x, int64_t B, int q, double plugin, int type, int minimization, double* out_grad);
 int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type, int minimization,
                     double* d_grad, void* stream);
-/* pmnorm(h_b, varcov = S_b) for B independent q-variate problems (q <= DK_MAX_Q): the device CDFs behind
+/* pmnorm(h_b, varcov = S_b) for B independent q-variate problems (q <= DK_MAX_Q_LATTICE): the device CDFs behind
  * dk_qei, exposed for parity tests against mnormt-class references.  h: B x q, S: B x q x q, row-major, host. */
 int dk_mvn_cdf(int q, int64_t B, const double* h, const double* S, double* out);
 

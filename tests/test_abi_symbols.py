@@ -44,3 +44,19 @@ def test_r_call_shim_compiles_against_declarations():
     subprocess.run(cmd, check=True)
     used = set(re.findall(r"\b(dk_[a-z_0-9]+)\s*\(", open(srcs[0]).read()))
     assert used <= set(_declared()) | {"dk_handle"}
+
+
+def test_integration_doc_lists_every_registered_call_entry():
+    """INTEGRATION.md section 1 is the registration file verbatim: every .Call entry registered in packagename_init.c is
+    named there and defined in dk_rcall.c (round 1 shipped a 5-entry table next to an 11-entry file)."""
+    init = open(os.path.join(ROOT, "r-package", "src", "packagename_init.c")).read()
+    entries = set(re.findall(r'\{"(dkR_[a-z_]+)"', init))
+    assert len(entries) >= 17
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    shim = open(os.path.join(ROOT, "r-package", "src", "dk_rcall.c")).read()
+    rsrc = open(os.path.join(ROOT, "r-package", "R", "gpu_engine.R")).read()
+    for e in entries:
+        assert f'"{e}"' in doc, f"{e} registered but missing from INTEGRATION.md"
+        assert re.search(r"SEXP\s+" + e + r"\s*\(", shim), f"{e} registered but not defined in dk_rcall.c"
+    for e in set(re.findall(r'\.Call\("(dkR_[a-z_]+)"', rsrc)):
+        assert e in entries, f"{e} called from R but not registered"

@@ -92,7 +92,7 @@ def test_qei_duplicates_follow_reference_unique_rule(gpu_lib):
     assert got[3] == 0.0 and ref[3] == 0.0
     assert np.all(np.abs(got - ref) <= 1e-10 * np.abs(ref) + 1e-12)
     with pytest.raises(Exception):
-        qEI(rng.random((5, 2)), km)                                      # q = 5 > DK_MAX_Q: refused loudly
+        qEI(rng.random((11, 2)), km)                                     # q = 11 > DK_MAX_Q_LATTICE: refused loudly
     km.release()
 
 
@@ -142,4 +142,62 @@ def test_qei_grad_guards(gpu_lib):
     assert np.all(qEI_grad(x, km, plugin=float(np.median(km.y))) == 0.0)
     x1 = rng.random((1, 2))
     assert np.allclose(qEI_grad(x1, km, plugin=0.1), EI_grad(x1[0], km, plugin=0.1)[None, :], rtol=0, atol=0)
+    km.release()
+
+
+# ---- q = 5 .. 10: the fixed-lattice Genz rule (csrc/dk_qei_gen.cuh, oracle.mvnorm.pmnorm_lattice) ----
+@pytest.mark.parametrize("q", [5, 7, 10])
+def test_device_lattice_cdf_matches_oracle_rule(gpu_lib, q):
+    """same rule on both sides (reordering, Cholesky, 8192 Richtmyer points): rounding-level agreement"""
+    from oracle import mvnorm as mv
+    rng = np.random.default_rng(60 + q)
+    B = 12
+    S = np.stack([_rand_cov(rng, q) for _ in range(B)])
+    h = (rng.standard_normal((B, q)) * 0.8 + 0.6) * np.sqrt(np.einsum("bii->bi", S))
+    out = np.empty(B)
+    rc = gpu_lib.dk_mvn_cdf(q, B, C.c_void_p(np.ascontiguousarray(h).ctypes.data),
+                            C.c_void_p(np.ascontiguousarray(S).ctypes.data), C.c_void_p(out.ctypes.data))
+    assert rc == 0, gpu_lib.dk_last_error()
+    ref = np.array([mv.pmnorm(h[b], varcov=S[b]) for b in range(B)])
+    assert np.max(np.abs(out - ref)) < 1e-11, np.max(np.abs(out - ref))
+    assert ref.max() > 1e-3
+
+
+@pytest.mark.parametrize("q,trend,type", [(5, "const", "UK"), (6, "linear", "UK"), (8, "const", "SK"), (10, "const", "UK")])
+def test_qei_general_q_matches_oracle(gpu_lib, q, trend, type):
+    km = small_model("matern5_2", trend, n=140, d=3, seed=70 + q)
+    ko = to_oracle(km)
+    from diceoptim_b200 import qEI
+    from oracle import diceoptim as do
+    rng = np.random.default_rng(q)
+    B = 9
+    xb = rng.random((B, q, 3))
+    xb[1, 2] = km.X[5]                       # a design row: the batch shrinks to q - 1 points
+    xb[2, 3] = xb[2, 0] + 1e-10              # an in-batch duplicate after rounding
+    xb[3, 1:] = km.X[1:q]                    # q' = 1 -> EI
+    plugin = float(np.median(km.y))
+    got = qEI(xb, km, plugin=plugin, type=type)
+    ref = np.array([do.qEI(xb[b], ko, plugin=plugin, type=type, fastCompute=False) for b in range(B)])
+    scale = np.max(np.abs(km.y)) + np.sqrt(km.covariance.sd2)
+    assert np.all(np.abs(got - ref) <= 1e-9 * np.abs(ref) + 1e-11 * scale), np.max(np.abs(got - ref))
+    assert np.max(ref) > 1e-3
+    gm = qEI(xb[:4], km, plugin=plugin, type=type, minimization=False)
+    rm = np.array([do.qEI(xb[b], ko, plugin=plugin, type=type, minimization=False, fastCompute=False) for b in range(4)])
+    assert np.all(np.abs(gm - rm) <= 1e-9 * np.abs(rm) + 1e-11 * scale)
+    km.release()
+
+
+def test_qei_q10_against_monte_carlo_reference_example(gpu_lib):
+    """The reference's own self-check (R/qEI.R:66-115): hartman4, 3^4 = 81-point factorial design, q = 10, exact qEI against
+    the Monte-Carlo mean improvement over draws of the conditional Gaussian vector."""
+    from diceoptim_b200 import qEI, synth
+    from oracle import diceoptim as do
+    g = np.array([0.0, 0.5, 1.0])
+    X = np.array(np.meshgrid(g, g, g, g, indexing="ij")).reshape(4, -1).T
+    y = synth.hartman4(X)
+    km = synth.make_km(X, y, "matern5_2", np.full(4, 0.6), float(np.var(y)), trend="const")
+    x = np.random.default_rng(7).random((10, 4))
+    got = qEI(x, km)
+    mc, se = do.qEI_monte_carlo(x, to_oracle(km), nsim=600000)
+    assert got > 0 and abs(got - mc) < 4 * se + 2e-5 * (np.max(np.abs(y)) + 1), (got, mc, se)
     km.release()

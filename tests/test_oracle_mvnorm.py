@@ -68,3 +68,33 @@ def test_qei_grad_oracle_vs_finite_differences():
         assert np.max(np.abs(g - fd)) <= 1e-6 * np.max(np.abs(g))
         gf = do.qEI_grad(x, km, plugin=plugin, fastCompute=True)
         assert np.max(np.abs(g - gf)) <= 1e-6 * np.max(np.abs(g))
+
+
+def test_lattice_rule_against_low_dimensional_rules_and_monte_carlo():
+    """The fixed-lattice Genz rule that serves dimensions 5..10: (i) on 4-variate problems against the deterministic
+    Plackett rule (its error class: mean ~2e-5, worst case below 1e-3 on ill-conditioned correlation matrices, which is
+    sadmvn's class at the reference's maxpts = 200 q); (ii) on 6- and 9-variate problems against plain Monte-Carlo."""
+    rng = np.random.default_rng(0)
+    errs = []
+    for _ in range(30):
+        A = rng.standard_normal((4, 5)); S = A @ A.T
+        h = rng.standard_normal(4) * 1.5 * np.sqrt(np.diag(S))
+        sd = np.sqrt(np.diag(S))
+        errs.append(abs(mv.pmnorm_lattice(h / sd, S / np.outer(sd, sd)) - mv.pmnorm(h, varcov=S)))
+    assert max(errs) < 1e-3 and np.mean(errs) < 5e-5
+    for q in (6, 9):
+        A = rng.standard_normal((q, q + 2)); S = A @ A.T
+        sd = np.sqrt(np.diag(S)); h = (rng.standard_normal(q) * 0.5 + 1.0) * sd
+        v = mv.pmnorm(h, varcov=S)
+        Z = rng.standard_normal((1_000_000, q)) @ np.linalg.cholesky(S).T
+        mc = np.mean(np.all(Z <= h, axis=1)); se = np.sqrt(mc * (1 - mc) / 1e6)
+        assert abs(v - mc) < 4 * se + 1e-4, (q, v, mc, se)
+
+
+def test_qei_q6_exact_vs_monte_carlo():
+    km = to_oracle(small_model("matern5_2", "const", n=30, d=3, seed=13, noise_var=0.05))
+    x = np.random.default_rng(8).random((6, 3))
+    plugin = float(np.median(km.y))
+    ex = do.qEI(x, km, plugin=plugin, fastCompute=False)
+    mc, se = do.qEI_monte_carlo(x, km, plugin=plugin, nsim=300000, seed=6)
+    assert abs(ex - mc) < 4 * se + 1e-4 * abs(ex), (ex, mc, se)
