@@ -41,6 +41,11 @@ class dk_crit_spec(C.Structure):
                 ("plugin", C.c_double), ("qnorm_beta", C.c_double), ("new_noise_var", C.c_double)]
 
 
+class dk_lbfgs_options(C.Structure):
+    _fields_ = [("maxit", C.c_int), ("history", C.c_int), ("pgtol", C.c_double), ("factr", C.c_double),
+                ("max_backtracks", C.c_int)]
+
+
 # every symbol include/dk_b200.h declares: name -> (restype, argtypes)
 _I, _L, _D, _P, _V = C.c_int, C.c_int64, C.c_double, c_double_p, C.c_void_p
 SIGNATURES = {
@@ -65,6 +70,8 @@ SIGNATURES = {
     "dk_screen_ei": (_I, [_V, _V, _I, _L, _D, _I, _I, _I, _I, _V, _V, _V]),
     "dk_screen": (_I, [_V, _V, _I, C.POINTER(dk_uniform_spec), _L, C.POINTER(dk_crit_spec), _I, _V, _V, _V, _V]),
     "dk_multi_screen": (_I, [_V, _V, C.POINTER(dk_uniform_spec), _L, C.POINTER(dk_crit_spec), _I, _V, _V, _V]),
+    "dk_polish": (_I, [_V, C.POINTER(dk_crit_spec), _I, _V, _I, _V, _V, C.POINTER(dk_lbfgs_options), _V, _V, _V]),
+    "dk_sample_from_ei": (_I, [_V, _V, _L, _D, _I, _I, C.c_ulonglong, _V]),
     "dk_sample_weights": (_I, [_V, _V, _L, _D, _I, _V]),
     "dk_sample_weights_dev": (_I, [_V, _V, _L, _D, _I, _V, _V]),
     "dk_feas_dev": (_I, [_V, _V, _L, _I, _I, _D, _I, _V, _V]),

@@ -170,15 +170,22 @@ def max_crit(model: KM, type="UK", lower=None, upper=None, minimization=True, co
     N = int(control.get("n.ei", min(2000, 500 * d)))
     plugin = _default_plugin(model, minimization)
     rng = np.random.default_rng(seed)
-    if control.get("optimizer", "batched") == "batched":
-        # every restart's screen, then ONE batched polish of the restarts' winners (optim.py)
-        from .optim import batched_lbfgsb
+    optimizer = control.get("optimizer", "device")
+    if optimizer in ("device", "batched"):
+        # every restart's screen, then ONE polish of all the restarts' winners together: on the device (dk_polish, the
+        # optimiser state never leaves it) or, "batched", with the L-BFGS algebra on the host (optim.py)
+        from .optim import batched_lbfgsb, device_polish
         starts = np.empty((restarts, d)); vals = np.empty(restarts)
         for r in range(restarts):
             x = lower + rng.random((N, d)) * (upper - lower)
             idx, val = screen_EI(x, model, plugin=None, type=type, minimization=minimization, proxy=proxy, device=device)
             starts[r], vals[r] = x[idx[0]], val[0]
-        if bfgs:
+        if bfgs and optimizer == "device":
+            res = device_polish(model, "EI", starts, lower, upper, type=type, minimization=True, proxy=proxy, plugin=plugin,
+                                maxit=int(control.get("maxit", 100)), device=device)   # minimization = TRUE: R/max_crit.R:119
+            improved = res["f"] >= vals
+            starts = np.where(improved[:, None], res["x"], starts); vals = np.where(improved, res["f"], vals)
+        elif bfgs:
             def fg(X):
                 ei, gr = _ei_value_and_grad(X, model, plugin, type, True, proxy, device)   # R/max_crit.R:119
                 return -ei, -np.asarray(gr)
@@ -237,10 +244,16 @@ def max_EI(model: KM, plugin=None, type="UK", lower=None, upper=None, parinit=No
         val = ei[idx]
     starts = x[idx]
 
-    def fg(X):
-        ei, gr = _ei_value_and_grad(X, model, plugin, type, minimization, False, device)
-        return -ei, -np.asarray(gr)
-    res = batched_lbfgsb(fg, starts, lower, upper, maxit=maxit)
+    if control.get("optimizer", "device") == "device":
+        from .optim import device_polish
+        res = device_polish(model, "EI", starts, lower, upper, type=type, minimization=minimization, plugin=plugin,
+                            maxit=maxit, device=device)
+        res = {"x": res["x"], "f": -res["f"]}
+    else:
+        def fg(X):
+            ei, gr = _ei_value_and_grad(X, model, plugin, type, minimization, False, device)
+            return -ei, -np.asarray(gr)
+        res = batched_lbfgsb(fg, starts, lower, upper, maxit=maxit)
     vals = np.where(np.isfinite(res["f"]), -res["f"], -np.inf)
     b = int(np.argmax(vals))
     if not vals[b] >= val[0]:
@@ -291,10 +304,11 @@ def randLHS(n, k, rng):
 
 
 def sampleFromEI(model: KM, minimization=True, n=1, initdistrib=None, lower=None, upper=None, T=None, seed=None,
-                 device=0):
+                 device=0, method=None):
     """R/sampleFromEI.R:77-141: draw ``n`` points with probability proportional to EI among 1000 d LHS points
-    (or ``initdistrib``).  The prediction + weight screen runs on the GPU; the weighted draw without
-    replacement uses numpy's generator in place of R's sample()."""
+    (or ``initdistrib``).  method = "device" (default for n <= 64): weights, the reference's fix-up and the draw without
+    replacement all on the GPU (dk_sample_from_ei, counter-based uniforms seeded by ``seed``); "host": weights on the GPU,
+    numpy's generator for the draw in place of R's sample()."""
     d = model.d
     lower = np.zeros(d) if lower is None else np.asarray(lower, float)
     upper = np.ones(d) if upper is None else np.asarray(upper, float)
@@ -306,8 +320,16 @@ def sampleFromEI(model: KM, minimization=True, n=1, initdistrib=None, lower=None
     N = pts.shape[0]
     if T is None:
         T = float(np.min(model.y)) if minimization else float(np.max(model.y))
-    ei = np.empty(N)
     h = model.handle(device)
+    if method is None:
+        method = "device" if n <= 64 else "host"
+    if method == "device":
+        idx = np.empty(n, dtype=np.int64)
+        s64 = int(rng.integers(0, 2 ** 63)) if seed is None else int(seed) & (2 ** 64 - 1)
+        _lib.check(_lib.load().dk_sample_from_ei(h.ptr, _vp(pts), N, float(T), int(bool(minimization)), int(n), s64, _vp(idx)),
+                   "dk_sample_from_ei")
+        return np.asarray(pts[idx]).reshape(n, d)
+    ei = np.empty(N)
     _lib.check(_lib.load().dk_sample_weights(h.ptr, _vp(pts), N, float(T), int(bool(minimization)), _vp(ei)),
                "dk_sample_weights")
     if np.count_nonzero(ei) < n:                             # R/sampleFromEI.R:126-133
@@ -372,7 +394,19 @@ def max_qEI(model: KM, npoints, lower, upper, crit="exact", minimization=True, o
     lo = np.tile(lower, npoints); up = np.tile(upper, npoints)
     plugin_v = float(np.min(model.y)) if minimization else float(np.max(model.y))
     plugin_g = float(np.min(model.y)) if minimization else -float(np.max(model.y))
-    if oc.get("optimizer", "batched") == "batched":
+    optimizer = oc.get("optimizer", "device" if (minimization and 2 <= npoints <= 4) else "batched")
+    if optimizer == "device":
+        # all nStarts runs advance together ON THE DEVICE (dk_polish): one qEI + one qEI.grad launch per trip.  (Maximisation
+        # keeps the host variant: the reference evaluates value and gradient with different plugins there, R/qEI.R:130 vs
+        # R/qEI.grad.R:272-276.)
+        from .optim import device_polish
+        S = start.shape[0]
+        res = device_polish(model, "qEI", start.reshape(S, npoints * d), lower, upper, q=npoints, minimization=True,
+                            plugin=plugin_v, maxit=int(oc.get("maxit", 100)), device=device)
+        vals = np.where(np.isfinite(res["f"]), res["f"], -np.inf)
+        b = int(np.argmax(vals))
+        return {"par": res["x"][b].reshape(npoints, d).copy(), "value": float(vals[b])}
+    if optimizer == "batched":
         # all nStarts runs advance together: one qEI and one qEI.grad launch per evaluation (optim.py)
         from .optim import batched_lbfgsb
         S = start.shape[0]
@@ -680,7 +714,7 @@ def crit_SUR_cst(x, model_fun: KM, model_constraint, equality=False, critcontrol
 
 
 # ---- the noisy-criteria maximisers (rgenoud in the reference): screen, then batched polish of the best starts ----
-def _screen_and_polish(value, value_grad, d, lower, upper, parinit, control, seed, maximise=True):
+def _screen_and_polish(value, value_grad, d, lower, upper, parinit, control, seed, maximise=True, device_crit=None):
     """Engine replacement of the genoud calls of R/max_AEI.R:95-112, R/max_AKG.R:97-113, R/max_EQI.R:97-114 and
     R/min_quantile.R:96-108: ``control["n.screen"]`` uniform candidates (default 2^15, plus ``parinit``) are scored in
     one launch, the ``pop.size`` best (reference default 3 x 2^d for d <= 6, else 32 d) are polished together by the
@@ -704,10 +738,17 @@ def _screen_and_polish(value, value_grad, d, lower, upper, parinit, control, see
     idx = np.argpartition(v, k - 1)[:k]
     idx = idx[np.lexsort((idx, v[idx]))]
 
-    def fg(X):
-        f, g = value_grad(X)
-        return sgn * np.asarray(f, float), sgn * np.asarray(g, float)
-    res = batched_lbfgsb(fg, x[idx], lower, upper, maxit=maxit)
+    if device_crit is not None and control.get("optimizer", "device") == "device":
+        # the polish on the device: device_crit = (model, criterion name, keyword arguments of optim.device_polish)
+        from .optim import device_polish
+        mdl, name, kw = device_crit
+        res = device_polish(mdl, name, x[idx], lower, upper, maxit=maxit, **kw)
+        res = {"x": res["x"], "f": sgn * res["f"]}
+    else:
+        def fg(X):
+            f, g = value_grad(X)
+            return sgn * np.asarray(f, float), sgn * np.asarray(g, float)
+        res = batched_lbfgsb(fg, x[idx], lower, upper, maxit=maxit)
     f = np.where(np.isfinite(res["f"]), res["f"], np.inf)
     b = int(np.argmin(f))
     if not f[b] <= v[idx[0]]:
@@ -724,7 +765,8 @@ def max_AEI(model: KM, new_noise_var=0.0, y_min=None, type="UK", lower=None, upp
         lambda X: AEI(X, model, new_noise_var=new_noise_var, y_min=y_min, type=type, device=device),
         lambda X: (AEI(X, model, new_noise_var=new_noise_var, y_min=y_min, type=type, device=device),
                    AEI_grad(X, model, new_noise_var=new_noise_var, y_min=y_min, type=type, device=device)),
-        model.d, lower, upper, parinit, control, seed)
+        model.d, lower, upper, parinit, control, seed,
+        device_crit=(model, "AEI", dict(type=type, plugin=y_min, new_noise_var=new_noise_var, device=device)))
 
 
 def max_AKG(model: KM, new_noise_var=0.0, type="UK", lower=None, upper=None, parinit=None, control=None, seed=None,
@@ -734,7 +776,8 @@ def max_AKG(model: KM, new_noise_var=0.0, type="UK", lower=None, upper=None, par
         lambda X: AKG(X, model, new_noise_var=new_noise_var, type=type, device=device),
         lambda X: (AKG(X, model, new_noise_var=new_noise_var, type=type, device=device),
                    AKG_grad(X, model, new_noise_var=new_noise_var, type=type, device=device)),
-        model.d, lower, upper, parinit, control, seed)
+        model.d, lower, upper, parinit, control, seed,
+        device_crit=(model, "AKG", dict(type=type, new_noise_var=new_noise_var, device=device)))
 
 
 def max_EQI(model: KM, new_noise_var=0.0, beta=0.9, q_min=None, type="UK", lower=None, upper=None, parinit=None,
@@ -747,7 +790,9 @@ def max_EQI(model: KM, new_noise_var=0.0, beta=0.9, q_min=None, type="UK", lower
         lambda X: EQI(X, model, new_noise_var=new_noise_var, beta=beta, q_min=q_min, type=type, device=device),
         lambda X: (EQI(X, model, new_noise_var=new_noise_var, beta=beta, q_min=q_min, type=type, device=device),
                    EQI_grad(X, model, new_noise_var=new_noise_var, beta=beta, q_min=q_min, type=type, device=device)),
-        model.d, lower, upper, parinit, control, seed)
+        model.d, lower, upper, parinit, control, seed,
+        device_crit=(model, "EQI", dict(type=type, plugin=q_min, new_noise_var=new_noise_var, qnorm_beta=float(ndtri(beta)),
+                                        device=device)))
 
 
 def min_quantile(model: KM, beta=0.1, type="UK", lower=None, upper=None, parinit=None, control=None, seed=None, device=0):
@@ -756,7 +801,8 @@ def min_quantile(model: KM, beta=0.1, type="UK", lower=None, upper=None, parinit
         lambda X: kriging_quantile(X, model, beta=beta, type=type, device=device),
         lambda X: (kriging_quantile(X, model, beta=beta, type=type, device=device),
                    kriging_quantile_grad(X, model, beta=beta, type=type, device=device)),
-        model.d, lower, upper, parinit, control, seed, maximise=False)
+        model.d, lower, upper, parinit, control, seed, maximise=False,
+        device_crit=(model, "quantile", dict(type=type, qnorm_beta=float(ndtri(beta)), device=device)))
 
 
 def integration_design_cst(integcontrol=None, lower=None, upper=None, model_fun=None, model_constraint=None, equality=False,

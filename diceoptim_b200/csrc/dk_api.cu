@@ -881,6 +881,20 @@ int host_screen(dk_model* m, const ScreenSpec& S, const double* x, int x_on_devi
   return DK_OK;
 }
 
+// criterion S over the caller's host matrix into the handle's device vector d_vec (dk_sample_from_ei ranks keys made
+// from it); synchronises nothing: the values are complete in stream order on m->stream
+int host_weights_to_vec(dk_model* m, const ScreenSpec& S, const double* x, int64_t N) {
+  DeviceGuard guard(m->device);
+  int rc = ensure_vec(m, (size_t)std::max<int64_t>(N, 1));
+  if (rc) return rc;
+  rc = run_chunked(m, x, N, 0, N, 1, chunk_units_for(m, 1, BN), nullptr, 0,
+                   [&](const double* d_x, int64_t rows, double* const*, int64_t u0, cudaStream_t s) {
+                     return crit_launch(m, S, d_x, rows, m->d_vec + u0, s);
+                   });
+  if (rc) cudaStreamSynchronize(m->stream);
+  return rc;
+}
+
 // ScreenSpec of the public dk_crit_spec (argument checks included)
 int make_screen_spec(const dk_model* m, const dk_crit_spec* c, ScreenSpec* S) {
   if (!c) return fail(DK_ERR_ARG, "criterion spec is NULL");
@@ -893,7 +907,7 @@ int make_screen_spec(const dk_model* m, const dk_crit_spec* c, ScreenSpec* S) {
       S->P = CritParams{MODE_PREDICT, c->type, 1, 0, 0.0, 0.0};
       if (!(c->new_noise_var >= 0)) return fail(DK_ERR_ARG, "new.noise.var must be >= 0");
       break;
-    default: return fail(DK_ERR_ARG, "criterion %d is not one of DK_CRIT_EI / DK_CRIT_QUANTILE / DK_CRIT_AKG", c->criterion);
+    default: return fail(DK_ERR_ARG, "criterion %d cannot be screened (DK_CRIT_EI / DK_CRIT_QUANTILE / DK_CRIT_AKG can)", c->criterion);
   }
   (void)m;
   return DK_OK;

@@ -30,7 +30,7 @@ __device__ __forceinline__ bool topk_better(const TopkEntry& a, const TopkEntry&
   return a.val > b.val || (a.val == b.val && a.idx < b.idx);
 }
 
-__global__ void __launch_bounds__(RED_THREADS)
+static __global__ void __launch_bounds__(RED_THREADS)
 k_topk_pass(const double* __restrict__ v, int64_t N, int t, double sign, unsigned char* __restrict__ ws) {
   TopkEntry* result = reinterpret_cast<TopkEntry*>(ws);
   unsigned* counter = reinterpret_cast<unsigned*>(ws + sizeof(TopkEntry) * DK_TOPK_MAX);
@@ -123,7 +123,7 @@ __host__ __device__ inline double gen_coordinate(const GenSpec& G, long long j, 
 #endif
 }
 // rows [first, first + rows) of the candidate matrix into out (rows x d, column-major, ld = rows)
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 k_gen_uniform(const GenSpec G, int d, long long first, long long rows, double* __restrict__ out) {
   const long long total = rows * d;
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {

@@ -100,3 +100,32 @@ def batched_lbfgsb(fg, x0, lower, upper, maxit=100, m=8, pgtol=0.0, factr=1e7, c
         x, f, g = x_new, f_new, g_new
         done |= stalled | (active & small)
     return {"x": x, "f": f, "iterations": iters, "evaluations": evals, "converged": done}
+
+
+CRIT_IDS = {"EI": 0, "quantile": 1, "AKG": 2, "AEI": 3, "EQI": 4, "qEI": 5}
+
+
+def device_polish(model, criterion, x0, lower, upper, q=1, type="UK", minimization=True, proxy=False, plugin=0.0,
+                  qnorm_beta=0.0, new_noise_var=0.0, maxit=100, history=8, pgtol=0.0, factr=1e7, max_backtracks=25, device=0):
+    """dk_polish (include/dk_b200.h): the same projected L-BFGS with the optimiser state resident on the device and one
+    criterion launch per trip for all starts.  x0: S x D (D = q d; for qEI the rows of a start are its q points, row-major
+    like ``x.reshape(S, q, d)``).  Returns dict(x[S, D], f[S] = criterion value at x, iterations[S])."""
+    import ctypes as C
+    from . import _lib
+    lib = _lib.load()
+    d = model.d
+    x0 = np.asarray(x0, float).reshape(-1, q * d)
+    S = x0.shape[0]
+    rows = np.asfortranarray(x0.reshape(S * q, d))                      # (S q) x d column-major
+    lower = np.ascontiguousarray(np.broadcast_to(np.asarray(lower, float).ravel()[:d], (d,)))
+    upper = np.ascontiguousarray(np.broadcast_to(np.asarray(upper, float).ravel()[:d], (d,)))
+    crit = _lib.dk_crit_spec(criterion=CRIT_IDS[criterion], type={"SK": 0, "UK": 1}[type], minimization=int(bool(minimization)),
+                             proxy=int(bool(proxy)), plugin=float(plugin), qnorm_beta=float(qnorm_beta),
+                             new_noise_var=float(new_noise_var))
+    opt = _lib.dk_lbfgs_options(maxit=int(maxit), history=int(history), pgtol=float(pgtol), factr=float(factr),
+                                max_backtracks=int(max_backtracks))
+    out_x = np.empty((S * q, d), order="F"); out_v = np.empty(S); out_it = np.empty(S, dtype=np.int32)
+    vp = lambda a: C.c_void_p(a.ctypes.data)
+    _lib.check(lib.dk_polish(model.handle(device).ptr, C.byref(crit), int(q), vp(rows), S, vp(lower), vp(upper), C.byref(opt),
+                             vp(out_x), vp(out_v), vp(out_it)), "dk_polish")
+    return {"x": np.ascontiguousarray(out_x).reshape(S, q * d), "f": out_v, "iterations": out_it}

@@ -31,8 +31,8 @@ enum { DK_GAUSS = 0, DK_EXP = 1, DK_MATERN3_2 = 2, DK_MATERN5_2 = 3, DK_POWEXP =
 enum { DK_TREND_CONST = 0, DK_TREND_LINEAR = 1 };
 /* predict type */
 enum { DK_SK = 0, DK_UK = 1 };
-/* criteria of dk_screen: EI and AKG rank by the LARGEST value, kriging.quantile by the SMALLEST */
-enum { DK_CRIT_EI = 0, DK_CRIT_QUANTILE = 1, DK_CRIT_AKG = 2 };
+/* criteria of dk_screen (the first three) and dk_polish (all): kriging.quantile is MINIMISED, the others MAXIMISED */
+enum { DK_CRIT_EI = 0, DK_CRIT_QUANTILE = 1, DK_CRIT_AKG = 2, DK_CRIT_AEI = 3, DK_CRIT_EQI = 4, DK_CRIT_QEI = 5 };
 
 enum {
   DK_OK = 0,
@@ -152,16 +152,43 @@ typedef struct {
   const double* upper; /* d, NULL = 1 */
 } dk_uniform_spec;
 typedef struct {
-  int criterion;        /* DK_CRIT_EI | DK_CRIT_QUANTILE | DK_CRIT_AKG */
+  int criterion;        /* DK_CRIT_* */
   int type;             /* DK_SK | DK_UK */
-  int minimization;     /* EI */
+  int minimization;     /* EI, qEI */
   int proxy;            /* EI */
-  double plugin;        /* EI */
-  double qnorm_beta;    /* kriging.quantile: qnorm(beta) */
-  double new_noise_var; /* AKG */
+  double plugin;        /* EI, qEI: plugin;  AEI: y.min;  EQI: q.min */
+  double qnorm_beta;    /* kriging.quantile, EQI: qnorm(beta) */
+  double new_noise_var; /* AKG, AEI, EQI */
 } dk_crit_spec;
 int dk_screen(dk_model* m, const double* x, int x_on_device, const dk_uniform_spec* gen, int64_t N, const dk_crit_spec* crit,
               int k, int64_t* out_idx, double* out_val, double* out_x, void* stream);
+
+/* The polish step of the multistart maximisers ON THE DEVICE — replaces the restart-by-restart
+ * optim(par, fn = EI, gr = EI.grad, method = "L-BFGS-B", lower, upper) of /root/reference/R/max_crit.R:114-122, the
+ * optim(c(x), qEI, qEI.grad, ...) loop of R/max_qEI.R:204-222 and the BFGS stage of genoud in R/max_EI.R:207-219,
+ * R/max_AKG.R, R/max_AEI.R, R/max_EQI.R, R/min_quantile.R.  All S starts advance together: one criterion launch per trip
+ * evaluates every start's current trial point (value + gradient), the optimiser state (iterates, gradients, (s, y)
+ * history, step lengths) stays in device memory, the host reads one int per trip (starts still running).
+ * Projected L-BFGS with Armijo backtracking along the projection arc; same stopping rules as optim's L-BFGS-B (factr,
+ * pgtol, maxit).  x0 / out_x: (S q) x d column-major, rows s q .. s q + q - 1 = start s (q = 1 except for DK_CRIT_QEI,
+ * 2 <= q <= DK_MAX_Q); lower / upper: d (NULL = 0 / 1); out_val[S] = criterion at out_x; out_iters[S] may be NULL. */
+typedef struct {
+  int maxit;          /* iterations per start (optim's maxit; default 100) */
+  int history;        /* (s, y) pairs kept, 1..16 (default 8; optim's lmm is 5) */
+  double pgtol;       /* stop when the projected gradient's max-norm is <= pgtol (default 0, as optim) */
+  double factr;       /* stop when the decrease is <= factr * eps * max(|f|, |f'|, 1) (default 1e7, as optim) */
+  int max_backtracks; /* halvings per line search (default 25) */
+} dk_lbfgs_options;
+int dk_polish(dk_model* m, const dk_crit_spec* crit, int q, const double* x0, int S, const double* lower,
+              const double* upper, const dk_lbfgs_options* opt, double* out_x, double* out_val, int* out_iters);
+
+/* sampleFromEI's draw on the device — replaces /root/reference/R/sampleFromEI.R:109-135: the EI weights of the N rows of x
+ * (dk_sample_weights), the reference's fix-up when fewer than n weights are positive (:126-133), then n_draw <= 64 rows
+ * drawn WITHOUT replacement with probability proportional to the weights: out_idx[n_draw], 0-based, in draw order.
+ * Successive sampling is realised as "the n largest keys log(u_i) / w_i" (Efraimidis & Spirakis), u_i from the
+ * counter-based generator with `seed`: the same law as R's sample(prob =, replace = FALSE), not R's random stream. */
+int dk_sample_from_ei(dk_model* m, const double* x, int64_t N, double T, int minimization, int n_draw,
+                      unsigned long long seed, int64_t* out_idx);
 
 /* The candidate screen of sampleFromEI — replaces /root/reference/R/sampleFromEI.R:109-125: the
  * EI-proportional sampling weight sn (u Phi(u) + phi(u)) of every row (type "UK" as in the reference,

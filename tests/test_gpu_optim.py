@@ -114,3 +114,86 @@ def test_noisy_criteria_maximisers(gpu_lib):
         else:
             assert res["value"] <= np.nanmin(scr) + 1e-9 * abs(np.nanmin(scr)), fn.__name__
     km.release()
+
+
+def test_device_polish_matches_host_batched_lbfgs(gpu_lib):
+    """dk_polish (optimiser state on the device) against the host-side batched L-BFGS (optim.py) from the same starts:
+    same method, so the optima agree to optimiser tolerance; both must sit on a stationary point of the box problem."""
+    from diceoptim_b200 import EI, EI_grad, synth
+    from diceoptim_b200.api import _ei_value_and_grad
+    from diceoptim_b200.optim import batched_lbfgsb, device_polish
+    km = small_model("matern5_2", "const", n=80, d=4, seed=33)
+    lo, up = np.zeros(4), np.ones(4)
+    x0 = np.random.default_rng(4).random((24, 4))
+    pl = float(np.min(km.y))
+    dev = device_polish(km, "EI", x0, lo, up, plugin=pl, maxit=80)
+
+    def fg(X):
+        ei, gr = _ei_value_and_grad(X, km, pl, "UK", True, False, 0)
+        return -ei, -np.asarray(gr)
+    host = batched_lbfgsb(fg, x0, lo, up, maxit=80)
+    start = EI(x0, km)
+    assert np.all(dev["f"] >= start * (1 - 1e-12) - 1e-300)                 # never worse than the start
+    assert np.all(dev["x"] >= lo) and np.all(dev["x"] <= up)
+    assert np.allclose(EI(dev["x"], km), dev["f"], rtol=1e-12, atol=1e-300)   # the reported value is the criterion there
+    # same local optima for most starts (asynchronous vs synchronous line searches may pick different basins rarely)
+    close = np.abs(dev["f"] - (-host["f"])) <= 1e-6 * np.maximum(np.abs(host["f"]), 1e-12)
+    assert close.mean() >= 0.75, (dev["f"], -host["f"])
+    assert dev["f"].max() >= (-host["f"]).max() * (1 - 1e-6)
+    g = EI_grad(dev["x"], km)
+    best = int(np.argmax(dev["f"]))
+    assert _projected_grad_norm(g[best], dev["x"][best], lo, up) <= 1e-4 * dev["f"][best] + 1e-10
+    km.release()
+
+
+def test_device_polish_quantile_and_qei(gpu_lib):
+    from diceoptim_b200 import kriging_quantile, qEI
+    from diceoptim_b200.optim import device_polish
+    km = small_model("matern5_2", "const", n=60, d=2, seed=34, noise_var=0.02)
+    lo, up = np.zeros(2), np.ones(2)
+    x0 = np.random.default_rng(5).random((8, 2))
+    res = device_polish(km, "quantile", x0, lo, up, qnorm_beta=-1.2815515655446004, maxit=60)
+    q0 = kriging_quantile(x0, km, beta=0.1)
+    assert np.all(res["f"] <= q0 + 1e-12)                                   # a minimisation
+    assert np.allclose(kriging_quantile(res["x"], km, beta=0.1), res["f"], rtol=1e-12)
+    xb = np.random.default_rng(6).random((5, 3, 2))
+    pl = float(np.median(km.y))
+    r2 = device_polish(km, "qEI", xb.reshape(5, 6), lo, up, q=3, plugin=pl, maxit=40)
+    v0 = qEI(xb, km, plugin=pl)
+    assert np.all(r2["f"] >= v0 * (1 - 1e-12))
+    assert np.allclose(qEI(r2["x"].reshape(5, 3, 2), km, plugin=pl), r2["f"], rtol=1e-10)
+    km.release()
+
+
+def test_sample_from_ei_on_device_follows_the_weights(gpu_lib):
+    """dk_sample_from_ei: draws without replacement with probability proportional to the EI weights.  Statistical check of
+    the first draw against the weights (chi-square over 8 bins of a small population), distinctness, determinism by seed."""
+    import ctypes as C
+    from diceoptim_b200 import _lib
+    km = small_model("matern5_2", "const", n=40, d=2, seed=35)
+    h = km.handle(0)
+    N = 64
+    x = np.asfortranarray(np.random.default_rng(7).random((N, 2)))
+    T = float(np.min(km.y))
+    w = np.empty(N)
+    _lib.check(gpu_lib.dk_sample_weights(h.ptr, C.c_void_p(x.ctypes.data), N, T, 1, C.c_void_p(w.ctypes.data)), "weights")
+    assert np.count_nonzero(w) >= 8
+    p = w / w.sum()
+    trials = 4000
+    first = np.zeros(N)
+    idx = np.empty(5, np.int64)
+    for s in range(trials):
+        _lib.check(gpu_lib.dk_sample_from_ei(h.ptr, C.c_void_p(x.ctypes.data), N, T, 1, 5, s + 1, C.c_void_p(idx.ctypes.data)), "draw")
+        assert len(set(idx.tolist())) == 5 and idx.min() >= 0
+        first[idx[0]] += 1
+    order = np.argsort(-p)
+    bins = np.array_split(order, 8)
+    obs = np.array([first[b].sum() for b in bins]); exp = np.array([p[b].sum() for b in bins]) * trials
+    keep = exp > 5
+    chi2 = float(np.sum((obs[keep] - exp[keep]) ** 2 / exp[keep]))
+    assert chi2 < 30.0, (chi2, obs, exp)                                   # 7 d.o.f.: P(chi2 > 30) ~ 1e-4
+    a = np.empty(5, np.int64); b = np.empty(5, np.int64)
+    gpu_lib.dk_sample_from_ei(h.ptr, C.c_void_p(x.ctypes.data), N, T, 1, 5, 99, C.c_void_p(a.ctypes.data))
+    gpu_lib.dk_sample_from_ei(h.ptr, C.c_void_p(x.ctypes.data), N, T, 1, 5, 99, C.c_void_p(b.ctypes.data))
+    assert np.array_equal(a, b)
+    km.release()
