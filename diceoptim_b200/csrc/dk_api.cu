@@ -1076,12 +1076,20 @@ extern "C" int dk_ei_dev_noalloc(dk_model* m, const double* d_x, int64_t N, doub
   double* scratch = nullptr;
   if ((rc = noalloc_scratch_address(m->device, &scratch))) return rc;
   if (N == 0) return DK_OK;
-  const int64_t ntiles = (N + BN - 1) / BN;
   const int64_t fit = (int64_t)(DK_NOALLOC_SCRATCH_DOUBLES / panel);  // CTAs whose panels fit the array
-  const int grid = (int)std::min<int64_t>(std::min<int64_t>(ntiles, m->grid), fit);
   CritParams P{MODE_EI, type, minimization, proxy, plugin, 0.0};
-  k_predict_fused<<<grid, NT, SM_TOTAL, (cudaStream_t)stream>>>(m->dm, P, d_x, N, ntiles, scratch, panel, d_ei, d_mean,
-                                                                 d_sd);
+  if (use_narrow(m, N)) {
+    // the same tile shape dk_ei_dev picks for this batch size, so the two entry points return the same numbers
+    const int64_t nt = (N + BNN - 1) / BNN;
+    const int grid = (int)std::min<int64_t>(std::min<int64_t>(nt, m->grid), fit);
+    k_predict_narrow<<<grid, NT, SM_TOTAL + PIPE_SMEM, (cudaStream_t)stream>>>(m->dm, P, d_x, N, nt, scratch, panel, d_ei,
+                                                                               d_mean, d_sd);
+  } else {
+    const int64_t ntiles = (N + BN - 1) / BN;
+    const int grid = (int)std::min<int64_t>(std::min<int64_t>(ntiles, m->grid), fit);
+    k_predict_fused<<<grid, NT, SM_TOTAL, (cudaStream_t)stream>>>(m->dm, P, d_x, N, ntiles, scratch, panel, d_ei, d_mean,
+                                                                   d_sd);
+  }
   m->launches++;
   DK_CUDA_TRY(cudaGetLastError());
   return DK_OK;

@@ -57,6 +57,31 @@ def test_noalloc_matches_regular_entry_point_on_two_calls_in_a_row(gpu_lib):
     km.release(); km2.release()
 
 
+def test_noalloc_allocates_nothing_and_caps_the_grid(gpu_lib):
+    """The entry point's defining property: device memory in use is the same before and after a call (the ordinary entry
+    point is warmed first, so neither the context nor the module load is counted), for a model whose panels only partly
+    fit the fixed array (n = 2000: 1 MiB per CTA, 64 of the 296 CTAs get one), with 64- and with 16-candidate tiles."""
+    import torch
+    from diceoptim_b200 import synth, _lib
+    km = synth.config_model("cfg4_sphere10_n2000")
+    h = km.handle(0)
+    rng = np.random.default_rng(34)
+    for N in (6400, 300):                                  # 100 wide tiles (> 64 panels) / 19 narrow tiles
+        _assert_same(_both(gpu_lib, km, rng.random((N, km.d))))         # warm both entry points
+        x = torch.rand((km.d, N), dtype=torch.float64, device="cuda")
+        ei = torch.empty(N, dtype=torch.float64, device="cuda")
+        torch.cuda.synchronize()
+        before = torch.cuda.mem_get_info()[0]
+        bytes_before = gpu_lib.dk_model_device_bytes(h.ptr)
+        for _ in range(3):
+            _lib.check(gpu_lib.dk_ei_dev_noalloc(h.ptr, _ptr(x), N, float(np.min(km.y)), 1, 1, 0, _ptr(ei), None, None, None), "noalloc")
+        torch.cuda.synchronize()
+        assert torch.cuda.mem_get_info()[0] == before      # free device memory unchanged: nothing allocated or freed
+        assert gpu_lib.dk_model_device_bytes(h.ptr) == bytes_before
+        assert torch.isfinite(ei).all()
+    km.release()
+
+
 def test_noalloc_argument_errors(gpu_lib):
     """Bad arguments are refused with a message and nothing runs.  (The size limit itself, a per-CTA
     panel larger than the 64 MiB array, needs n + p + 1 > 131072 rows, too large a model to build in a test.)"""
