@@ -30,11 +30,12 @@ namespace {
 struct AugFactor {
   const double *T, *z, *M;
   int n, p, n_aug;
+  size_t ldT, ldM;   // leading dimensions of T and of M (z is a plain vector)
   double operator()(int i, int j) const {  // j <= i
-    if (i < n) return T[(size_t)j + (size_t)i * n];
+    if (i < n) return T[(size_t)j + (size_t)i * ldT];
     if (i < n_aug) {
       const int r = i - n;
-      if (j < n) return r == 0 ? z[j] : M[(size_t)j + (size_t)(r - 1) * n];
+      if (j < n) return r == 0 ? z[j] : M[(size_t)j + (size_t)(r - 1) * ldM];
     }
     return i == j ? 1.0 : 0.0;
   }
@@ -43,8 +44,9 @@ struct AugFactor {
 struct FlipFactor {
   const double* T;
   int n;
+  size_t ldT;
   double operator()(int i, int j) const {  // j <= i
-    if (i < n) return T[(size_t)(n - 1 - i) + (size_t)(n - 1 - j) * n];
+    if (i < n) return T[(size_t)(n - 1 - i) + (size_t)(n - 1 - j) * ldT];
     return i == j ? 1.0 : 0.0;
   }
 };
@@ -52,13 +54,16 @@ struct FlipFactor {
 // Build the fragment-ordered tile array of a lower-triangular factor: for each block row I the
 // 8 I tiles of -L_IJ (J < I, k-chunks of 16 columns) followed by the 8 tiles of inv(L_II).
 // The 128 x 128 diagonal inverses are formed in long double and rounded once.
+// Block rows [I0, nblk) only when I0 > 0 (dk_model_append: a new design row changes the last block rows only); `tiles`
+// then starts at block row I0.
 template <class Factor>
-void build_tiles(const Factor& L, int nblk, std::vector<double>& tiles) {
-  tiles.assign(tile_base(nblk) * A_TILE, 0.0);
+void build_tiles(const Factor& L, int nblk, std::vector<double>& tiles, int I0 = 0) {
+  const size_t first = tile_base(I0) * A_TILE;
+  tiles.assign(tile_base(nblk) * A_TILE - first, 0.0);
   std::vector<long double> inv((size_t)BM * BM);
 #pragma omp parallel for schedule(dynamic) firstprivate(inv)
-  for (int I = 0; I < nblk; I++) {
-    double* base = tiles.data() + tile_base(I) * A_TILE;
+  for (int I = I0; I < nblk; I++) {
+    double* base = tiles.data() + (tile_base(I) * A_TILE - first);
     const int r0 = I * BM;
     for (int kc = 0; kc < CHUNKS_PER_BLOCK * I; kc++) {
       double* t = base + (size_t)kc * A_TILE;
@@ -115,36 +120,41 @@ int ensure_red(dk_model* m, size_t bytes) {
 }
 
 int ensure_bwd(dk_model* m) {
-  if (m->d_tiles_bwd) return DK_OK;
+  if (m->d_tiles_bwd && m->bwd_valid) return DK_OK;
   std::vector<double> tiles;
   try {
-    FlipFactor L{m->h_T, m->n};
+    FlipFactor L{m->h_T, m->n, (size_t)m->ld};
     build_tiles(L, m->dm.nblk_b, tiles);
   } catch (const std::bad_alloc&) {
     return fail(DK_ERR_NOMEM, "host allocation for the backward tiles failed");
   }
-  // allocate into locals and publish every pointer only once all steps succeeded: a failed call leaves the handle
-  // exactly as it was (a later gradient call retries instead of launching with half of the buffers)
-  double *t = nullptr, *w = nullptr, *c = nullptr;
-  const size_t wcount = (size_t)m->grid * (m->scratch_doubles_per_cta + COEF_DOUBLES);
-  const size_t ccount = (size_t)m->grid * m->scratch_doubles_per_cta;
-  int rc = dev_alloc(m, &t, tiles.size());
-  if (!rc) rc = dev_alloc(m, &w, wcount);
-  if (!rc) rc = dev_alloc(m, &c, ccount);  // covariance panels (gradients)
-  if (!rc) {
-    cudaError_t e = cudaMemcpy(t, tiles.data(), tiles.size() * 8, cudaMemcpyHostToDevice);
-    if (e != cudaSuccess) rc = fail(DK_ERR_CUDA, "upload of the backward tiles failed: %s", cudaGetErrorString(e));
+  if (!m->d_tiles_bwd) {
+    // allocate into locals and publish every pointer only once all steps succeeded: a failed call leaves the handle
+    // exactly as it was (a later gradient call retries instead of launching with half of the buffers).  The tile buffer
+    // is sized for the handle's row capacity, so dk_model_append only has to refill it.
+    const int cap_blk = (int)((m->scratch_doubles_per_cta / BN) / BM);
+    double *t = nullptr, *w = nullptr, *c = nullptr;
+    const size_t tcount = tile_base(cap_blk) * A_TILE;
+    const size_t wcount = (size_t)m->grid * (m->scratch_doubles_per_cta + COEF_DOUBLES);
+    const size_t ccount = (size_t)m->grid * m->scratch_doubles_per_cta;
+    int rc = dev_alloc(m, &t, tcount);
+    if (!rc) rc = dev_alloc(m, &w, wcount);
+    if (!rc) rc = dev_alloc(m, &c, ccount);  // covariance panels (gradients)
+    if (rc) {
+      dev_release(m, &t, tcount);
+      dev_release(m, &w, wcount);
+      dev_release(m, &c, ccount);
+      return rc;
+    }
+    m->d_wscratch = w;
+    m->d_cscratch = c;
+    m->d_tiles_bwd = t;
+    m->bwd_tile_doubles = tcount;
   }
-  if (rc) {
-    dev_release(m, &t, tiles.size());
-    dev_release(m, &w, wcount);
-    dev_release(m, &c, ccount);
-    return rc;
-  }
-  m->d_wscratch = w;
-  m->d_cscratch = c;
-  m->d_tiles_bwd = t;
-  m->dm.tiles_bwd = t;
+  cudaError_t e = cudaMemcpy(m->d_tiles_bwd, tiles.data(), tiles.size() * 8, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) return fail(DK_ERR_CUDA, "upload of the backward tiles failed: %s", cudaGetErrorString(e));
+  m->dm.tiles_bwd = m->d_tiles_bwd;
+  m->bwd_valid = true;
   return DK_OK;
 }
 
@@ -435,7 +445,7 @@ int dk_model_create(const dk_model_desc* D, dk_model** out) {
   try {
     // ---- tiles of the augmented factor ----
     std::vector<double> tiles;
-    AugFactor L{D->T, D->z, D->M, n, p, dm.n_aug};
+    AugFactor L{D->T, D->z, D->M, n, p, dm.n_aug, (size_t)n, (size_t)n};
     build_tiles(L, dm.nblk, tiles);
     if ((rc = dev_alloc(m, &m->d_tiles_fwd, tiles.size()))) return bail(rc);
     m->tiles_fwd_doubles = tiles.size();
@@ -529,8 +539,11 @@ int dk_model_create(const dk_model_desc* D, dk_model** out) {
     off += (size_t)n * (p + 1);
     const size_t o_nv = off;
     if (D->noise_var) std::memcpy(&small[off], D->noise_var, (size_t)n * 8);
-    if ((rc = dev_alloc(m, &m->d_small, small.size()))) return bail(rc);
-    m->small_doubles = small.size();
+    // capacity: the rows the padded panels can hold (dk_model_append fills them without reallocating)
+    const size_t cap_n = (size_t)dm.n_pad - (size_t)(p + 1);
+    const size_t small_cap = (size_t)p + 2 * (size_t)p * p + 2 * cap_n * (p + 1) + cap_n;
+    if ((rc = dev_alloc(m, &m->d_small, small_cap))) return bail(rc);
+    m->small_doubles = small_cap;
     if ((rc = upload(m->d_small, small.data(), small.size(), "the trend / weight arrays"))) return bail(rc);
     dm.beta = m->d_small + o_beta; dm.RM = m->d_small + o_RM; dm.tuuinv = m->d_small + o_tu;
     dm.alpha = m->d_small + o_al; dm.KinvF = m->d_small + o_al + n;
@@ -554,6 +567,15 @@ int dk_model_create(const dk_model_desc* D, dk_model** out) {
     m->h_T = (double*)std::malloc((size_t)n * n * 8);
     if (!m->h_T) return bail(fail(DK_ERR_NOMEM, "host allocation failed"));
     std::memcpy(m->h_T, D->T, (size_t)n * n * 8);
+    // what dk_model_append needs to grow the model without re-factorising it
+    m->ld = n;
+    m->h_X = (double*)std::malloc((size_t)n * d * 8);
+    m->h_aK = (double*)std::malloc((size_t)n * (p + 1) * 8);
+    if (!m->h_X || !m->h_aK) return bail(fail(DK_ERR_NOMEM, "host allocation failed"));
+    std::memcpy(m->h_X, Xrm.data(), (size_t)n * d * 8);
+    std::memcpy(m->h_aK, aK.data(), (size_t)n * (p + 1) * 8);
+    std::memcpy(m->h_G, G.data(), (size_t)p * p * 8);
+    std::memcpy(m->h_beta, D->beta, (size_t)p * 8);
   } catch (const std::bad_alloc&) {
     return bail(fail(DK_ERR_NOMEM, "host allocation failed while tiling the factor"));
   }
@@ -630,9 +652,14 @@ int dk_model_clone(const dk_model* src, int device, dk_model** out) {
     std::memcpy(*dst, h, count * 8);
     return true;
   };
-  if (!dup(src->h_T, n * n, &m->h_T) || !dup(src->h_zM, n * (p + 1), &m->h_zM) || !dup(src->h_y, n, &m->h_y) ||
-      !dup(src->h_nv, n, &m->h_nv))
+  const size_t ld = (size_t)src->ld;
+  m->ld = src->ld;
+  if (!dup(src->h_T, ld * ld, &m->h_T) || !dup(src->h_zM, ld * (p + 1), &m->h_zM) || !dup(src->h_y, ld, &m->h_y) ||
+      !dup(src->h_nv, ld, &m->h_nv) || !dup(src->h_X, ld * src->d, &m->h_X) || !dup(src->h_aK, ld * (p + 1), &m->h_aK))
     return bail(fail(DK_ERR_NOMEM, "host allocation failed"));
+  std::memcpy(m->h_G, src->h_G, sizeof m->h_G);
+  std::memcpy(m->h_beta, src->h_beta, sizeof m->h_beta);
+  (void)n;
   m->grid = src->grid * m->num_sms / std::max(1, src->num_sms);
   m->scratch_doubles_per_cta = src->scratch_doubles_per_cta;
   if ((rc = dev_alloc(m, &m->d_vscratch, (size_t)m->grid * m->scratch_doubles_per_cta))) return bail(rc);
@@ -643,6 +670,285 @@ int dk_model_clone(const dk_model* src, int device, dk_model** out) {
   *out = m;
   return DK_OK;
 }
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// dk_model_append: one more observation, hyper-parameters and trend coefficients unchanged
+// ------------------------------------------------------------------------------------------
+namespace {
+
+// 1-D kernels as DiceKriging codes them: k(x, X_i) for the n design rows held on the host
+void host_cov_vector(const dk_model* m, const double* x, double* c) {
+  const DevModel& dm = m->dm;
+  const int n = m->n, d = m->d;
+  for (int i = 0; i < n; i++) {
+    double s = 0.0, hs = 0.0;
+    for (int k = 0; k < d; k++) {
+      const double h = std::fabs(m->h_X[(size_t)i * d + k] - x[k]);
+      hs += h;
+      switch (dm.kernel) {
+        case DK_GAUSS: { const double a = h / dm.theta[k]; s += 0.5 * a * a; break; }
+        case DK_EXP: s += h / dm.theta[k]; break;
+        case DK_MATERN3_2: { const double a = std::sqrt(3.0) * h / dm.theta[k]; s += a - std::log1p(a); break; }
+        case DK_MATERN5_2: { const double a = std::sqrt(5.0) * h / dm.theta[k]; s += a - std::log(1.0 + a + a * a / 3.0); break; }
+        default: s += std::pow(h / dm.theta[k], dm.shape[k]); break;
+      }
+    }
+    c[i] = dm.sd2 * std::exp(-s);
+    if (dm.nugget_flag && hs < 1e-15) c[i] += dm.nugget;
+  }
+}
+
+void free_lazy(dk_model* m) {
+  // everything built lazily from the factor: rebuilt on next use (ensure_bwd refills its buffers in place when they fit)
+  m->bwd_valid = false;
+  const size_t n = (size_t)m->n;
+  auto drop = [&](double** q) { if (*q) { cudaFree(*q); *q = nullptr; } };
+  if (m->d_akg_const) { m->device_bytes -= 2 * n * 8; drop(&m->d_akg_const); }
+  if (m->d_akg_perm) { m->device_bytes -= n * 4; cudaFree(m->d_akg_perm); m->d_akg_perm = nullptr; }
+  if (m->d_akg_scratch) { cudaFree(m->d_akg_scratch); m->d_akg_scratch = nullptr; }
+  if (m->d_Kinv) { m->device_bytes -= n * n * 8; drop(&m->d_Kinv); }
+  if (m->d_delta) { m->device_bytes -= n * 8; drop(&m->d_delta); }
+  for (int t = 0; t < 2; t++)
+    if (m->d_knyy[t]) { m->device_bytes -= n * 8; drop(&m->d_knyy[t]); }
+  m->dm.akg_a_sorted = nullptr; m->dm.akg_delta = nullptr; m->dm.akg_perm = nullptr;
+}
+
+// host leading dimension and device buffers for at least want_n design points (+ 256 rows of head-room)
+int grow_capacity(dk_model* m, int want_n) {
+  const int p = m->p, d = m->d, n = m->n;
+  const int old_pad = (int)(m->scratch_doubles_per_cta / BN);
+  const int new_pad = BM * ((want_n + 256 + p + 1 + BM - 1) / BM);
+  // ---- host: re-stride to the new leading dimension ----
+  const size_t ld0 = (size_t)m->ld, ld1 = (size_t)new_pad;
+  auto restride = [&](double** a, int cols, size_t rows_used) -> bool {
+    if (!*a) return true;
+    double* b = (double*)std::calloc(ld1 * (size_t)cols, 8);
+    if (!b) return false;
+    for (int c = 0; c < cols; c++) std::memcpy(b + (size_t)c * ld1, *a + (size_t)c * ld0, rows_used * 8);
+    std::free(*a);
+    *a = b;
+    return true;
+  };
+  bool ok = restride(&m->h_T, n, (size_t)n);
+  if (ok) {  // h_T must be ld1 x ld1, not ld1 x n
+    double* b = (double*)std::realloc(m->h_T, ld1 * ld1 * 8);
+    ok = b != nullptr;
+    if (ok) { m->h_T = b; std::memset(m->h_T + ld1 * (size_t)n, 0, ld1 * (ld1 - (size_t)n) * 8); }
+  }
+  ok = ok && restride(&m->h_zM, p + 1, (size_t)n) && restride(&m->h_aK, p + 1, (size_t)n);
+  auto regrow = [&](double** a, size_t per_row) -> bool {
+    if (!*a) return true;
+    double* b = (double*)std::realloc(*a, ld1 * per_row * 8);
+    if (!b) return false;
+    std::memset(b + (size_t)n * per_row, 0, (ld1 - (size_t)n) * per_row * 8);
+    *a = b;
+    return true;
+  };
+  ok = ok && regrow(&m->h_y, 1) && regrow(&m->h_nv, 1) && regrow(&m->h_X, (size_t)d);
+  if (!ok) return fail(DK_ERR_NOMEM, "host allocation failed while growing the model");
+  m->ld = new_pad;
+  // ---- device ----
+  if (new_pad > old_pad) {
+    DK_CUDA_TRY(cudaDeviceSynchronize());
+    double *t = nullptr, *X = nullptr, *sm = nullptr, *vs = nullptr;
+    const size_t tcount = tile_base(new_pad / BM) * A_TILE, xcount = 3 * (size_t)new_pad * d;
+    const size_t cap_n = (size_t)new_pad - (size_t)(p + 1);
+    const size_t scount = (size_t)p + 2 * (size_t)p * p + 2 * cap_n * (p + 1) + cap_n;
+    const size_t vcount = (size_t)m->grid * (size_t)new_pad * BN;
+    // the V panels go first: freeing the old ones makes room for the new ones
+    dev_release(m, &m->d_vscratch, (size_t)m->grid * m->scratch_doubles_per_cta);
+    if (m->d_wscratch) dev_release(m, &m->d_wscratch, (size_t)m->grid * (m->scratch_doubles_per_cta + COEF_DOUBLES));
+    if (m->d_cscratch) dev_release(m, &m->d_cscratch, (size_t)m->grid * m->scratch_doubles_per_cta);
+    if (m->d_tiles_bwd) dev_release(m, &m->d_tiles_bwd, m->bwd_tile_doubles);
+    m->dm.tiles_bwd = nullptr;
+    int rc = dev_alloc(m, &vs, vcount);
+    if (!rc) rc = dev_alloc(m, &t, tcount);
+    if (!rc) rc = dev_alloc(m, &X, xcount);
+    if (!rc) rc = dev_alloc(m, &sm, scount);
+    if (rc) return rc;   // the handle is unusable after this (out of device memory): the caller destroys it
+    DK_CUDA_TRY(cudaMemcpy(t, m->d_tiles_fwd, m->tiles_fwd_doubles * 8, cudaMemcpyDeviceToDevice));
+    DK_CUDA_TRY(cudaMemset(X, 0, xcount * 8));
+    for (int a = 0; a < 3; a++)
+      DK_CUDA_TRY(cudaMemcpy(X + (size_t)a * new_pad * d, m->d_Xrm + (size_t)a * old_pad * d, (size_t)old_pad * d * 8,
+                             cudaMemcpyDeviceToDevice));
+    dev_release(m, &m->d_tiles_fwd, m->tiles_fwd_doubles);
+    dev_release(m, &m->d_Xrm, m->xrm_doubles);
+    dev_release(m, &m->d_small, m->small_doubles);
+    m->d_vscratch = vs; m->d_tiles_fwd = t; m->d_Xrm = X; m->d_small = sm;
+    m->tiles_fwd_doubles = tcount; m->xrm_doubles = xcount; m->small_doubles = scount;
+    m->scratch_doubles_per_cta = (size_t)new_pad * BN;
+    m->dm.tiles_fwd = t;
+    m->dm.Xrm = X; m->dm.Xrm_s = X + (size_t)new_pad * d; m->dm.Xrm_r8 = X + 2 * (size_t)new_pad * d;
+  }
+  return DK_OK;
+}
+
+// pack beta | RM | tuuinv | [alpha | T^-1 M] | [z | M] | noise.var from the host state, upload, set the kernel pointers
+int upload_small(dk_model* m) {
+  const int n = m->n, p = m->p;
+  const size_t ld = (size_t)m->ld;
+  std::vector<double> RM((size_t)p * p, 0.0), Ginv((size_t)p * p, 0.0);
+  const double* G = m->h_G;
+  for (int j = 0; j < p; j++)
+    for (int i = 0; i <= j; i++) {
+      double s = G[i + (size_t)j * p];
+      for (int k = 0; k < i; k++) s -= RM[k + (size_t)i * p] * RM[k + (size_t)j * p];
+      if (i < j) RM[i + (size_t)j * p] = s / RM[i + (size_t)i * p];
+      else {
+        if (!(s > 0)) return fail(DK_ERR_ARG, "M'M is not positive definite (trend matrix rank deficient)");
+        RM[j + (size_t)j * p] = std::sqrt(s);
+      }
+    }
+  std::vector<double> col(p);
+  for (int e = 0; e < p; e++) {
+    for (int i = 0; i < p; i++) {
+      double s = (i == e) ? 1.0 : 0.0;
+      for (int k = 0; k < i; k++) s -= RM[k + (size_t)i * p] * col[k];
+      col[i] = s / RM[i + (size_t)i * p];
+    }
+    for (int i = p - 1; i >= 0; i--) {
+      double s = col[i];
+      for (int k = i + 1; k < p; k++) s -= RM[i + (size_t)k * p] * col[k];
+      col[i] = s / RM[i + (size_t)i * p];
+    }
+    for (int i = 0; i < p; i++) Ginv[i + (size_t)e * p] = col[i];
+  }
+  const bool nv = m->h_nv != nullptr;
+  std::vector<double> small((size_t)p + 2 * (size_t)p * p + 2 * (size_t)n * (p + 1) + (nv ? n : 0));
+  if (small.size() > m->small_doubles) return fail(DK_ERR_NOMEM, "internal: small-array capacity exceeded");
+  size_t off = 0;
+  const size_t o_beta = off; std::memcpy(&small[off], m->h_beta, p * 8); off += p;
+  const size_t o_RM = off; std::memcpy(&small[off], RM.data(), (size_t)p * p * 8); off += (size_t)p * p;
+  const size_t o_tu = off; std::memcpy(&small[off], Ginv.data(), (size_t)p * p * 8); off += (size_t)p * p;
+  const size_t o_al = off;
+  for (int c = 0; c <= p; c++) std::memcpy(&small[off + (size_t)c * n], m->h_aK + (size_t)c * ld, (size_t)n * 8);
+  off += (size_t)n * (p + 1);
+  const size_t o_zM = off;
+  for (int c = 0; c <= p; c++) std::memcpy(&small[off + (size_t)c * n], m->h_zM + (size_t)c * ld, (size_t)n * 8);
+  off += (size_t)n * (p + 1);
+  const size_t o_nv = off;
+  if (nv) std::memcpy(&small[off], m->h_nv, (size_t)n * 8);
+  DK_CUDA_TRY(cudaMemcpy(m->d_small, small.data(), small.size() * 8, cudaMemcpyHostToDevice));
+  DevModel& dm = m->dm;
+  dm.beta = m->d_small + o_beta; dm.RM = m->d_small + o_RM; dm.tuuinv = m->d_small + o_tu;
+  dm.alpha = m->d_small + o_al; dm.KinvF = m->d_small + o_al + n;
+  dm.noise_var = nv ? m->d_small + o_nv : nullptr;
+  dm.Mcm = m->d_small + o_zM + n;
+  return DK_OK;
+}
+
+}  // namespace
+
+// The last column of the new Cholesky factor needs one forward substitution against the old one:
+//   v = T'^-1 c(x),  t = sqrt(k(x, x) - v'v),  T+ = [[T, v], [0, t]],  z+ = [z, (y - f'beta - v'z) / t],
+//   M+ = [M; (f - v'M) / t],  alpha+ = [alpha - a u; a] with a = z+_n / t and u = T^-1 v (likewise T^-1 M),
+// and on the device only the block rows of the tiled factor that hold row n or later change (the new row of T', and the
+// augmented rows [z M]' one row further down).
+extern "C" int dk_model_append(dk_model* m, const double* x_new, double y_new, double new_noise_var) {
+  if (!m || !x_new) return fail(DK_ERR_ARG, "dk_model_append: NULL argument");
+  if (!m->h_y) return fail(DK_ERR_ARG, "dk_model_append needs model@y (dk_model_desc.y was NULL)");
+  DeviceGuard guard(m->device);
+  DK_CUDA_TRY(cudaDeviceSynchronize());   // nothing of this handle may be in flight while its factor changes
+  const int n = m->n, p = m->p, d = m->d;
+  int rc;
+  if (n + 1 + p + 1 > (int)(m->scratch_doubles_per_cta / BN) || n + 1 > m->ld)
+    if ((rc = grow_capacity(m, n + 1))) return rc;
+  const size_t ld = (size_t)m->ld;
+  DevModel& dm = m->dm;
+  std::vector<double> v((size_t)n), u((size_t)n);
+  host_cov_vector(m, x_new, v.data());
+  // v <- T'^-1 c: row i of T' is column i of T (contiguous)
+  for (int i = 0; i < n; i++) {
+    const double* col = m->h_T + (size_t)i * ld;
+    long double s = v[i];
+    for (int j = 0; j < i; j++) s -= (long double)col[j] * v[j];
+    v[i] = (double)(s / col[i]);
+  }
+  long double vv = 0.0L;
+  for (int i = 0; i < n; i++) vv += (long double)v[i] * v[i];
+  const double knn = dm.sd2 + (dm.nugget_flag ? dm.nugget : (m->h_nv ? new_noise_var : 0.0));
+  const double t2 = (double)((long double)knn - vv);
+  if (!(t2 > 0.0))
+    return fail(DK_ERR_ARG, "the new point makes the covariance matrix numerically singular (k(x,x) - v'v = %.3e); "
+                            "checkPredict guards against this (R/checkPredict.R)", t2);
+  const double t = std::sqrt(t2);
+  // trend row f(x), z+ and M+
+  double f[DK_MAX_P], mnew[DK_MAX_P];
+  f[0] = 1.0;
+  if (dm.trend == DK_TREND_LINEAR)
+    for (int k = 0; k < d; k++) f[1 + k] = x_new[k];
+  long double fb = 0.0L, vz = 0.0L;
+  for (int j = 0; j < p; j++) fb += (long double)f[j] * m->h_beta[j];
+  for (int i = 0; i < n; i++) vz += (long double)v[i] * m->h_zM[i];
+  const double znew = (double)(((long double)y_new - fb - vz) / t);
+  for (int j = 0; j < p; j++) {
+    long double vm = 0.0L;
+    const double* Mj = m->h_zM + (size_t)(1 + j) * ld;
+    for (int i = 0; i < n; i++) vm += (long double)v[i] * Mj[i];
+    mnew[j] = (double)(((long double)f[j] - vm) / t);
+  }
+  // u = T^-1 v (column-oriented back substitution: column k of T is contiguous)
+  u = v;
+  for (int k = n - 1; k >= 0; k--) {
+    const double* col = m->h_T + (size_t)k * ld;
+    u[k] /= col[k];
+    const double uk = u[k];
+    for (int i = 0; i < k; i++) u[i] -= uk * col[i];
+  }
+  // ---- host state ----
+  std::memcpy(m->h_T + (size_t)n * ld, v.data(), (size_t)n * 8);
+  m->h_T[(size_t)n * ld + n] = t;
+  m->h_zM[n] = znew;
+  for (int j = 0; j < p; j++) m->h_zM[(size_t)(1 + j) * ld + n] = mnew[j];
+  for (int c = 0; c <= p; c++) {
+    double* col = m->h_aK + (size_t)c * ld;
+    const double a = (c == 0 ? znew : mnew[c - 1]) / t;
+    for (int i = 0; i < n; i++) col[i] -= a * u[i];
+    col[n] = a;
+  }
+  for (int a = 0; a < p; a++)
+    for (int b = 0; b < p; b++) m->h_G[a + (size_t)b * p] += mnew[a] * mnew[b];
+  m->h_y[n] = y_new;
+  if (m->h_nv) m->h_nv[n] = new_noise_var;
+  std::memcpy(m->h_X + (size_t)n * d, x_new, (size_t)d * 8);
+  // ---- device: lazily built pieces go stale, sizes move on ----
+  free_lazy(m);
+  const int I0 = n / BM;                        // first block row that holds row n of L_aug
+  m->n = n + 1;
+  dm.n = n + 1;
+  dm.n_aug = n + 1 + p + 1;
+  dm.nblk = (dm.n_aug + BM - 1) / BM;
+  dm.n_pad = dm.nblk * BM;
+  dm.nblk_b = (n + 1 + BM - 1) / BM;
+  std::vector<double> tiles;
+  try {
+    AugFactor L{m->h_T, m->h_zM, m->h_zM + ld, n + 1, p, dm.n_aug, ld, ld};
+    build_tiles(L, dm.nblk, tiles, I0);
+  } catch (const std::bad_alloc&) {
+    return fail(DK_ERR_NOMEM, "host allocation failed while tiling the new rows");
+  }
+  if (tile_base(dm.nblk) * A_TILE > m->tiles_fwd_doubles) return fail(DK_ERR_NOMEM, "internal: tile capacity exceeded");
+  DK_CUDA_TRY(cudaMemcpy(m->d_tiles_fwd + tile_base(I0) * A_TILE, tiles.data(), tiles.size() * 8, cudaMemcpyHostToDevice));
+  // design row n in its three forms (plain, scaled by w_k, rounded to 8 digits)
+  const size_t cap_pad = m->scratch_doubles_per_cta / BN;
+  std::vector<double> row(3 * (size_t)d);
+  for (int k = 0; k < d; k++) {
+    row[k] = x_new[k];
+    row[d + k] = x_new[k] * dm.w[k];
+    row[2 * d + k] = std::nearbyint(x_new[k] * 1e8) / 1e8;
+  }
+  for (int a = 0; a < 3; a++)
+    DK_CUDA_TRY(cudaMemcpy(m->d_Xrm + (size_t)a * cap_pad * d + (size_t)n * d, row.data() + (size_t)a * d, (size_t)d * 8,
+                           cudaMemcpyHostToDevice));
+  if ((rc = upload_small(m))) return rc;
+  return DK_OK;
+}
+
+extern "C" {
+
+int dk_model_n(const dk_model* m) { return m ? m->n : 0; }
 
 void dk_model_destroy(dk_model* m) {
   if (!m) return;
@@ -665,6 +971,8 @@ void dk_model_destroy(dk_model* m) {
   if (m->ev1) cudaEventDestroy(m->ev1);
   if (m->ev_mid) cudaEventDestroy(m->ev_mid);
   std::free(m->h_T);
+  std::free(m->h_X);
+  std::free(m->h_aK);
   std::free(m->h_zM);
   std::free(m->h_y);
   std::free(m->h_nv);
@@ -1005,8 +1313,8 @@ int dk_debug_plain(dk_model* m, const double* x, int64_t N, int mode, double plu
   DK_CUDA_TRY(bv.alloc((size_t)n * N));
   DK_CUDA_TRY(bxo.alloc((size_t)N * (m->d + 3)));
   double *d_T = bT.p, *d_zM = bzM.p, *d_v = bv.p, *d_xo = bxo.p;
-  DK_CUDA_TRY(cudaMemcpy(d_T, m->h_T, (size_t)n * n * 8, cudaMemcpyHostToDevice));
-  DK_CUDA_TRY(cudaMemcpy(d_zM, m->h_zM, (size_t)n * (p + 1) * 8, cudaMemcpyHostToDevice));
+  DK_CUDA_TRY(cudaMemcpy2D(d_T, (size_t)n * 8, m->h_T, (size_t)m->ld * 8, (size_t)n * 8, n, cudaMemcpyHostToDevice));
+  DK_CUDA_TRY(cudaMemcpy2D(d_zM, (size_t)n * 8, m->h_zM, (size_t)m->ld * 8, (size_t)n * 8, p + 1, cudaMemcpyHostToDevice));
   DK_CUDA_TRY(cudaMemcpy(d_xo, x, (size_t)N * m->d * 8, cudaMemcpyHostToDevice));
   double* d_main = d_xo + (size_t)N * m->d;
   CritParams P{mode, type, minimization, proxy, plugin, qnorm_beta};

@@ -119,7 +119,7 @@ struct dk_model {
   double* d_tiles_bwd = nullptr;
   double* d_Xrm = nullptr;
   double* d_small = nullptr;     // beta | RM | tuuinv | alpha | KinvF | noise_var
-  size_t tiles_fwd_doubles = 0, xrm_doubles = 0, small_doubles = 0;  // sizes of the three uploads (dk_model_clone)
+  size_t tiles_fwd_doubles = 0, xrm_doubles = 0, small_doubles = 0, bwd_tile_doubles = 0;  // sizes of the three uploads (dk_model_clone)
   double* d_vscratch = nullptr;  // per-CTA V panels (forward solve), grid x n_pad x 64 doubles
   double* d_wscratch = nullptr;  // per-CTA W panels (backward solve)
   double* d_cscratch = nullptr;  // per-CTA covariance panels kept for the gradient kernels
@@ -150,8 +150,15 @@ struct dk_model {
   size_t device_bytes = 0;
   // host copies kept for lazily built pieces
   int n = 0, d = 0, p = 0;
-  double* h_T = nullptr;         // n x n column-major copy (for the backward tiles)
-  double* h_zM = nullptr;        // [z | M], n x (p+1) column-major
+  // Host copies use the leading dimension `ld` (= n after dk_model_create, the capacity after dk_model_append grew it).
+  int ld = 0;                    // leading dimension of h_T, h_zM, h_aK; rows held by h_y, h_nv, h_X
+  bool bwd_valid = false;        // d_tiles_bwd matches the current factor (dk_model_append invalidates it)
+  double* h_X = nullptr;         // design, ld x d row-major
+  double* h_aK = nullptr;        // [alpha | T^-1 M], ld x (p+1) column-major
+  double h_G[DK_MAX_P * DK_MAX_P] = {};   // M'M, p x p
+  double h_beta[DK_MAX_P] = {};
+  double* h_T = nullptr;         // ld x ld column-major copy of the upper factor (for the backward tiles)
+  double* h_zM = nullptr;        // [z | M], ld x (p+1) column-major
   double* h_y = nullptr;         // n
   double* h_nv = nullptr;        // n noise.var or NULL
   double* d_akg_const = nullptr; // a_sorted | delta

@@ -20,10 +20,12 @@ from .km import KM
 from .synth import _corr
 
 
-def update_km(model: KM, x_new, y_new, new_noise_var: float = 0.0) -> KM:
+def update_km(model: KM, x_new, y_new, new_noise_var: float = 0.0, reuse_handles: bool = True) -> KM:
     """The km model with (x_new, y_new) appended; covariance parameters and trend.coef kept (the reference's
     ``computeAuxVariables`` after rbind of X, y, F).  Models with ``noise.var`` give the new point
-    ``new_noise_var`` (the reference's loop uses 0 there, R/max_qEI.R:311-314); nugget models add their nugget."""
+    ``new_noise_var`` (the reference's loop uses 0 there, R/max_qEI.R:311-314); nugget models add their nugget.
+    reuse_handles: the device handles of ``model`` are grown in place (dk_model_append: only the last block rows of the
+    tiled factor are rebuilt and uploaded) and MOVE to the returned model; ``model`` loses them."""
     x = np.asarray(x_new, float).reshape(1, -1)
     if x.shape[1] != model.d:
         raise ValueError("x_new does not have the right size")
@@ -45,6 +47,20 @@ def update_km(model: KM, x_new, y_new, new_noise_var: float = 0.0) -> KM:
     z_new = (float(y_new) - float(f @ model.trend_coef) - float(v @ model.z)) / t
     m_new = (f - v @ M) / t
     nv = None if model.noise_var is None else np.append(model.noise_var, float(new_noise_var))
-    return KM(X=np.vstack([model.X, x]), y=np.append(model.y, float(y_new)), F=np.vstack([model.F, f[None, :]]),
+    handles = {}
+    if reuse_handles and model._handles:
+        from . import _lib
+        import ctypes as C
+        lib = _lib.load()
+        xc = np.ascontiguousarray(x[0])
+        for dev, h in list(model._handles.items()):
+            _lib.check(lib.dk_model_append(h.ptr, C.c_void_p(xc.ctypes.data), float(y_new), float(new_noise_var)),
+                       "dk_model_append")
+            h.n = n + 1
+            handles[dev] = h
+        model._handles.clear()
+    new = KM(X=np.vstack([model.X, x]), y=np.append(model.y, float(y_new)), F=np.vstack([model.F, f[None, :]]),
               trend=model.trend, trend_coef=model.trend_coef, covariance=cov, T=T, z=np.append(model.z, z_new),
               M=np.vstack([M, m_new[None, :]]), noise_var=nv)
+    new._handles.update(handles)
+    return new

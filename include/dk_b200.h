@@ -81,6 +81,17 @@ const char* dk_version(void);
  * candidate-independent arrays (alpha = T^-1 z, T^-1 M, (M'M)^-1, chol(M'M), block inverses). */
 int dk_model_create(const dk_model_desc* desc, dk_model** out);
 void dk_model_destroy(dk_model* m);
+/* One more observation (x_new[d], y_new) with the covariance parameters and trend.coef unchanged — replaces the
+ * rbind(X, x) / computeAuxVariables refresh of the constant-liar loop, /root/reference/R/max_qEI.R:305-316 (and update()
+ * with cov.reestim = FALSE, R/fastEGO.nsteps.R:231-235), which re-factorises the whole model (n^3 / 3 flops) and, with a
+ * device handle, re-tiles and re-uploads it.  Here the new Cholesky column is one forward substitution (n^2 flops on
+ * the host), and on the device only the block rows of the tiled factor that hold the new row change (one or two of
+ * n / 128), plus one design row and the O(n p) weight vectors.  new_noise_var is the new point's noise.var for models
+ * that have one (the reference's loop uses 0).  Buffers grow by 256 rows at a time when the padded capacity runs out.
+ * The pieces built lazily from the factor (backward tiles for gradients, AKG constants, K^-1) are rebuilt on next use.
+ * Not to be called while another call on the handle is in flight.  dk_model_n: the handle's current design size. */
+int dk_model_append(dk_model* m, const double* x_new, double y_new, double new_noise_var);
+int dk_model_n(const dk_model* m);
 /* Device-memory bytes held by the handle (tiles + scratch). */
 size_t dk_model_device_bytes(const dk_model* m);
 /* Number of kernels launched through the handle so far (bench.py's gpu_launches). */

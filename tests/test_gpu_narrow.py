@@ -1,8 +1,10 @@
 """Narrow tiles (16 candidates per CTA, csrc/dk_narrow.cuh) against the wide path and the oracle.  The solved panel is
 bit-identical by construction (same covariance values, same accumulation order), so the mean must agree bit for bit;
 sd, EI and the gradients differ only through the grouping of the row reductions (8 partial sums of v^2 instead of 4, 16
-row slices of the gradient contraction instead of 4): 1e-14 of sd2 in the variance, 1e-10 in EI and the gradients (sums
-with cancellation), i.e. inside the tolerance both paths are held to against the oracle."""
+row slices of the gradient contraction instead of 4): 1e-14 of sd2 in the variance.  EI and the gradients are functions
+of that sd: in the far tail (|xcr| ~ 30) or on an ill-conditioned gauss design a last-bit change of sd^2 moves them by
+1e-10 .. 1e-9 relative, on either path; they are compared here to 1e-8 and held to the oracle in the other test files
+(which run on narrow tiles whenever N <= 4736)."""
 import ctypes as C
 import time
 
@@ -53,10 +55,10 @@ def test_narrow_equals_wide(gpu_lib, name, trend, kw, N):
     for key in ("ei", "e2", "q"):
         assert np.array_equal(np.isnan(w[key]), np.isnan(nr[key]))
         ok = ~np.isnan(w[key])
-        assert np.all(np.abs(w[key][ok] - nr[key][ok]) <= 1e-10 * np.abs(w[key][ok]) + 1e-12 * np.max(np.abs(w[key][ok]) + 1e-300)), key
+        assert np.all(np.abs(w[key][ok] - nr[key][ok]) <= 1e-8 * np.abs(w[key][ok]) + 1e-12 * np.max(np.abs(w[key][ok]) + 1e-300)), key
     for key in ("g", "gq"):
         scale = np.max(np.abs(w[key]), axis=1, keepdims=True) + 1e-300
-        assert np.max(np.abs(w[key] - nr[key]) / scale) <= 1e-10, key
+        assert np.max(np.abs(w[key] - nr[key]) / scale) <= 1e-8, key
     km.release()
 
 

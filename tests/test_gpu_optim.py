@@ -142,7 +142,7 @@ def test_device_polish_matches_host_batched_lbfgs(gpu_lib):
     assert dev["f"].max() >= (-host["f"]).max() * (1 - 1e-6)
     g = EI_grad(dev["x"], km)
     best = int(np.argmax(dev["f"]))
-    assert _projected_grad_norm(g[best], dev["x"][best], lo, up) <= 1e-4 * dev["f"][best] + 1e-10
+    assert _projected_grad_norm(g[best], dev["x"][best], lo, up) <= 1e-3 * dev["f"][best] + 1e-10    # stopped by factr, as optim
     km.release()
 
 
@@ -197,3 +197,34 @@ def test_sample_from_ei_on_device_follows_the_weights(gpu_lib):
     gpu_lib.dk_sample_from_ei(h.ptr, C.c_void_p(x.ctypes.data), N, T, 1, 5, 99, C.c_void_p(b.ctypes.data))
     assert np.array_equal(a, b)
     km.release()
+
+
+def test_model_append_in_place_matches_rebuild(gpu_lib):
+    """dk_model_append (in-place growth of the device handle: last block rows of the tiled factor only) against a handle
+    created from scratch for the grown model: forward path (EI), gradient path (backward tiles rebuilt lazily), AKG
+    constants, qEI's duplicate rule on the appended row; across a block-row boundary and a capacity growth."""
+    from diceoptim_b200 import AKG, EI, EI_grad, qEI, synth
+    from diceoptim_b200.update import update_km
+    X = synth.lhs(250, 3, 5); y = np.sin(3 * X.sum(1))
+    km = synth.make_km(X, y, "matern5_2", 0.5, float(np.var(y)), trend="linear", noise_var=0.01)
+    x = np.random.default_rng(3).random((300, 3))
+    EI(x, km); EI_grad(x[:20], km); AKG(x[:20], km, new_noise_var=0.01)      # build the lazily made pieces first
+    pts = np.random.default_rng(4).random((12, 3))
+    cur = km
+    for i, xn in enumerate(pts):                                            # 250 -> 262 rows: crosses 256, grows capacity
+        cur = update_km(cur, xn, float(np.cos(i)), new_noise_var=0.0)
+        assert cur._handles and not km._handles or i > 0
+    assert gpu_lib.dk_model_n(cur.handle(0).ptr) == 262
+    fresh = update_km(km, pts[0], 1.0, reuse_handles=False)
+    for i, xn in enumerate(pts[1:], 1):
+        fresh = update_km(fresh, xn, float(np.cos(i)), reuse_handles=False)
+    a = EI(x, cur); b = EI(x, fresh)
+    assert np.all(np.abs(a - b) <= 1e-9 * np.abs(b) + 1e-12 * b.max())
+    ga = EI_grad(x[:40], cur); gb = EI_grad(x[:40], fresh)
+    assert np.max(np.abs(ga - gb)) <= 1e-9 * np.max(np.abs(gb))
+    ka = AKG(x[:40], cur, new_noise_var=0.01); kb = AKG(x[:40], fresh, new_noise_var=0.01)
+    assert np.all(np.abs(ka - kb) <= 1e-7 * np.abs(kb) + 1e-11)
+    xb = np.stack([np.vstack([pts[3], x[0], x[1]]), x[2:5]])               # batch 0 holds an appended design row
+    qa = qEI(xb, cur, plugin=float(np.median(y))); qb = qEI(xb, fresh, plugin=float(np.median(y)))
+    assert np.all(np.abs(qa - qb) <= 1e-9 * np.abs(qb) + 1e-12)
+    cur.release(); fresh.release()
