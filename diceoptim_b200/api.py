@@ -631,7 +631,8 @@ def _max_qEI_CL(model: KM, npoints, L, lower, upper, parinit=None, minimization=
     """max_qEI.CL, R/max_qEI.R:283-318: npoints rounds of max_EI, after each of which the maximiser joins the design
     with a "lie" as response (L = NULL: min(y) or max(y); "min"; "max"; "mean" = kriging believer; or a number) and the
     model's T, z, M are refreshed with covariance and trend coefficients kept.  The refresh is the n^2 append of
-    ``update_km`` instead of computeAuxVariables' full Cholesky."""
+    ``update_km`` instead of computeAuxVariables' full Cholesky, and the device handle grows IN PLACE (dk_model_append on a
+    device-to-device replica of the caller's handle: per round only the last block rows of the tiled factor are rebuilt)."""
     from .update import update_km
     n1 = model.n
     KB = False
@@ -659,7 +660,7 @@ def _max_qEI_CL(model: KM, npoints, L, lower, upper, parinit=None, minimization=
                    seed=int(rng.integers(1 << 31)), device=device)
         if KB:
             liar = float(predict(cur, o["par"], device=device)["mean"][0])
-        nxt = update_km(cur, o["par"], liar, new_noise_var=0.0)
+        nxt = update_km(cur, o["par"], liar, new_noise_var=0.0, reuse_handles="clone" if cur is model else True)
         if cur is not model:
             cur.release()
         cur = nxt

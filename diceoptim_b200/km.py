@@ -152,6 +152,16 @@ class DeviceModel:
             raise _lib.DkError("device model already destroyed")
         return self._h
 
+    def clone(self, device=None) -> "DeviceModel":
+        """A replica of this handle (device-to-device copy of the tiled model, no re-tiling on the host)."""
+        new = object.__new__(DeviceModel)
+        out = C.c_void_p()
+        dev = self.device if device is None else int(device)
+        _lib.check(self._lib.dk_model_clone(self.ptr, dev, C.byref(out)), "dk_model_clone")
+        new._h, new._lib = out, self._lib
+        new.n, new.d, new.p, new.device = self.n, self.d, self.p, dev
+        return new
+
     def device_bytes(self) -> int:
         return int(self._lib.dk_model_device_bytes(self.ptr))
 

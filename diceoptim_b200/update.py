@@ -24,8 +24,10 @@ def update_km(model: KM, x_new, y_new, new_noise_var: float = 0.0, reuse_handles
     """The km model with (x_new, y_new) appended; covariance parameters and trend.coef kept (the reference's
     ``computeAuxVariables`` after rbind of X, y, F).  Models with ``noise.var`` give the new point
     ``new_noise_var`` (the reference's loop uses 0 there, R/max_qEI.R:311-314); nugget models add their nugget.
-    reuse_handles: the device handles of ``model`` are grown in place (dk_model_append: only the last block rows of the
-    tiled factor are rebuilt and uploaded) and MOVE to the returned model; ``model`` loses them."""
+    reuse_handles: True: the device handles of ``model`` are grown in place (dk_model_append: only the last block rows of
+    the tiled factor are rebuilt and uploaded) and MOVE to the returned model, ``model`` loses them; "clone": replicas of
+    them (device-to-device copies) are grown instead and ``model`` keeps its own; False: the new model builds its handle
+    from scratch on first use."""
     x = np.asarray(x_new, float).reshape(1, -1)
     if x.shape[1] != model.d:
         raise ValueError("x_new does not have the right size")
@@ -54,11 +56,14 @@ def update_km(model: KM, x_new, y_new, new_noise_var: float = 0.0, reuse_handles
         lib = _lib.load()
         xc = np.ascontiguousarray(x[0])
         for dev, h in list(model._handles.items()):
+            if reuse_handles == "clone":
+                h = h.clone()
             _lib.check(lib.dk_model_append(h.ptr, C.c_void_p(xc.ctypes.data), float(y_new), float(new_noise_var)),
                        "dk_model_append")
             h.n = n + 1
             handles[dev] = h
-        model._handles.clear()
+        if reuse_handles != "clone":
+            model._handles.clear()
     new = KM(X=np.vstack([model.X, x]), y=np.append(model.y, float(y_new)), F=np.vstack([model.F, f[None, :]]),
               trend=model.trend, trend_coef=model.trend_coef, covariance=cov, T=T, z=np.append(model.z, z_new),
               M=np.vstack([M, m_new[None, :]]), noise_var=nv)

@@ -26,7 +26,7 @@ def _both(gpu_lib, km, x, type=1):
     h = km.handle(0)
     N, d = x.shape
     x = np.asfortranarray(x)
-    pl = float(np.min(km.y))
+    pl = float(np.median(km.y))      # a reachable target: EI of order 0.1 everywhere, not 1e-200 tails
     out = {}
     for mode in (WIDE, NARROW):
         _lib.check(gpu_lib.dk_model_set_tile_mode(h.ptr, mode), "tile mode")
