@@ -70,11 +70,12 @@ def test_narrow_vs_oracle_multi_block_and_timing(gpu_lib):
     ko = to_oracle(km)
     x = synth.config_candidates("cfg4_sphere10_n2000", N=16, rank=5)
     o = _both(gpu_lib, km, x)
-    ref = do.EI(x, ko)
+    plm = float(np.median(km.y))                        # _both's plugin
+    ref = do.EI(x, ko, plugin=plm)
     for mode in (WIDE, NARROW):
         assert np.all(np.abs(o[mode]["ei"] - ref) <= 1e-10 * np.abs(ref) + 1e-12 * ref.max())
     for j in (0, 7, 15):
-        gr = do.EI_grad(x[j], ko)
+        gr = do.EI_grad(x[j], ko, plugin=plm)
         assert np.max(np.abs(o[NARROW]["g"][j] - gr)) <= 1e-10 * np.max(np.abs(gr)) + 1e-14
     # latency of one 16-candidate call through the host entry points (H2D + kernel + D2H), best of 5
     h = km.handle(0)

@@ -14,6 +14,21 @@ x = synth.config_candidates("cfg4_sphere10_n2000", N=4096)
 pts = np.random.default_rng(1).random((8, km.d))
 EI(x, km); EI_grad(x[:16], km)
 res = {}
+# the C call alone (no Python KM bookkeeping): dk_model_append on a replica, 8 points
+import ctypes as C
+from diceoptim_b200 import _lib
+lib = _lib.load()
+hc = km.handle(0).clone()
+t0 = time.perf_counter()
+for i in range(8):
+    xc = np.ascontiguousarray(pts[i])
+    _lib.check(lib.dk_model_append(hc.ptr, C.c_void_p(xc.ctypes.data), float(np.min(km.y)), 0.0), "append")
+res["dk_model_append_ms_per_point"] = 1e3 * (time.perf_counter() - t0) / 8
+hc.close()
+t0 = time.perf_counter()
+for i in range(3):
+    hh = type(km.handle(0))(km, 0); hh.close()
+res["dk_model_create_ms"] = 1e3 * (time.perf_counter() - t0) / 3
 for mode in ("in_place", "rebuild"):
     cur = km
     t_upd = t_fwd = t_grad = 0.0
