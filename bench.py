@@ -242,9 +242,11 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
     torch.cuda.set_device(local)
+    host_group = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        host_group = dist.new_group(backend="gloo")     # CPU-side barrier: ranks that wait must not spin a kernel on their GPU
     lib = _lib.load()
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
@@ -552,7 +554,8 @@ def main():
             extra["weak"] = {"value": world * NT * args.steps / (msw * 1e-3), "unit": UNIT, "candidates_per_gpu_per_step": NT}
             del xw
 
-        # ---- one process, all N GPUs: dk_multi_screen_ei with the whole host matrix (rank 0; the others wait) ----
+        # ---- one process, all N GPUs: dk_multi_screen_ei with the whole host matrix (rank 0; the others wait on a
+        #      HOST barrier: an NCCL barrier would keep a spinning kernel on the very GPUs rank 0 is about to use) ----
         barrier()
         if rank == 0:
             ndev = min(world, torch.cuda.device_count())
@@ -564,10 +567,11 @@ def main():
             call = lambda: _lib.check(lib.dk_multi_screen_ei(mm, vp(x_all), NT, plugin, 1, 1, 0, 1, vp(im), vp(vm)), "dk_multi_screen_ei")
             call()
             t0 = time.perf_counter(); call(); dtm = time.perf_counter() - t0
-            extra["single_process"] = {"value": NT / dtm, "unit": UNIT, "devices": ndev, "timing": "host wall clock around one call",
+            extra["single_process"] = {"value": NT / dtm, "unit": UNIT, "devices": ndev, "timing": "host wall clock around one call (pageable host matrix, copies included)",
                                        "argmax_equals_sharded": bool(int(im[0]) == res_dev[0] and float(vm[0]) == res_dev[1])}
             mdm.close()
-        barrier()
+        if host_group is not None:
+            dist.barrier(group=host_group)
 
     if rank == 0:
         # CPU baselines: the oracle port on bounded samples of the same workloads, host cores
