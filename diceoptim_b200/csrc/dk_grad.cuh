@@ -200,7 +200,7 @@ k_grad_fused(const DevModel M, const CritParams P, const double* __restrict__ x,
             acc[mi][ni][e] = v;
           }
       }
-      solve_block_row<true>(acc, M.tiles_bwd, I, wpanel, smem, tid, &stage_base);
+      solve_block_row<true>(acc, M.tiles_bwd, I, wpanel, smem, tid, &stage_base, min(BM, n - I * BM));
       __syncthreads();
     }
 

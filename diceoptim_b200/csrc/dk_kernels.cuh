@@ -70,6 +70,26 @@ __device__ __forceinline__ void mma_stage(double (&acc)[4][4][2], const double* 
       for (int ni = 0; ni < 4; ni++) dmma884(acc[mi][ni], a[mi], b[ni]);
   }
 }
+// The same for ONE of the warp's two 16-row pairs (half = 0: rows 32 wm .. +15, acc[0..1]; half = 1: acc[2..3]): the
+// last block row of a small design is mostly padding, and a pair that is all padding has nothing to accumulate.
+__device__ __forceinline__ void mma_stage_half(double (&acc)[4][4][2], const double* __restrict__ As,
+                                               const double* __restrict__ Bs, int wm, int wn, int lane, int half) {
+#pragma unroll
+  for (int k4 = 0; k4 < 4; k4++) {
+    const double2 a = *reinterpret_cast<const double2*>(As + (((2 * wm + half) * 4 + k4) * 32 + lane) * 2);
+    const double2 b01 = *reinterpret_cast<const double2*>(Bs + ((k4 * 4 + 2 * wn) * 32 + lane) * 2);
+    const double2 b23 = *reinterpret_cast<const double2*>(Bs + ((k4 * 4 + 2 * wn + 1) * 32 + lane) * 2);
+    const double b[4] = {b01.x, b01.y, b23.x, b23.y};
+#pragma unroll
+    for (int ni = 0; ni < 4; ni++) { dmma884(acc[2 * half][ni], a.x, b[ni]); dmma884(acc[2 * half + 1][ni], a.y, b[ni]); }
+  }
+}
+// live16 = number of 16-row pairs of this block row that hold real rows (8 everywhere but in the last block row)
+__device__ __forceinline__ void mma_stage_live(double (&acc)[4][4][2], const double* __restrict__ As,
+                                               const double* __restrict__ Bs, int wm, int wn, int lane, int live16) {
+  if (2 * wm + 1 < live16) mma_stage(acc, As, Bs, wm, wn, lane);
+  else if (2 * wm < live16) mma_stage_half(acc, As, Bs, wm, wn, lane, 0);
+}
 
 // Row ownership AFTER the diagonal phase of solve_block_row.  The inverse of a diagonal block is lower triangular: the
 // 16-row pair q of the block needs the k-chunks 0..q only.  With the GEMM-phase ownership (warp row wm owns pairs 2wm,
@@ -123,6 +143,16 @@ __device__ __forceinline__ void covgen_rows(const DevModel& M, const double* __r
   const int d = M.d;
 #pragma unroll 1
   for (int rr = 0; rr < 16; rr += RB) {
+#ifndef DK_X_NOSKIP
+    if (row0_global + 16 * warp + rr >= M.n) {   // eight rows beyond the design (padding, augmented rows): zeros
+#pragma unroll
+      for (int j = 0; j < RB; j++) {
+        Cbuf[(16 * warp + rr + j) * CB_STRIDE + lane] = 0.0;
+        Cbuf[(16 * warp + rr + j) * CB_STRIDE + lane + 32] = 0.0;
+      }
+      continue;
+    }
+#endif
     double s[RB][2], pr[RB][2], hs[NUG ? RB : 1][2];
 #pragma unroll
     for (int j = 0; j < RB; j++) {
@@ -246,12 +276,20 @@ __device__ __forceinline__ void pipeline_init(unsigned char* smem, int tid) {
 // TMA = true: the GEMM phase is fed by bulk asynchronous copies (one 16 KB A tile + one 8 KB B tile per stage,
 // issued by thread 0) and synchronised per stage by full/empty mbarriers instead of __syncthreads; `stage_base`
 // counts the stages this CTA has consumed so far (slot = index % STAGES, parity = (index / STAGES) & 1).
+// live_rows: rows of this block row that are real (< 128 only in the last block row of the system); 16-row pairs made of
+// padding alone are skipped in both phases (their V is zero: zero right-hand side, identity diagonal).
 template <bool TMA = false>
 __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const double* __restrict__ tiles, int I,
                                                 double* __restrict__ panel, unsigned char* smem, int tid,
-                                                unsigned* stage_base = nullptr) {
+                                                unsigned* stage_base = nullptr, int live_rows = BM) {
   DK_MARK_INIT;
   const int warp = tid >> 5, lane = tid & 31, wm = warp >> 1, wn = warp & 1;
+#ifdef DK_X_NOSKIP   // what-if build: execute the padded pairs as round 1 did
+  const int live16 = 8;
+  (void)live_rows;
+#else
+  const int live16 = (live_rows + 15) >> 4;
+#endif
   double* ring = reinterpret_cast<double*>(smem);
   const double* Atiles = tiles + tile_base(I) * A_TILE;
   const int nk = CHUNKS_PER_BLOCK * I;
@@ -282,7 +320,7 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
       const unsigned gi = base + kc, slot = gi % STAGES, par = (gi / STAGES) & 1;
       mbar_wait(&full[slot], par);
       const double* s = ring + slot * (A_TILE + B_TILE);
-      mma_stage(acc, s, s + A_TILE, wm, wn, lane);
+      mma_stage_live(acc, s, s + A_TILE, wm, wn, lane, live16);
       // this slot is refilled through the async proxy: order this lane's generic-proxy reads of it before that
       // (without this fence the refill raced the LDS reads: about one corrupted tile in a thousand)
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -317,7 +355,7 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
       cp_async_commit();
     }
     const double* slot = ring + (kc % STAGES) * (A_TILE + B_TILE);
-    mma_stage(acc, slot, slot + A_TILE, wm, wn, lane);
+    mma_stage_live(acc, slot, slot + A_TILE, wm, wn, lane, live16);
   }
   cp_async_wait<0>();
   __syncthreads();  // every warp is done with the ring: region 0 can change role
@@ -356,7 +394,8 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
       cp_async_commit();
     }
     // inverse is lower triangular: pair q needs chunks 0..q (see solved_pair)
-    if (j <= 7 - wm) mma_stage_diag(acc, Abuf + (j & 1) * A_TILE, Rbuf + j * B_TILE, wm, wn, lane, j <= wm, true);
+    if (j <= 7 - wm && (wm < live16 || 7 - wm < live16))
+      mma_stage_diag(acc, Abuf + (j & 1) * A_TILE, Rbuf + j * B_TILE, wm, wn, lane, j <= wm && wm < live16, 7 - wm < live16);
   }
 
   DK_MARK(3);
@@ -540,7 +579,7 @@ __device__ __forceinline__ void forward_tile(const DevModel& M, const double* __
     __syncthreads();
     DK_MARK(0);  // P1 + P2: cov-gen and fragment load
     // ---- P3..P5 ----
-    solve_block_row<TMA>(acc, M.tiles_fwd, I, panel, smem, tid, stage_base);
+    solve_block_row<TMA>(acc, M.tiles_fwd, I, panel, smem, tid, stage_base, min(BM, M.n_aug - I * BM));
     DK_MARK(7);  // (solve_block_row accounts 2 = GEMM, 3 = diagonal, 4 = panel store itself)
     // ---- s2 += sum over this block's real rows of v^2 (fixed order: rows, then lanes, then warps) ----
     {

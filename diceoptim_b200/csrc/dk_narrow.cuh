@@ -37,6 +37,11 @@ __device__ __forceinline__ void covgen_rows_narrow(const DevModel& M, const doub
                                                    int row0_global, int warp, int lane) {
   constexpr int RB = 8;
   const int d = M.d, col = lane & 15, rr = 8 * (lane >> 4);
+  if (row0_global + 16 * warp + rr >= M.n) {   // eight rows beyond the design: zeros
+#pragma unroll
+    for (int j = 0; j < RB; j++) Cbuf[(16 * warp + rr + j) * CB_STRIDE + col] = 0.0;
+    return;
+  }
   double s[RB], pr[RB], hs[NUG ? RB : 1];
 #pragma unroll
   for (int j = 0; j < RB; j++) {
@@ -97,8 +102,9 @@ __device__ __forceinline__ void covgen_block_narrow(const DevModel& M, const dou
 // acc[mi][ni][e]: row 16 warp + 8 mi + (lane >> 2), column 8 ni + 2 (lane & 3) + e.
 __device__ __forceinline__ void solve_block_row_narrow(double (&acc)[2][2][2], const double* __restrict__ tiles, int I,
                                                        double* __restrict__ panel, unsigned char* smem, int tid,
-                                                       unsigned* stage_base) {
+                                                       unsigned* stage_base, int live_rows = BM) {
   const int warp = tid >> 5, lane = tid & 31;
+  const bool pair_live = 16 * warp < live_rows;   // a row pair made of padding alone has nothing to accumulate
   double* ring = reinterpret_cast<double*>(smem);
   const double* Atiles = tiles + tile_base(I) * A_TILE;
   const int nk = CHUNKS_PER_BLOCK * I;
@@ -127,7 +133,7 @@ __device__ __forceinline__ void solve_block_row_narrow(double (&acc)[2][2][2], c
     const unsigned gi = base + kc, slot = gi % STAGES, par = (gi / STAGES) & 1;
     mbar_wait(&full[slot], par);
     const double* s = ring + slot * (A_TILE + B_TILE);
-    mma_stage_narrow(acc, s, s + A_TILE, warp, lane);
+    if (pair_live) mma_stage_narrow(acc, s, s + A_TILE, warp, lane);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[slot]);
@@ -161,7 +167,7 @@ __device__ __forceinline__ void solve_block_row_narrow(double (&acc)[2][2][2], c
       load_tile_async(Abuf + ((j + 1) & 1) * A_TILE, Dtiles + (size_t)(j + 1) * A_TILE, A_TILE, tid);
       cp_async_commit();
     }
-    if (j <= warp) mma_stage_narrow(acc, Abuf + (j & 1) * A_TILE, Rbuf + j * B_TILE, warp, lane);  // pair q: chunks 0..q
+    if (j <= warp && pair_live) mma_stage_narrow(acc, Abuf + (j & 1) * A_TILE, Rbuf + j * B_TILE, warp, lane);  // pair q: chunks 0..q
   }
   // ---- publish V_I ----
 #pragma unroll
@@ -248,7 +254,7 @@ __device__ __forceinline__ void forward_tile_narrow(const DevModel& M, const dou
         if (cpanel) *reinterpret_cast<double2*>(cpanel + (size_t)(I * BM + row) * BN + col) = v;
       }
     __syncthreads();
-    solve_block_row_narrow(acc, M.tiles_fwd, I, panel, smem, tid, stage_base);
+    solve_block_row_narrow(acc, M.tiles_fwd, I, panel, smem, tid, stage_base, min(BM, M.n_aug - I * BM));
     {
       double part[2][2];
 #pragma unroll
@@ -432,7 +438,7 @@ k_grad_narrow(const DevModel M, const CritParams P, const double* __restrict__ x
             acc[mi][ni][e] = v;
           }
       }
-      solve_block_row_narrow(acc, M.tiles_bwd, I, wpanel, smem, tid, &stage_base);
+      solve_block_row_narrow(acc, M.tiles_bwd, I, wpanel, smem, tid, &stage_base, min(BM, n - I * BM));
       __syncthreads();
     }
     // gradient reduction: 16 row slices x 16 candidates
