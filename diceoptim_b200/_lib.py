@@ -61,6 +61,7 @@ SIGNATURES = {
     "dk_model_last_kernel_ms": (_D, [_V]),
     "dk_model_last_phase_ms": (_D, [_V]),
     "dk_model_set_tile_mode": (_I, [_V, _I]),
+    "dk_model_prepare": (_I, [_V, _I]),
     "dk_predict": (_I, [_V, _V, _L, _I, _V, _V]),
     "dk_predict_dev": (_I, [_V, _V, _L, _I, _V, _V, _V]),
     "dk_ei": (_I, [_V, _V, _L, _D, _I, _I, _I, _V, _V, _V]),

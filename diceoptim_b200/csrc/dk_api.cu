@@ -1008,6 +1008,16 @@ double dk_model_last_kernel_ms(dk_model* m) {
   return (double)ms;
 }
 
+int dk_model_prepare(dk_model* m, int what) {
+  if (!m) return fail(DK_ERR_ARG, "model handle is NULL");
+  DeviceGuard guard(m->device);
+  int rc = DK_OK;
+  if (what & (DK_PREP_GRADIENTS | DK_PREP_AKG | DK_PREP_AKG_GRAD)) rc = ensure_bwd(m);
+  if (!rc && (what & (DK_PREP_AKG | DK_PREP_AKG_GRAD))) rc = prepare_akg(m, (what & DK_PREP_AKG_GRAD) != 0, m->stream);
+  if (!rc) DK_CUDA_TRY(cudaDeviceSynchronize());
+  return rc;
+}
+
 int dk_model_set_tile_mode(dk_model* m, int mode) {
   if (!m) return fail(DK_ERR_ARG, "model handle is NULL");
   if (mode != DK_TILE_AUTO && mode != DK_TILE_WIDE && mode != DK_TILE_NARROW) return fail(DK_ERR_ARG, "tile mode %d", mode);

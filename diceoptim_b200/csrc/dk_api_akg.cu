@@ -176,3 +176,11 @@ extern "C" int dk_akg_grad(dk_model* m, const double* x, int64_t N, double new_n
   if (rc) { cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
   return rc;
 }
+
+// the AKG family's lazily built pieces, for dk_model_prepare (dk_api.cu)
+int dk::prepare_akg(dk_model* m, bool with_grad, cudaStream_t st) {
+  int rc = ensure_bwd(m);
+  if (!rc) rc = ensure_akg(m);
+  if (!rc && with_grad) rc = ensure_akg_grad(m, st);
+  return rc;
+}

@@ -102,6 +102,7 @@ int host_screen(dk_model* m, const ScreenSpec& S, const double* x, int x_on_devi
                 int64_t row0, int64_t n, int k, int64_t* out_idx, double* out_val, cudaStream_t user_stream);
 void generated_rows(const dk_uniform_spec* gen, int d, const int64_t* idx, int k, double* out_x);
 int host_weights_to_vec(dk_model* m, const ScreenSpec& S, const double* x, int64_t N);
+int prepare_akg(dk_model* m, bool with_grad, cudaStream_t st);                    // dk_api_akg.cu
 int host_akg(dk_model* m, const double* x, int64_t ldx, int64_t row0, int64_t n, double new_noise_var, int type,
              double* out);                                                       // dk_api_akg.cu
 int host_qei(dk_model* m, const double* x, int64_t ldx, int64_t b0, int64_t nb, int q, double plugin, int type,

@@ -104,6 +104,13 @@ double dk_model_last_kernel_ms(dk_model* m);
  * timed call, < 0 if that call had a single kernel. */
 double dk_model_last_phase_ms(dk_model* m);
 
+/* Pieces of a handle that are built on first use — the flipped factor's tiles and the second panels (every gradient,
+ * AKG, covdist, crit_SUR_cst), the AKG constants, K^-1 for AKG.grad — allocate device memory, copy and (K^-1) launch on
+ * the FIRST call of their family, so that first *_dev call is not "enqueue only".  dk_model_prepare builds them up front
+ * (and synchronises), e.g. before a stream capture or a latency-sensitive loop.  what: OR of DK_PREP_*. */
+enum { DK_PREP_GRADIENTS = 1, DK_PREP_AKG = 2, DK_PREP_AKG_GRAD = 4 };
+int dk_model_prepare(dk_model* m, int what);
+
 /* Tile shape of the forward / gradient kernels (EI, quantile, predict, AEI, EQI and their gradients).  AUTO (default):
  * 16-candidate tiles when the call would leave three quarters of the persistent grid without a 64-candidate tile
  * (N <= 4736 on a B200: the optimiser-sized batches of optim(fn = EI, gr = EI.grad), /root/reference/R/max_crit.R:118-121),
