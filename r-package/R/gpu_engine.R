@@ -215,3 +215,45 @@ sampleFromEI <- function(model, minimization = TRUE, n = 1, initdistrib = NULL, 
   if (n == 1) my.points <- matrix(my.points, ncol = d)
   my.points
 }
+
+## ---- round-2 entry points ----
+.dk_crit <- function(criterion, type = "UK", minimization = TRUE, proxy = FALSE, plugin = 0, qnorm.beta = 0, new.noise.var = 0)
+  list(criterion = match(criterion, c("EI", "quantile", "AKG", "AEI", "EQI", "qEI")) - 1L, type = .type_id(type),
+       minimization = minimization, proxy = proxy, plugin = plugin, qnorm.beta = qnorm.beta, new.noise.var = new.noise.var)
+.dk_seed <- function() as.integer(c(sample.int(.Machine$integer.max, 1), sample.int(.Machine$integer.max, 1)))
+
+## The random search of max_crit with the N candidates drawn on the device (nothing is built in R nor uploaded): list(index, value, x).
+## The draws come from the library's counter-based generator seeded from R's RNG state, not from runif() itself.
+screen_generated <- function(model, N, lower, upper, criterion = "EI", k = 1L, ...)
+  .Call("dkR_screen_generated", dk_handle(model), as.numeric(N), as.numeric(lower), as.numeric(upper), .dk_seed(),
+        .dk_crit(criterion, ...), as.integer(k))
+
+## All starts polished together on the device (projected L-BFGS): x0 has one start per row (q rows per start for qEI)
+polish <- function(model, x0, lower, upper, criterion = "EI", q = 1L, maxit = 100L, ...)
+  .Call("dkR_polish", dk_handle(model), .dk_crit(criterion, ...), as.integer(q), .as_rows(x0, model@d), as.numeric(lower),
+        as.numeric(upper), as.integer(maxit))
+
+## max_crit with control$optimizer = "device": same screen, the polish of all restarts in one dk_polish call
+max_crit_device <- function(model, type = "UK", lower, upper, minimization = TRUE, control = NULL, proxy = FALSE) {
+  d <- ncol(model@X)
+  R <- if (is.null(control$restarts)) min(10, d) else control$restarts
+  N <- if (!is.null(control$n.ei)) control$n.ei else min(2e3, 500 * d)
+  plugin <- if (minimization) min(model@y) else -max(model@y)
+  starts <- t(sapply(seq_len(R), function(r)
+    screen_generated(model, N, lower, upper, "EI", 1L, type = type, minimization = minimization, proxy = proxy, plugin = plugin)[[3]]))
+  o <- polish(model, matrix(starts, ncol = d), lower, upper, "EI", type = type, minimization = TRUE, proxy = proxy, plugin = plugin)
+  I <- which.max(o[[2]])
+  list(par = as.numeric(o[[1]][I, ]), value = o[[2]][I])
+}
+
+## update of the constant-liar loop (R/max_qEI.R:305-316) on the device handle, in place: call it with the model BEFORE the
+## rbind and re-key the cache entry to the grown model afterwards (dk_rekey).
+dk_append <- function(model, x.new, y.new, new.noise.var = 0)
+  invisible(.Call("dkR_model_append", dk_handle(model), as.numeric(x.new), as.numeric(y.new), as.numeric(new.noise.var)))
+dk_rekey <- function(old.model, new.model, devices = getOption("DiceOptim.gpu.devices", 0L)) {
+  key <- function(m) paste0(.Call("dkR_model_key", .dk_slots(m)), "@", paste(devices, collapse = ","))
+  hs <- .dk_cache$handles
+  h <- hs[[key(old.model)]]
+  if (!is.null(h)) { hs[[key(old.model)]] <- NULL; hs[[key(new.model)]] <- h; .dk_cache$handles <- hs }
+  invisible(NULL)
+}

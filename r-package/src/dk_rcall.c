@@ -283,4 +283,82 @@ SEXP dkR_eqi(SEXP h, SEXP x, SEXP q_min, SEXP new_noise_var, SEXP qnorm_beta, SE
   if (rc) Rf_error("dk_eqi: %s", dk_last_error());
   return out;
 }
+/* ---- round-2 entry points: on-device candidates, on-device polish, on-device draw, in-place model growth ---- */
+
+static void fill_crit(dk_crit_spec* c, SEXP crit) {
+  /* crit: list(criterion, type, minimization, proxy, plugin, qnorm.beta, new.noise.var) */
+  c->criterion = Rf_asInteger(el(crit, "criterion"));
+  c->type = Rf_asInteger(el(crit, "type"));
+  c->minimization = Rf_asLogical(el(crit, "minimization"));
+  c->proxy = Rf_asLogical(el(crit, "proxy"));
+  c->plugin = Rf_asReal(el(crit, "plugin"));
+  c->qnorm_beta = Rf_asReal(el(crit, "qnorm.beta"));
+  c->new_noise_var = Rf_asReal(el(crit, "new.noise.var"));
+}
+
+/* The random search of max_crit (R/max_crit.R:104-107) with the candidates drawn ON the device: N uniform points in
+ * [lower, upper] from the counter-based generator seeded by `seed` (two integers: low and high 32 bits), criterion `crit`,
+ * the k best: list(index (1-based), value, x (k x d)). */
+SEXP dkR_screen_generated(SEXP h, SEXP N, SEXP lower, SEXP upper, SEXP seed, SEXP crit, SEXP k) {
+  dk_multi* m = multi_of(h);
+  int kk = Rf_asInteger(k), d = (int)Rf_xlength(lower);
+  dk_crit_spec c;
+  fill_crit(&c, crit);
+  dk_uniform_spec g;
+  g.seed = ((unsigned long long)(unsigned)INTEGER(seed)[1] << 32) | (unsigned)INTEGER(seed)[0];
+  g.lower = REAL(lower); g.upper = REAL(upper);
+  SEXP out = PROTECT(Rf_allocVector(VECSXP, 3));
+  SEXP idx = PROTECT(Rf_allocVector(REALSXP, kk));
+  SEXP val = PROTECT(Rf_allocVector(REALSXP, kk));
+  SEXP xs = PROTECT(Rf_allocMatrix(REALSXP, kk, d));
+  int64_t* tmp = (int64_t*)R_alloc(kk, sizeof(int64_t));
+  int rc = dk_multi_screen(m, NULL, &g, (int64_t)Rf_asReal(N), &c, kk, tmp, REAL(val), REAL(xs));
+  for (int i = 0; i < kk; i++) REAL(idx)[i] = tmp[i] < 0 ? NA_REAL : (double)(tmp[i] + 1);
+  SET_VECTOR_ELT(out, 0, idx); SET_VECTOR_ELT(out, 1, val); SET_VECTOR_ELT(out, 2, xs);
+  UNPROTECT(4);
+  if (rc) Rf_error("dk_screen: %s", dk_last_error());
+  return out;
+}
+
+/* The L-BFGS-B polish of all starts together on the device (replaces the optim() calls of R/max_crit.R:114-122 and
+ * R/max_qEI.R:204-222): x0 is (S q) x d, rows s q .. s q + q - 1 = start s; list(par, value, iterations). */
+SEXP dkR_polish(SEXP h, SEXP crit, SEXP q, SEXP x0, SEXP lower, SEXP upper, SEXP maxit) {
+  dk_model* m = handle_of(h);
+  dk_crit_spec c;
+  fill_crit(&c, crit);
+  int qq = Rf_asInteger(q), rows = Rf_nrows(x0), d = Rf_ncols(x0), S = rows / qq;
+  dk_lbfgs_options o = {Rf_asInteger(maxit), 8, 0.0, 1e7, 25};
+  SEXP out = PROTECT(Rf_allocVector(VECSXP, 3));
+  SEXP par = PROTECT(Rf_allocMatrix(REALSXP, rows, d));
+  SEXP val = PROTECT(Rf_allocVector(REALSXP, S));
+  SEXP its = PROTECT(Rf_allocVector(INTSXP, S));
+  int rc = dk_polish(m, &c, qq, REAL(x0), S, REAL(lower), REAL(upper), &o, REAL(par), REAL(val), INTEGER(its));
+  SET_VECTOR_ELT(out, 0, par); SET_VECTOR_ELT(out, 1, val); SET_VECTOR_ELT(out, 2, its);
+  UNPROTECT(4);
+  if (rc) Rf_error("dk_polish: %s", dk_last_error());
+  return out;
+}
+
+/* sampleFromEI's draw on the device (R/sampleFromEI.R:109-135): 1-based row indices of the n drawn points */
+SEXP dkR_sample_from_ei(SEXP h, SEXP x, SEXP T, SEXP minimization, SEXP n, SEXP seed) {
+  dk_model* m = handle_of(h);
+  int nn = Rf_asInteger(n);
+  SEXP idx = PROTECT(Rf_allocVector(REALSXP, nn));
+  int64_t* tmp = (int64_t*)R_alloc(nn, sizeof(int64_t));
+  unsigned long long s = ((unsigned long long)(unsigned)INTEGER(seed)[1] << 32) | (unsigned)INTEGER(seed)[0];
+  int rc = dk_sample_from_ei(m, REAL(x), (int64_t)Rf_nrows(x), Rf_asReal(T), Rf_asLogical(minimization), nn, s, tmp);
+  for (int i = 0; i < nn; i++) REAL(idx)[i] = (double)(tmp[i] + 1);
+  UNPROTECT(1);
+  if (rc) Rf_error("dk_sample_from_ei: %s", dk_last_error());
+  return idx;
+}
+
+/* One more observation in place (the refresh of the constant-liar loop, R/max_qEI.R:305-316), on every replica */
+SEXP dkR_model_append(SEXP h, SEXP x_new, SEXP y_new, SEXP new_noise_var) {
+  dk_multi* mm = multi_of(h);
+  for (int g = 0; g < dk_multi_count(mm); g++)
+    if (dk_model_append(dk_multi_model(mm, g), REAL(x_new), Rf_asReal(y_new), Rf_asReal(new_noise_var)))
+      Rf_error("dk_model_append: %s", dk_last_error());
+  return R_NilValue;
+}
 #endif /* DK_HAVE_R */

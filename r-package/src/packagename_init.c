@@ -25,6 +25,10 @@ extern SEXP dkR_predict(SEXP, SEXP, SEXP);
 extern SEXP dkR_akg_grad(SEXP, SEXP, SEXP, SEXP);
 extern SEXP dkR_aei(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
 extern SEXP dkR_eqi(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
+extern SEXP dkR_screen_generated(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
+extern SEXP dkR_polish(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
+extern SEXP dkR_sample_from_ei(SEXP, SEXP, SEXP, SEXP, SEXP, SEXP);
+extern SEXP dkR_model_append(SEXP, SEXP, SEXP, SEXP);
 
 static const R_CMethodDef CEntries[] = {{"davies", (DL_FUNC)&davies, 13}, {NULL, NULL, 0}};
 static const R_CallMethodDef CallEntries[] = {
@@ -38,6 +42,8 @@ static const R_CallMethodDef CallEntries[] = {
     {"dkR_release", (DL_FUNC)&dkR_release, 1},           {"dkR_model_key", (DL_FUNC)&dkR_model_key, 1},
     {"dkR_predict", (DL_FUNC)&dkR_predict, 3},           {"dkR_akg_grad", (DL_FUNC)&dkR_akg_grad, 4},
     {"dkR_aei", (DL_FUNC)&dkR_aei, 6},                   {"dkR_eqi", (DL_FUNC)&dkR_eqi, 7},
+    {"dkR_screen_generated", (DL_FUNC)&dkR_screen_generated, 7}, {"dkR_polish", (DL_FUNC)&dkR_polish, 7},
+    {"dkR_sample_from_ei", (DL_FUNC)&dkR_sample_from_ei, 6},     {"dkR_model_append", (DL_FUNC)&dkR_model_append, 4},
     {NULL, NULL, 0}};
 
 void R_init_DiceOptim(DllInfo* dll) {

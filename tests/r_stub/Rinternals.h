@@ -12,6 +12,7 @@ extern double R_NaReal;
 extern int R_NaInt;
 #define NA_REAL R_NaReal
 #define NA_INTEGER R_NaInt
+#define INTSXP 13
 #define REALSXP 14
 #define VECSXP 19
 double* REAL(SEXP); int* INTEGER(SEXP); int* LOGICAL(SEXP); const char* CHAR(SEXP);
