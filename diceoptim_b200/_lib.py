@@ -104,6 +104,7 @@ SIGNATURES = {
     "dk_multi_count": (_I, [_V]),
     "dk_multi_model": (_V, [_V, _I]),
     "dk_model_clone": (_I, [_V, _I, C.POINTER(_V)]),
+    "dk_multi_append": (_I, [_V, _V, _D, _D]),
     "dk_multi_predict": (_I, [_V, _V, _L, _I, _V, _V]),
     "dk_multi_ei": (_I, [_V, _V, _L, _D, _I, _I, _I, _V, _V, _V]),
     "dk_multi_ei_grad": (_I, [_V, _V, _L, _D, _I, _I, _I, _V, _V]),

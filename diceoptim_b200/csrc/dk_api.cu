@@ -1094,7 +1094,7 @@ int host_predict(dk_model* m, const CritParams& P, const double* x, int64_t ldx,
                        [&](const double* d_x, int64_t rows, double* const* o, int64_t, cudaStream_t st) {
                          return launch_predict(m, P, d_x, rows, o[0], o[1], o[2], st);
                        });
-  if (rc) { cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
+  if (rc) { cudaStreamSynchronize(m->copy_in); cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
   return rc;
 }
 
@@ -1108,7 +1108,7 @@ int host_grad(dk_model* m, const CritParams& P, const double* x, int64_t ldx, in
                    [&](const double* d_x, int64_t rows, double* const* o, int64_t, cudaStream_t st) {
                      return launch_grad(m, P, d_x, rows, o[0], o[1], st);
                    });
-  if (rc) { cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
+  if (rc) { cudaStreamSynchronize(m->copy_in); cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
   return rc;
 }
 
@@ -1184,7 +1184,7 @@ int host_screen(dk_model* m, const ScreenSpec& S, const double* x, int x_on_devi
                      [&](const double* d_x, int64_t rows, double* const*, int64_t u0, cudaStream_t s) {
                        return crit_launch(m, S, d_x, rows, m->d_vec + u0, s);
                      });
-    if (rc) { cudaStreamSynchronize(m->stream); return rc; }
+    if (rc) { cudaStreamSynchronize(m->copy_in); cudaStreamSynchronize(m->stream); return rc; }
   }
   const double sign = S.criterion == DK_CRIT_QUANTILE ? -1.0 : 1.0;
   if ((rc = launch_topk(m->d_vec, n, k, m->d_red, st, sign))) return rc;

@@ -96,7 +96,7 @@ int dk::host_akg(dk_model* m, const double* x, int64_t ldx, int64_t row0, int64_
                        [&](const double* d_x, int64_t rows, double* const* o, int64_t, cudaStream_t st) {
                          return dk_akg_dev(m, d_x, rows, new_noise_var, type, o[0], st);
                        });
-  if (rc) { cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
+  if (rc) { cudaStreamSynchronize(m->copy_in); cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
   return rc;
 }
 
@@ -173,7 +173,7 @@ extern "C" int dk_akg_grad(dk_model* m, const double* x, int64_t N, double new_n
                    [&](const double* d_x, int64_t rows, double* const* o, int64_t, cudaStream_t st) {
                      return dk_akg_grad_dev(m, d_x, rows, new_noise_var, type, o[0], o[1], st);
                    });
-  if (rc) { cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
+  if (rc) { cudaStreamSynchronize(m->copy_in); cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
   return rc;
 }
 

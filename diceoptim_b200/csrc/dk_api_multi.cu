@@ -116,6 +116,13 @@ dk_model* dk_multi_model(dk_multi* mm, int i) {
   return (mm && i >= 0 && i < (int)mm->models.size()) ? mm->models[i] : nullptr;
 }
 
+int dk_multi_append(dk_multi* mm, const double* x_new, double y_new, double new_noise_var) {
+  if (!mm || mm->models.empty()) return fail(DK_ERR_ARG, "multi-GPU handle is NULL");
+  if (!x_new) return fail(DK_ERR_ARG, "x_new is NULL");
+  // every replica grows its own copy (the n^2 host substitution is repeated per device: a few ms each, in parallel)
+  return on_every_device(mm, [&](int g) { return dk_model_append(mm->models[g], x_new, y_new, new_noise_var); });
+}
+
 int dk_multi_predict(dk_multi* mm, const double* x, int64_t N, int type, double* out_mean, double* out_sd) {
   int rc = check_multi(mm, x, N);
   if (rc) return rc;

@@ -102,7 +102,7 @@ int dk::host_qei(dk_model* m, const double* x, int64_t ldx, int64_t b0, int64_t 
                          if (!r && o[1]) r = dk_qei_grad_dev(m, d_x, rows / q, q, plugin, type, minimization, o[1], st);
                          return r;
                        });
-  if (rc) { cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
+  if (rc) { cudaStreamSynchronize(m->copy_in); cudaStreamSynchronize(m->stream); cudaStreamSynchronize(m->copy_out); }
   return rc;
 }
 

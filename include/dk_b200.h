@@ -336,6 +336,8 @@ void dk_multi_destroy(dk_multi* mm);
 int dk_multi_count(const dk_multi* mm);
 /* The single-device handle of replica i (owned by mm), e.g. for the *_dev entry points. */
 dk_model* dk_multi_model(dk_multi* mm, int i);
+/* dk_model_append on every replica. */
+int dk_multi_append(dk_multi* mm, const double* x_new, double y_new, double new_noise_var);
 /* A replica of an existing handle on another device (device-to-device copy of the tiled model). */
 int dk_model_clone(const dk_model* src, int device, dk_model** out);
 /* Host-pointer criteria, same arguments and results as dk_predict / dk_ei / dk_ei_grad / dk_quantile / dk_akg / dk_qei

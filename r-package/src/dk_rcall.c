@@ -355,10 +355,8 @@ SEXP dkR_sample_from_ei(SEXP h, SEXP x, SEXP T, SEXP minimization, SEXP n, SEXP 
 
 /* One more observation in place (the refresh of the constant-liar loop, R/max_qEI.R:305-316), on every replica */
 SEXP dkR_model_append(SEXP h, SEXP x_new, SEXP y_new, SEXP new_noise_var) {
-  dk_multi* mm = multi_of(h);
-  for (int g = 0; g < dk_multi_count(mm); g++)
-    if (dk_model_append(dk_multi_model(mm, g), REAL(x_new), Rf_asReal(y_new), Rf_asReal(new_noise_var)))
-      Rf_error("dk_model_append: %s", dk_last_error());
+  if (dk_multi_append(multi_of(h), REAL(x_new), Rf_asReal(y_new), Rf_asReal(new_noise_var)))
+    Rf_error("dk_model_append: %s", dk_last_error());
   return R_NilValue;
 }
 #endif /* DK_HAVE_R */
