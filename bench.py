@@ -390,6 +390,17 @@ def main():
         extra["e2e_pinned"] = {"value": NT * args.steps / (ms_pin * 1e-3), "unit": UNIT, "ms_per_step": ms_pin / args.steps}
         del x_pin
 
+        # ---- the same screen with the candidates GENERATED on the device (dk_screen + dk_uniform_spec): no upload at all ----
+        gen = _lib.dk_uniform_spec(seed=1000 + rank, lower=None, upper=None)
+        crit = _lib.dk_crit_spec(criterion=0, type=1, minimization=1, proxy=0, plugin=plugin, qnorm_beta=0.0, new_noise_var=0.0)
+        gi = np.empty(1, dtype=np.int64); gv = np.empty(1); gx = np.empty((1, d), order="F")
+        step_gen = lambda: _lib.check(lib.dk_screen(h.ptr, None, 0, C.byref(gen), N, C.byref(crit), 1, vp(gi), vp(gv), vp(gx), None), "dk_screen")
+        step_gen()
+        ms_gen, _ = timed(step_gen, args.steps)
+        extra["e2e_generated"] = {"value": NT * args.steps / (ms_gen * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0,
+                                  "d2h_bytes_per_step": 16, "note": "uniform candidates drawn on the device by the counter-based generator "
+                                  "(what lower + runif(d N) (upper - lower) of R/max_crit.R:104 draws on the host); every rank its own seed"}
+
         # ---- EI + EI.grad on cfg4, every rank on its share of 2^21 candidates ----
         NG = 1 << 21
         glo, ghi = parallel.shard_range(NG, rank, world)
@@ -597,6 +608,27 @@ def main():
             extra["qei"]["cpu_baseline"] = {"value": qs / dtq, "unit": "evals/s", "cores": os.cpu_count(), "kind": "port",
                                             "sample": f"{qs} batches, oracle qEI(fastCompute=FALSE) (R/qEI.R:119-194), one process per core, {dtq:.1f} s",
                                             "max_rel_err_gpu_vs_oracle": float(np.max(np.abs(qgpu - np.array(qref)) / np.maximum(np.abs(qref), 1e-12)))}
+        if not args.no_extras:
+            # latencies of the optimiser-sized shapes (rank 0, host calls, copies included; best of 5)
+            def best_ms(fn, reps=5):
+                b = 1e9
+                for _ in range(reps):
+                    t0 = time.perf_counter(); fn(); b = min(b, time.perf_counter() - t0)
+                return 1e3 * b
+            x16 = np.asfortranarray(xs[:16]); e16 = np.empty(16); g16 = np.empty((16, d), order="F")
+            from diceoptim_b200.optim import device_polish
+            x10 = xs[100:110].copy()
+            lat = {"ei_16_candidates_ms": best_ms(lambda: _lib.check(lib.dk_ei(h.ptr, vp(x16), 16, plugin, 1, 1, 0, vp(e16), None, None), "ei")),
+                   "ei_grad_16_candidates_ms": best_ms(lambda: _lib.check(lib.dk_ei_grad(h.ptr, vp(x16), 16, plugin, 1, 1, 0, vp(g16), vp(e16)), "grad")),
+                   "polish_10_starts_maxit100_ms": best_ms(lambda: device_polish(km, "EI", x10, np.zeros(d), np.ones(d), plugin=plugin, maxit=100, device=local), 2)}
+            hc = h.clone()
+            xn = np.ascontiguousarray(np.random.default_rng(5).random((4, d)))
+            t0 = time.perf_counter()
+            for i in range(4):
+                _lib.check(lib.dk_model_append(hc.ptr, vp(xn[i]), plugin, 0.0), "append")
+            lat["model_append_ms_per_point"] = 1e3 * (time.perf_counter() - t0) / 4
+            hc.close()
+            extra["latency"] = lat
         if extra:
             line["extra"] = extra
         print(json.dumps(line), flush=True)

@@ -138,3 +138,26 @@ def test_chunked_pipeline_many_chunks(gpu_lib):
     _lib.check(gpu_lib.dk_screen_ei(h.ptr, _vp(x), 0, N, pl, 1, 1, 0, 1, _vp(idx), _vp(val), None), "dk_screen_ei")
     assert idx[0] == int(np.argmax(a)) and val[0] == a[idx[0]]
     km.release()
+
+
+def test_multi_append_grows_every_replica(gpu_lib):
+    """dk_multi_append: every replica grows in place; the multi-device EI of the grown model equals a fresh handle's"""
+    from diceoptim_b200 import EI, _lib
+    from diceoptim_b200.km import MultiDeviceModel
+    from diceoptim_b200.update import update_km
+    km = small_model("matern5_2", "const", n=120, d=3, seed=26, noise_var=0.01)
+    mdm = MultiDeviceModel(km, [0, 0])
+    pts = np.random.default_rng(8).random((10, 3))                       # 120 -> 130: crosses the 128-row block boundary
+    grown = km
+    for i, p in enumerate(pts):
+        pc = np.ascontiguousarray(p)
+        _lib.check(gpu_lib.dk_multi_append(mdm.ptr, _vp(pc), float(i) / 10, 0.0), "dk_multi_append")
+        grown = update_km(grown, p, float(i) / 10, reuse_handles=False)
+    assert gpu_lib.dk_model_n(gpu_lib.dk_multi_model(mdm.ptr, 1)) == 130
+    x = np.asfortranarray(np.random.default_rng(9).random((500, 3)))
+    a = np.empty(500)
+    pl = float(np.median(km.y))
+    _lib.check(gpu_lib.dk_multi_ei(mdm.ptr, _vp(x), 500, pl, 1, 1, 0, _vp(a), None, None), "dk_multi_ei")
+    b = EI(x, grown, plugin=pl)
+    assert np.all(np.abs(a - b) <= 1e-9 * np.abs(b) + 1e-12 * b.max())
+    mdm.close(); grown.release(); km.release()
