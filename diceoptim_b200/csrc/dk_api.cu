@@ -6,6 +6,7 @@
 #include "dk_predict_kernels.cuh"
 #include "dk_grad.cuh"
 #include "dk_narrow.cuh"
+#include "dk_small.cuh"
 #include "dk_reduce.cuh"
 
 namespace dk {
@@ -88,7 +89,55 @@ void build_tiles(const Factor& L, int nblk, std::vector<double>& tiles, int I0 =
   }
 }
 
+// Small designs (n_pad <= 256): the explicit inverse of the WHOLE padded factor, formed in long double and rounded once,
+// as A tiles [row block rb][k-chunk kc <= 8 rb + 7] for k_predict_small (dk_small.cuh).
+template <class Factor>
+void build_small_tiles(const Factor& L, int n_pad, std::vector<double>& tiles) {
+  const int N = n_pad, nrb = N / BM;
+  std::vector<long double> inv((size_t)N * N, 0.0L);
+  for (int j = 0; j < N; j++) {
+    inv[(size_t)j * N + j] = 1.0L / (long double)L(j, j);
+    for (int i = j + 1; i < N; i++) {
+      long double s = 0.0L;
+      for (int k = j; k < i; k++) s += (long double)L(i, k) * inv[(size_t)k * N + j];
+      inv[(size_t)i * N + j] = -s / (long double)L(i, i);
+    }
+  }
+  tiles.assign(small_tile_base(nrb) * A_TILE, 0.0);
+  for (int rb = 0; rb < nrb; rb++)
+    for (int kc = 0; kc < CHUNKS_PER_BLOCK * (rb + 1); kc++) {
+      double* t = tiles.data() + (small_tile_base(rb) + kc) * A_TILE;
+      for (int r = 0; r < BM; r++)
+        for (int k = 0; k < KC; k++) t[a_tile_index(r, k)] = (double)inv[(size_t)(rb * BM + r) * N + kc * KC + k];
+    }
+}
+
 }  // namespace
+
+// (re)build the small-design tiles of a handle from its host copies; no-op for n_pad > 256
+int refresh_small_tiles(dk_model* m) {
+  if (m->dm.n_pad > SMALL_MAX_PAD) {
+    dev_release(m, &m->d_tiles_small, m->tiles_small_doubles);
+    m->tiles_small_doubles = 0;
+    m->dm.tiles_small = nullptr;
+    return DK_OK;
+  }
+  std::vector<double> tiles;
+  const size_t ld = (size_t)m->ld;
+  AugFactor L{m->h_T, m->h_zM, m->h_zM + ld, m->n, m->p, m->dm.n_aug, ld, ld};
+  build_small_tiles(L, m->dm.n_pad, tiles);
+  if (m->tiles_small_doubles < tiles.size()) {
+    dev_release(m, &m->d_tiles_small, m->tiles_small_doubles);
+    m->tiles_small_doubles = 0;
+    m->dm.tiles_small = nullptr;
+    int rc = dev_alloc(m, &m->d_tiles_small, tiles.size());
+    if (rc) return rc;
+    m->tiles_small_doubles = tiles.size();
+  }
+  DK_CUDA_TRY(cudaMemcpy(m->d_tiles_small, tiles.data(), tiles.size() * 8, cudaMemcpyHostToDevice));
+  m->dm.tiles_small = m->d_tiles_small;
+  return DK_OK;
+}
 
 int ensure_io(dk_model* m, size_t doubles) {
   if (m->io_doubles >= doubles) return DK_OK;
@@ -168,6 +217,7 @@ int set_kernel_attrs(int device) {
   DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_fused_tma<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
   DK_ATTR_TMA(DK_GAUSS) DK_ATTR_TMA(DK_EXP) DK_ATTR_TMA(DK_MATERN3_2) DK_ATTR_TMA(DK_MATERN5_2) DK_ATTR_TMA(DK_POWEXP)
 #undef DK_ATTR_TMA
+  DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_small, cudaFuncAttributeMaxDynamicSharedMemorySize, SS_TOTAL));
   DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_narrow, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
   DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_narrow, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
   DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_fused<-1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
@@ -195,6 +245,13 @@ static bool use_narrow(const dk_model* m, int64_t N) {
   return ((N + BN - 1) / BN) * 4 <= m->grid;
 }
 
+// Small designs (n_pad <= 256) take the single-block kernel of dk_small.cuh for every batch the narrow tiles do not serve.
+// DK_SMALL=0 keeps them on the blocked kernel (A/B runs); DK_TILE_WIDE / DK_TILE_NARROW also bypass it.
+static bool use_small(const dk_model* m) {
+  static const bool off = [] { const char* e = std::getenv("DK_SMALL"); return e && std::atoi(e) == 0; }();
+  return !off && m->dm.tiles_small != nullptr && m->tile_mode == DK_TILE_AUTO;
+}
+
 // forward pass over device-resident candidates
 int launch_predict(dk_model* m, const CritParams& P, const double* d_x, int64_t N, double* d_main, double* d_mean,
                    double* d_sd, cudaStream_t st) {
@@ -204,6 +261,15 @@ int launch_predict(dk_model* m, const CritParams& P, const double* d_x, int64_t 
     if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
     k_predict_narrow<<<(int)std::min<int64_t>(nt, m->grid), NT, SM_TOTAL + PIPE_SMEM, st>>>(
         m->dm, P, d_x, N, nt, m->d_vscratch, m->scratch_doubles_per_cta, d_main, d_mean, d_sd);
+    if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; m->ev_mid_valid = false; }
+    m->launches++;
+    DK_CUDA_TRY(cudaGetLastError());
+    return DK_OK;
+  }
+  if (use_small(m)) {
+    const int64_t nt = (N + SBN - 1) / SBN;
+    if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
+    k_predict_small<<<(int)std::min<int64_t>(nt, m->grid), NT, SS_TOTAL, st>>>(m->dm, P, d_x, N, nt, d_main, d_mean, d_sd);
     if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; m->ev_mid_valid = false; }
     m->launches++;
     DK_CUDA_TRY(cudaGetLastError());
@@ -580,6 +646,8 @@ int dk_model_create(const dk_model_desc* D, dk_model** out) {
     return bail(fail(DK_ERR_NOMEM, "host allocation failed while tiling the factor"));
   }
 
+  if ((rc = refresh_small_tiles(m))) return bail(rc);
+
   // ---- per-CTA V panels: two resident CTAs per SM ----
   m->grid = 2 * m->num_sms;
   if (const char* e = std::getenv("DK_CTAS_PER_SM")) {  // experiment knob: 1 = one resident CTA per SM
@@ -660,6 +728,12 @@ int dk_model_clone(const dk_model* src, int device, dk_model** out) {
   std::memcpy(m->h_G, src->h_G, sizeof m->h_G);
   std::memcpy(m->h_beta, src->h_beta, sizeof m->h_beta);
   (void)n;
+  if (src->d_tiles_small) {
+    if ((rc = dev_alloc(m, &m->d_tiles_small, src->tiles_small_doubles))) return bail(rc);
+    m->tiles_small_doubles = src->tiles_small_doubles;
+    if ((rc = peer(m->d_tiles_small, src->d_tiles_small, src->tiles_small_doubles))) return bail(rc);
+    dm.tiles_small = m->d_tiles_small;
+  } else dm.tiles_small = nullptr;
   m->grid = src->grid * m->num_sms / std::max(1, src->num_sms);
   m->scratch_doubles_per_cta = src->scratch_doubles_per_cta;
   if ((rc = dev_alloc(m, &m->d_vscratch, (size_t)m->grid * m->scratch_doubles_per_cta))) return bail(rc);
@@ -943,7 +1017,7 @@ extern "C" int dk_model_append(dk_model* m, const double* x_new, double y_new, d
     DK_CUDA_TRY(cudaMemcpy(m->d_Xrm + (size_t)a * cap_pad * d + (size_t)n * d, row.data() + (size_t)a * d, (size_t)d * 8,
                            cudaMemcpyHostToDevice));
   if ((rc = upload_small(m))) return rc;
-  return DK_OK;
+  return refresh_small_tiles(m);   // small designs: the whole-factor inverse (dropped once n_pad exceeds 256)
 }
 
 extern "C" {
@@ -954,7 +1028,7 @@ void dk_model_destroy(dk_model* m) {
   if (!m) return;
   DeviceGuard guard(m->device);
   cudaDeviceSynchronize();
-  cudaFree(m->d_tiles_fwd); cudaFree(m->d_tiles_bwd); cudaFree(m->d_Xrm); cudaFree(m->d_small);
+  cudaFree(m->d_tiles_fwd); cudaFree(m->d_tiles_bwd); cudaFree(m->d_tiles_small); cudaFree(m->d_Xrm); cudaFree(m->d_small);
   cudaFree(m->d_vscratch); cudaFree(m->d_wscratch); cudaFree(m->d_cscratch); cudaFree(m->d_io); cudaFree(m->d_red);
   cudaFree(m->d_aux); cudaFree(m->d_mom); cudaFree(m->d_deriv);
   if (m->stream) cudaStreamDestroy(m->stream);
@@ -1396,7 +1470,11 @@ extern "C" int dk_ei_dev_noalloc(dk_model* m, const double* d_x, int64_t N, doub
   if (N == 0) return DK_OK;
   const int64_t fit = (int64_t)(DK_NOALLOC_SCRATCH_DOUBLES / panel);  // CTAs whose panels fit the array
   CritParams P{MODE_EI, type, minimization, proxy, plugin, 0.0};
-  if (use_narrow(m, N)) {
+  if (!use_narrow(m, N) && use_small(m)) {
+    // small designs: the single-block kernel needs no scratch at all
+    const int64_t nt = (N + SBN - 1) / SBN;
+    k_predict_small<<<(int)std::min<int64_t>(nt, m->grid), NT, SS_TOTAL, (cudaStream_t)stream>>>(m->dm, P, d_x, N, nt, d_ei, d_mean, d_sd);
+  } else if (use_narrow(m, N)) {
     // the same tile shape dk_ei_dev picks for this batch size, so the two entry points return the same numbers
     const int64_t nt = (N + BNN - 1) / BNN;
     const int grid = (int)std::min<int64_t>(std::min<int64_t>(nt, m->grid), fit);

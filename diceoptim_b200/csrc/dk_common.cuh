@@ -61,6 +61,7 @@ struct DevModel {
   double sd2, nugget, total_sd2;
   const double* tiles_fwd;  // forward tiles: -L_aug off-diagonal, block inverses on the diagonal
   const double* tiles_bwd;  // backward (flipped T) tiles, same format; NULL until a gradient call
+  const double* tiles_small; // n_pad <= 256 only: the explicit inverse of the whole padded factor as A tiles (dk_small.cuh)
   const double* Xrm;        // [n_pad][d] row-major design (pad rows zero)
   const double* Xrm_s;      // the same rows scaled by w_k (cov-gen operand)
   const double* Xrm_r8;     // the same rows rounded to 8 digits, rint(v 1e8) / 1e8 (qEI's duplicate rule)
@@ -117,6 +118,8 @@ struct dk_model {
   // device allocations owned by the handle
   double* d_tiles_fwd = nullptr;
   double* d_tiles_bwd = nullptr;
+  double* d_tiles_small = nullptr;   // small designs: inverse of the whole factor (dk_small.cuh)
+  size_t tiles_small_doubles = 0;
   double* d_Xrm = nullptr;
   double* d_small = nullptr;     // beta | RM | tuuinv | alpha | KinvF | noise_var
   size_t tiles_fwd_doubles = 0, xrm_doubles = 0, small_doubles = 0, bwd_tile_doubles = 0;  // sizes of the three uploads (dk_model_clone)

@@ -1,0 +1,82 @@
+"""The single-block kernel for small designs (n + p + 1 <= 256, csrc/dk_small.cuh) against the oracle and against the
+blocked kernel: it serves every batch of such a model that is too large for the narrow tiles (N > 4736), i.e. the grid /
+random-search screens of BASELINE cfg1 and cfg2."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import assert_close_adjudicated, small_model, to_oracle
+
+pytestmark = pytest.mark.gpu
+N_BIG = 6000        # 94 wide tiles: neither narrow nor (for small designs) blocked
+
+
+def _vp(a):
+    return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+def _ei(gpu_lib, km, x, mode, plugin, type=1, minimization=1):
+    from diceoptim_b200 import _lib
+    h = km.handle(0)
+    N = x.shape[0]
+    x = np.asfortranarray(x)
+    ei = np.empty(N); mean = np.empty(N); sd = np.empty(N)
+    _lib.check(gpu_lib.dk_model_set_tile_mode(h.ptr, mode), "tile mode")
+    _lib.check(gpu_lib.dk_ei(h.ptr, _vp(x), N, plugin, type, minimization, 0, _vp(ei), _vp(mean), _vp(sd)), "dk_ei")
+    gpu_lib.dk_model_set_tile_mode(h.ptr, 0)
+    return ei, mean, sd
+
+
+@pytest.mark.parametrize("n", [1, 20, 100, 126, 127, 200, 253])
+@pytest.mark.parametrize("name,trend,kw", [("matern5_2", "const", {}), ("gauss", "linear", {}), ("exp", "const", {"nugget": 0.02}),
+                                           ("powexp", "linear", {"noise_var": 0.01})])
+def test_small_kernel_matches_oracle_and_blocked_kernel(gpu_lib, n, name, trend, kw):
+    d = 3
+    if trend == "linear" and n < d + 2:
+        pytest.skip("fewer design points than trend columns")
+    if n + (d + 1 if trend == "linear" else 1) + 1 > 256:
+        pytest.skip("not a small design")
+    from oracle import dicekriging as dk, diceoptim as do, hiprec as hp
+    km = small_model(name, trend, n=n, d=d, seed=90 + n, **kw)
+    ko = to_oracle(km)
+    x = np.random.default_rng(n).random((N_BIG, d))
+    x[5] = km.X[0]                                                   # a design point
+    pl = float(np.median(km.y))
+    for type_id, type in ((1, "UK"), (0, "SK")):
+        ei, mean, sd = _ei(gpu_lib, km, x, 0, pl, type=type_id)      # AUTO -> the small kernel
+        eb, mb, sb = _ei(gpu_lib, km, x, 1, pl, type=type_id)        # WIDE -> the blocked kernel
+        ref = dk.predict_km(ko, x, type=type, light_return=True)
+        scale = np.max(np.abs(km.y)) + np.sqrt(km.covariance.sd2)
+        tot = km.covariance.sd2 + (km.covariance.nugget if km.covariance.nugget_flag else 0.0)
+        assert np.max(np.abs(mean - ref["mean"])) <= 1e-10 * scale
+        assert np.max(np.abs(sd ** 2 - ref["sd"] ** 2)) <= 1e-10 * tot
+        assert np.max(np.abs(mean - mb)) <= 1e-11 * scale and np.max(np.abs(sd ** 2 - sb ** 2)) <= 1e-11 * tot
+        with np.errstate(all="ignore"):
+            eref = do.EI(x, ko, plugin=pl, type=type)
+        assert np.array_equal(np.isnan(ei), np.isnan(eref))
+        ok = np.flatnonzero(~np.isnan(eref))
+        floor = 1e-12 * np.max(np.abs(eref[ok]))
+        assert_close_adjudicated(ei[ok], eref[ok], lambda bad: hp.EI(x[ok[bad]], ko, plugin=pl, type=type), floor=floor,
+                                 what="EI (small kernel)")
+    km.release()
+
+
+def test_small_kernel_cfg2_shape_and_other_criteria(gpu_lib):
+    """cfg2's own shape (hartman4, gauss, n = 200, d = 4) on 20 000 candidates: EI and which.max against the oracle, the
+    quantile epilogue, the host pipeline, and bit-exact repeats."""
+    from diceoptim_b200 import synth, EI, kriging_quantile, screen_EI
+    from oracle import diceoptim as do
+    km = synth.config_model("cfg2_hartman4_n200")
+    ko = to_oracle(km)
+    x = synth.config_candidates("cfg2_hartman4_n200", N=20_000, rank=3)
+    ei = EI(x, km)
+    ref = do.EI(x, ko)
+    assert np.all(np.abs(ei - ref) <= 1e-10 * np.abs(ref) + 1e-12 * ref.max())
+    idx, val = screen_EI(x, km)
+    assert idx[0] == do.which_max(ref) and val[0] == ei[idx[0]]
+    q = kriging_quantile(x, km, beta=0.1)
+    qref = do.kriging_quantile(x, ko, beta=0.1)
+    assert np.max(np.abs(q - qref)) <= 1e-10 * (np.max(np.abs(km.y)) + np.sqrt(km.covariance.sd2))
+    assert np.array_equal(ei, EI(x, km))
+    km.release()
