@@ -55,6 +55,7 @@ SIGNATURES = {
     "dk_model_destroy": (None, [_V]),
     "dk_model_append": (_I, [_V, _V, _D, _D]),
     "dk_model_n": (_I, [_V]),
+    "dk_model_small_kernel": (_I, [_V]),
     "dk_model_device_bytes": (C.c_size_t, [_V]),
     "dk_model_launches": (C.c_longlong, [_V]),
     "dk_model_set_timing": (_I, [_V, _I]),

@@ -92,9 +92,8 @@ void build_tiles(const Factor& L, int nblk, std::vector<double>& tiles, int I0 =
 // Small designs (n_pad <= 256): the explicit inverse of the WHOLE padded factor, formed in long double and rounded once,
 // as A tiles [row block rb][k-chunk kc <= 8 rb + 7] for k_predict_small (dk_small.cuh).
 template <class Factor>
-void build_small_tiles(const Factor& L, int n_pad, std::vector<double>& tiles) {
-  const int N = n_pad, nrb = N / BM;
-  std::vector<long double> inv((size_t)N * N, 0.0L);
+void invert_factor(const Factor& L, int N, std::vector<long double>& inv) {
+  inv.assign((size_t)N * N, 0.0L);
   for (int j = 0; j < N; j++) {
     inv[(size_t)j * N + j] = 1.0L / (long double)L(j, j);
     for (int i = j + 1; i < N; i++) {
@@ -103,33 +102,87 @@ void build_small_tiles(const Factor& L, int n_pad, std::vector<double>& tiles) {
       inv[(size_t)i * N + j] = -s / (long double)L(i, i);
     }
   }
-  tiles.assign(small_tile_base(nrb) * A_TILE, 0.0);
-  for (int rb = 0; rb < nrb; rb++)
-    for (int kc = 0; kc < CHUNKS_PER_BLOCK * (rb + 1); kc++) {
-      double* t = tiles.data() + (small_tile_base(rb) + kc) * A_TILE;
-      for (int r = 0; r < BM; r++)
-        for (int k = 0; k < KC; k++) t[a_tile_index(r, k)] = (double)inv[(size_t)(rb * BM + r) * N + kc * KC + k];
+}
+
+void host_cov_vector(const dk_model* m, const double* x, double* c);
+
+// Applying the rounded whole-factor inverse is less accurate than substitution when the factor is ill-conditioned (the
+// off-diagonal block of the inverse cancels against the diagonal one).  Probe: eight points of the design's bounding box,
+// the mean term z'v and sum v^2 from the rounded inverse (double, ascending k, as the kernel accumulates) against
+// long-double substitution; the kernel is enabled only if both stay 2e-11 of their scales (a tenth of the tolerance).
+template <class Factor>
+bool small_inverse_is_accurate(const dk_model* m, const Factor& L, const std::vector<long double>& inv, int N) {
+  const int n = m->n, d = m->d;
+  std::vector<double> lo(d, 1e300), hi(d, -1e300), x(d), c(n), vs(N);
+  std::vector<long double> vr(N);
+  for (int i = 0; i < n; i++)
+    for (int k = 0; k < d; k++) {
+      lo[k] = std::min(lo[k], m->h_X[(size_t)i * d + k]);
+      hi[k] = std::max(hi[k], m->h_X[(size_t)i * d + k]);
     }
+  double ymax = 0.0;
+  if (m->h_y)
+    for (int i = 0; i < n; i++) ymax = std::max(ymax, std::fabs(m->h_y[i]));
+  const double scale = ymax + std::sqrt(m->dm.sd2);
+  unsigned long long rng = 0x9E3779B97F4A7C15ULL;
+  for (int t = 0; t < 8; t++) {
+    for (int k = 0; k < d; k++) {
+      rng = rng * 6364136223846793005ULL + 1442695040888963407ULL;
+      x[k] = lo[k] + (hi[k] - lo[k]) * ((double)(rng >> 11) * 1.1102230246251565e-16);
+    }
+    host_cov_vector(m, x.data(), c.data());
+    long double s2r = 0.0L;
+    for (int i = 0; i < N; i++) {          // long-double substitution, right-hand side [c; 0]
+      long double s = i < n ? (long double)c[i] : 0.0L;
+      for (int k = 0; k < i; k++) s -= (long double)L(i, k) * vr[k];
+      vr[i] = s / (long double)L(i, i);
+      if (i < n) s2r += vr[i] * vr[i];
+    }
+    double s2s = 0.0;
+    for (int i = 0; i <= n; i++) {         // rows 0..n: the design rows and the z'v row
+      double a = 0.0;
+      for (int k = 0; k <= std::min(i, n - 1); k++) a = std::fma((double)inv[(size_t)i * N + k], c[k], a);
+      vs[i] = a;
+      if (i < n) s2s = std::fma(a, a, s2s);
+    }
+    if (std::fabs((double)((long double)vs[n] - vr[n])) > 2e-11 * scale) return false;
+    if (std::fabs((double)((long double)s2s - s2r)) > 2e-11 * m->dm.total_sd2) return false;
+  }
+  return true;
 }
 
 }  // namespace
 
-// (re)build the small-design tiles of a handle from its host copies; no-op for n_pad > 256
+// (re)build the small-design tiles of a handle from its host copies; no-op for n_pad > 256 and for factors on which the
+// whole-factor inverse would lose accuracy (the blocked kernels then serve the model as before)
 int refresh_small_tiles(dk_model* m) {
-  if (m->dm.n_pad > SMALL_MAX_PAD) {
+  auto drop = [&] {
     dev_release(m, &m->d_tiles_small, m->tiles_small_doubles);
     m->tiles_small_doubles = 0;
     m->dm.tiles_small = nullptr;
     return DK_OK;
-  }
-  std::vector<double> tiles;
+  };
+  if (m->dm.n_pad > SMALL_MAX_PAD) return drop();
+  const int N = m->dm.n_pad, nrb = N / BM;
   const size_t ld = (size_t)m->ld;
   AugFactor L{m->h_T, m->h_zM, m->h_zM + ld, m->n, m->p, m->dm.n_aug, ld, ld};
-  build_small_tiles(L, m->dm.n_pad, tiles);
+  std::vector<long double> inv;
+  std::vector<double> tiles;
+  try {
+    invert_factor(L, N, inv);
+    if (!small_inverse_is_accurate(m, L, inv, N)) return drop();
+    tiles.assign(small_tile_base(nrb) * A_TILE, 0.0);
+    for (int rb = 0; rb < nrb; rb++)
+      for (int kc = 0; kc < CHUNKS_PER_BLOCK * (rb + 1); kc++) {
+        double* t = tiles.data() + (small_tile_base(rb) + kc) * A_TILE;
+        for (int r = 0; r < BM; r++)
+          for (int k = 0; k < KC; k++) t[a_tile_index(r, k)] = (double)inv[(size_t)(rb * BM + r) * N + kc * KC + k];
+      }
+  } catch (const std::bad_alloc&) {
+    return fail(DK_ERR_NOMEM, "host allocation failed while inverting the factor");
+  }
   if (m->tiles_small_doubles < tiles.size()) {
-    dev_release(m, &m->d_tiles_small, m->tiles_small_doubles);
-    m->tiles_small_doubles = 0;
-    m->dm.tiles_small = nullptr;
+    drop();
     int rc = dev_alloc(m, &m->d_tiles_small, tiles.size());
     if (rc) return rc;
     m->tiles_small_doubles = tiles.size();
@@ -269,7 +322,7 @@ int launch_predict(dk_model* m, const CritParams& P, const double* d_x, int64_t 
   if (use_small(m)) {
     const int64_t nt = (N + SBN - 1) / SBN;
     if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
-    k_predict_small<<<(int)std::min<int64_t>(nt, m->grid), NT, SS_TOTAL, st>>>(m->dm, P, d_x, N, nt, d_main, d_mean, d_sd);
+    k_predict_small<<<(int)std::min<int64_t>(nt, m->num_sms), NTS, SS_TOTAL, st>>>(m->dm, P, d_x, N, nt, d_main, d_mean, d_sd);
     if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; m->ev_mid_valid = false; }
     m->launches++;
     DK_CUDA_TRY(cudaGetLastError());
@@ -750,8 +803,7 @@ int dk_model_clone(const dk_model* src, int device, dk_model** out) {
 // ------------------------------------------------------------------------------------------
 // dk_model_append: one more observation, hyper-parameters and trend coefficients unchanged
 // ------------------------------------------------------------------------------------------
-namespace {
-
+namespace dk { namespace {
 // 1-D kernels as DiceKriging codes them: k(x, X_i) for the n design rows held on the host
 void host_cov_vector(const dk_model* m, const double* x, double* c) {
   const DevModel& dm = m->dm;
@@ -914,6 +966,7 @@ int upload_small(dk_model* m) {
 }
 
 }  // namespace
+}  // namespace dk
 
 // The last column of the new Cholesky factor needs one forward substitution against the old one:
 //   v = T'^-1 c(x),  t = sqrt(k(x, x) - v'v),  T+ = [[T, v], [0, t]],  z+ = [z, (y - f'beta - v'z) / t],
@@ -1023,6 +1076,7 @@ extern "C" int dk_model_append(dk_model* m, const double* x_new, double y_new, d
 extern "C" {
 
 int dk_model_n(const dk_model* m) { return m ? m->n : 0; }
+int dk_model_small_kernel(const dk_model* m) { return (m && m->dm.tiles_small) ? 1 : 0; }
 
 void dk_model_destroy(dk_model* m) {
   if (!m) return;
@@ -1473,7 +1527,7 @@ extern "C" int dk_ei_dev_noalloc(dk_model* m, const double* d_x, int64_t N, doub
   if (!use_narrow(m, N) && use_small(m)) {
     // small designs: the single-block kernel needs no scratch at all
     const int64_t nt = (N + SBN - 1) / SBN;
-    k_predict_small<<<(int)std::min<int64_t>(nt, m->grid), NT, SS_TOTAL, (cudaStream_t)stream>>>(m->dm, P, d_x, N, nt, d_ei, d_mean, d_sd);
+    k_predict_small<<<(int)std::min<int64_t>(nt, m->num_sms), NTS, SS_TOTAL, (cudaStream_t)stream>>>(m->dm, P, d_x, N, nt, d_ei, d_mean, d_sd);
   } else if (use_narrow(m, N)) {
     // the same tile shape dk_ei_dev picks for this batch size, so the two entry points return the same numbers
     const int64_t nt = (N + BNN - 1) / BNN;

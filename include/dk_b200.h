@@ -92,6 +92,11 @@ void dk_model_destroy(dk_model* m);
  * Not to be called while another call on the handle is in flight.  dk_model_n: the handle's current design size. */
 int dk_model_append(dk_model* m, const double* x_new, double y_new, double new_noise_var);
 int dk_model_n(const dk_model* m);
+/* 1 when the handle is a small design (n + p + 1 <= 256) whose large forward batches run the single-block kernel (the
+ * explicit inverse of the whole factor applied as one triangular GEMM, no scratch).  dk_model_create enables it only when
+ * a probe against long-double substitution shows that inverse loses no accuracy (ill-conditioned gauss designs do not
+ * qualify and stay on the blocked kernels). */
+int dk_model_small_kernel(const dk_model* m);
 /* Device-memory bytes held by the handle (tiles + scratch). */
 size_t dk_model_device_bytes(const dk_model* m);
 /* Number of kernels launched through the handle so far (bench.py's gpu_launches). */

@@ -40,6 +40,9 @@ def test_small_kernel_matches_oracle_and_blocked_kernel(gpu_lib, n, name, trend,
     from oracle import dicekriging as dk, diceoptim as do, hiprec as hp
     km = small_model(name, trend, n=n, d=d, seed=90 + n, **kw)
     ko = to_oracle(km)
+    uses_small = bool(gpu_lib.dk_model_small_kernel(km.handle(0).ptr))
+    if name != "gauss":
+        assert uses_small          # the ill-conditioned gauss designs may be refused by the accuracy probe, nothing else
     x = np.random.default_rng(n).random((N_BIG, d))
     x[5] = km.X[0]                                                   # a design point
     pl = float(np.median(km.y))
@@ -69,6 +72,7 @@ def test_small_kernel_cfg2_shape_and_other_criteria(gpu_lib):
     from oracle import diceoptim as do
     km = synth.config_model("cfg2_hartman4_n200")
     ko = to_oracle(km)
+    assert gpu_lib.dk_model_small_kernel(km.handle(0).ptr) == 1      # cfg2 itself qualifies
     x = synth.config_candidates("cfg2_hartman4_n200", N=20_000, rank=3)
     ei = EI(x, km)
     ref = do.EI(x, ko)
