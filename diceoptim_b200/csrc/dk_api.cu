@@ -107,9 +107,10 @@ void invert_factor(const Factor& L, int N, std::vector<long double>& inv) {
 void host_cov_vector(const dk_model* m, const double* x, double* c);
 
 // Applying the rounded whole-factor inverse is less accurate than substitution when the factor is ill-conditioned (the
-// off-diagonal block of the inverse cancels against the diagonal one).  Probe: eight points of the design's bounding box,
+// off-diagonal block of the inverse cancels against the diagonal one).  Probe: 64 points of the design's bounding box,
 // the mean term z'v and sum v^2 from the rounded inverse (double, ascending k, as the kernel accumulates) against
-// long-double substitution; the kernel is enabled only if both stay 2e-11 of their scales (a tenth of the tolerance).
+// long-double substitution; the kernel is enabled only if both stay within 1e-11 of their scales (a tenth of the
+// tolerance: the largest error over a screen of thousands of candidates is a few times the largest over 64 probes).
 template <class Factor>
 bool small_inverse_is_accurate(const dk_model* m, const Factor& L, const std::vector<long double>& inv, int N) {
   const int n = m->n, d = m->d;
@@ -125,7 +126,7 @@ bool small_inverse_is_accurate(const dk_model* m, const Factor& L, const std::ve
     for (int i = 0; i < n; i++) ymax = std::max(ymax, std::fabs(m->h_y[i]));
   const double scale = ymax + std::sqrt(m->dm.sd2);
   unsigned long long rng = 0x9E3779B97F4A7C15ULL;
-  for (int t = 0; t < 8; t++) {
+  for (int t = 0; t < 64; t++) {
     for (int k = 0; k < d; k++) {
       rng = rng * 6364136223846793005ULL + 1442695040888963407ULL;
       x[k] = lo[k] + (hi[k] - lo[k]) * ((double)(rng >> 11) * 1.1102230246251565e-16);
@@ -145,8 +146,8 @@ bool small_inverse_is_accurate(const dk_model* m, const Factor& L, const std::ve
       vs[i] = a;
       if (i < n) s2s = std::fma(a, a, s2s);
     }
-    if (std::fabs((double)((long double)vs[n] - vr[n])) > 2e-11 * scale) return false;
-    if (std::fabs((double)((long double)s2s - s2r)) > 2e-11 * m->dm.total_sd2) return false;
+    if (std::fabs((double)((long double)vs[n] - vr[n])) > 1e-11 * scale) return false;
+    if (std::fabs((double)((long double)s2s - s2r)) > 1e-11 * m->dm.total_sd2) return false;
   }
   return true;
 }
@@ -162,7 +163,8 @@ int refresh_small_tiles(dk_model* m) {
     m->dm.tiles_small = nullptr;
     return DK_OK;
   };
-  if (m->dm.n_pad > SMALL_MAX_PAD) return drop();
+  const SmallLayout lay = small_layout(m->n, m->dm.n_pad, m->d, m->p);
+  if (lay.stages == 0) return drop();   // more than 256 padded rows, or rows x d too large to keep the design in shared memory
   const int N = m->dm.n_pad, nrb = N / BM;
   const size_t ld = (size_t)m->ld;
   AugFactor L{m->h_T, m->h_zM, m->h_zM + ld, m->n, m->p, m->dm.n_aug, ld, ld};
@@ -189,6 +191,7 @@ int refresh_small_tiles(dk_model* m) {
   }
   DK_CUDA_TRY(cudaMemcpy(m->d_tiles_small, tiles.data(), tiles.size() * 8, cudaMemcpyHostToDevice));
   m->dm.tiles_small = m->d_tiles_small;
+  m->small_lay = lay;
   return DK_OK;
 }
 
@@ -270,7 +273,7 @@ int set_kernel_attrs(int device) {
   DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_fused_tma<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
   DK_ATTR_TMA(DK_GAUSS) DK_ATTR_TMA(DK_EXP) DK_ATTR_TMA(DK_MATERN3_2) DK_ATTR_TMA(DK_MATERN5_2) DK_ATTR_TMA(DK_POWEXP)
 #undef DK_ATTR_TMA
-  DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_small, cudaFuncAttributeMaxDynamicSharedMemorySize, SS_TOTAL));
+  DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_small, cudaFuncAttributeMaxDynamicSharedMemorySize, SMALL_SMEM_MAX));
   DK_CUDA_TRY(cudaFuncSetAttribute(k_predict_narrow, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
   DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_narrow, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
   DK_CUDA_TRY(cudaFuncSetAttribute(k_grad_fused<-1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
@@ -322,7 +325,7 @@ int launch_predict(dk_model* m, const CritParams& P, const double* d_x, int64_t 
   if (use_small(m)) {
     const int64_t nt = (N + SBN - 1) / SBN;
     if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
-    k_predict_small<<<(int)std::min<int64_t>(nt, m->num_sms), NTS, SS_TOTAL, st>>>(m->dm, P, d_x, N, nt, d_main, d_mean, d_sd);
+    k_predict_small<<<(int)std::min<int64_t>(nt, m->num_sms), NTS, m->small_lay.total, st>>>(m->dm, P, m->small_lay, d_x, N, nt, d_main, d_mean, d_sd);
     if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; m->ev_mid_valid = false; }
     m->launches++;
     DK_CUDA_TRY(cudaGetLastError());
@@ -786,6 +789,7 @@ int dk_model_clone(const dk_model* src, int device, dk_model** out) {
     m->tiles_small_doubles = src->tiles_small_doubles;
     if ((rc = peer(m->d_tiles_small, src->d_tiles_small, src->tiles_small_doubles))) return bail(rc);
     dm.tiles_small = m->d_tiles_small;
+    m->small_lay = src->small_lay;
   } else dm.tiles_small = nullptr;
   m->grid = src->grid * m->num_sms / std::max(1, src->num_sms);
   m->scratch_doubles_per_cta = src->scratch_doubles_per_cta;
@@ -1527,7 +1531,7 @@ extern "C" int dk_ei_dev_noalloc(dk_model* m, const double* d_x, int64_t N, doub
   if (!use_narrow(m, N) && use_small(m)) {
     // small designs: the single-block kernel needs no scratch at all
     const int64_t nt = (N + SBN - 1) / SBN;
-    k_predict_small<<<(int)std::min<int64_t>(nt, m->num_sms), NTS, SS_TOTAL, (cudaStream_t)stream>>>(m->dm, P, d_x, N, nt, d_ei, d_mean, d_sd);
+    k_predict_small<<<(int)std::min<int64_t>(nt, m->num_sms), NTS, m->small_lay.total, (cudaStream_t)stream>>>(m->dm, P, m->small_lay, d_x, N, nt, d_ei, d_mean, d_sd);
   } else if (use_narrow(m, N)) {
     // the same tile shape dk_ei_dev picks for this batch size, so the two entry points return the same numbers
     const int64_t nt = (N + BNN - 1) / BNN;

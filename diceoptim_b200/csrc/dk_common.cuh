@@ -53,6 +53,13 @@ __host__ __device__ __forceinline__ int b_tile_index(int k, int n) {  // k < 16,
 // first tile of block row I in a tile array: rows I' < I hold 8 I' off-diagonal tiles + 8 inverse tiles
 __host__ __device__ __forceinline__ size_t tile_base(int I) { return (size_t)4 * I * (I + 1); }
 
+// Shared-memory map of k_predict_small (dk_small.cuh), sized for the model by small_layout()
+struct SmallLayout {
+  int off_aug, off_cand, off_xs, off_rbuf, off_ring;   // bytes; barriers at 0, s2acc at 256
+  int stages;                                          // ring depth (3 .. 8); 0: the design does not fit
+  int total;                                           // bytes of dynamic shared memory
+};
+
 // Model constants handed to kernels by value (constant bank).
 struct DevModel {
   int n, d, p, n_aug, nblk, n_pad;
@@ -120,6 +127,7 @@ struct dk_model {
   double* d_tiles_bwd = nullptr;
   double* d_tiles_small = nullptr;   // small designs: inverse of the whole factor (dk_small.cuh)
   size_t tiles_small_doubles = 0;
+  dk::SmallLayout small_lay{};           // its shared-memory map (valid while dm.tiles_small != nullptr)
   double* d_Xrm = nullptr;
   double* d_small = nullptr;     // beta | RM | tuuinv | alpha | KinvF | noise_var
   size_t tiles_fwd_doubles = 0, xrm_doubles = 0, small_doubles = 0, bwd_tile_doubles = 0;  // sizes of the three uploads (dk_model_clone)

@@ -4,12 +4,21 @@
 // barriers and 8 serialised inverse-tile fetches per block row, FP64 pipe 50 % busy at cfg2.  Here the WHOLE padded factor
 // is one diagonal block: its explicit inverse (N x N, N = n_pad <= 256, formed in long double on the host like the 128 x 128
 // block inverses, and rounded once) is applied as a lower-triangular GEMM  V = inv(L_aug) c  straight from the covariance
-// tile, so a tile is: covariance generation (written directly as B fragments), then up to 24 GEMM stages on one
-// bulk-copy / mbarrier pipeline with no CTA barrier between them, then the epilogue.  No V panel: the sum of v^2 and the
-// augmented rows (-z'v, -M'v) are taken from the accumulators, so the kernel uses NO global scratch and DRAM traffic is
-// the algorithmic 8 d + 8 bytes per candidate.  One CTA per SM: 64 candidates, 16 warps as 4 x 4 (warp tile 32 x 16), the
-// covariance tile (up to 128 KB) resident in shared memory next to a 4-stage ring of 16 KB factor tiles, so that an L2
-// round trip per stage is hidden (a first version with two 32-candidate CTAs per SM and 2 stages was latency-bound).
+// tile.  No V panel: the sum of v^2 and the augmented rows (-z'v, -M'v) are taken from the accumulators, so the kernel uses
+// NO global scratch and DRAM traffic is the algorithmic 8 d + 8 bytes per candidate.
+//
+// One 512-thread CTA per SM, 64 candidates per tile, 16 warps as 4 x 4 (warp tile 32 x 16).  Per tile: covariance
+// generation straight into B fragments (one 16-row chunk per warp), then up to 24 GEMM stages with no CTA barrier between
+// them, then the epilogue — which warps 0 and 1 run for tile t - 1 while the other warps already generate tile t.
+// The factor tiles a candidate tile needs are the same for every tile, so thread 0 streams that list round and round
+// through a ring of 16 KB stages (bulk copies + mbarriers) that never drains: not between row blocks, not between
+// tiles, not during covariance generation.  The ring takes whatever shared memory the model leaves (small_layout).
+// Measured on the way (cfg2 / cfg1, 4e6 candidates, ms): blocked kernel 13.1 / 3.9; two 256-thread CTAs per SM with 32
+// candidates and a 2-stage ring 12.4 / 2.9; this shape with a ring that drains per row block and design rows re-staged
+// per tile 11.2 / 3.7; warp-specialised (8 producer warps generating the covariance of the next 32 candidates while 8
+// consumer warps multiply) 13.9 / 3.0 — eight warps with eight accumulators each do not keep the DMMA pipe busy; both
+// row blocks advancing together (16 accumulators per warp, the B fragments read once) 16.2 / 3.2: over the 128-register
+// limit of a 512-thread CTA.
 // The explicit inverse of the whole factor is less accurate than the blocked substitution on ill-conditioned factors
 // (the off-diagonal block of the inverse cancels against the diagonal one), so dk_model_create enables this kernel only
 // when a probe against long-double substitution shows it loses nothing (small_inverse_is_accurate, dk_api.cu).
@@ -20,84 +29,114 @@ namespace dk {
 
 constexpr int SBN = BN;                 // 64 candidates per tile; B tiles in the wide kernel's 16 x 64 fragment order
 constexpr int NTS = 512;                // 16 warps: 4 (rows) x 4 (columns), warp tile 32 x 16
-constexpr int S_STAGES = 4;
 constexpr int SMALL_MAX_PAD = 256;
-// shared-memory map (bytes), one CTA per SM
-constexpr int SS_RBUF = 0;                                   // covariance tile as B fragments: N x 64 doubles (<= 128 KB)
-constexpr int SS_RING = SMALL_MAX_PAD * SBN * 8;             // 131072: 4 A-tile stages; the design rows of cov-gen alias it
-constexpr int SS_CAND = SS_RING + S_STAGES * A_TILE * 8;     // 196608: xs[d][64]
-constexpr int SS_S2 = SS_CAND + DK_MAX_D * SBN * 8;          // 208896: s2acc[4][64]
-constexpr int SS_AUG = SS_S2 + 4 * SBN * 8;                  // 210944: aug[p + 1][64]
-constexpr int SS_BAR = SS_AUG + (DK_MAX_P + 1) * SBN * 8;    // 224256: 4 full + 4 empty mbarriers
-constexpr int SS_TOTAL = SS_BAR + 64;                        // 224320 (<= 227 KB)
+constexpr int SMALL_MAX_STAGES = 8;
+constexpr int SMALL_SMEM_MAX = 232448;  // 227 KB of dynamic shared memory per CTA
+
+// Shared-memory map, sized for the model: what the fixed parts leave goes to the ring (cfg2: 7 stages).  Designs whose
+// rows x d leave fewer than 3 stages stay on the blocked kernel.
+__host__ inline SmallLayout small_layout(int n, int n_pad, int d, int p) {
+  SmallLayout L{};
+  if (n_pad > SMALL_MAX_PAD) return L;
+  const int nchunks = (n + 15) / 16;
+  L.off_aug = 256 + 4 * SBN * 8;
+  L.off_cand = L.off_aug + (p + 1) * SBN * 8;
+  L.off_xs = L.off_cand + 4 * d * SBN * 8;   // [2 buffers][plain | scaled by w][d][64]
+  L.off_rbuf = L.off_xs + n_pad * d * 8;
+  L.off_ring = L.off_rbuf + nchunks * B_TILE * 8;
+  const int room = (SMALL_SMEM_MAX - L.off_ring) / (A_TILE * 8);
+  if (L.off_ring > SMALL_SMEM_MAX || room < 3) return L;
+  L.stages = room < SMALL_MAX_STAGES ? room : SMALL_MAX_STAGES;
+  L.total = L.off_ring + L.stages * A_TILE * 8;
+  return L;
+}
 // first tile of row block rb in the small tile array: row block rb' < rb holds 8 (rb' + 1) tiles
 __host__ __device__ __forceinline__ size_t small_tile_base(int rb) { return (size_t)4 * rb * (rb + 1); }
 
-// covariance of ALL design rows with the 64 candidates, written as B fragments into Rbuf.  Warp w (of 16) owns rows
-// 16 w .. 16 w + 15 (= k-chunk w), lane owns candidates lane and lane + 32; two passes of 8 rows x 2 columns = 16 chains
-// (the arithmetic per pair is covgen_rows' own).
-template <int KERNEL, bool NUG>
-__device__ __forceinline__ void covgen_small(const DevModel& M, const double* __restrict__ Xs, const double* __restrict__ xs,
-                                             double* __restrict__ Rbuf, int warp, int lane) {
-  constexpr int RB = 8;
-  const int d = M.d;
-  double* chunk = Rbuf + (size_t)warp * B_TILE;
-#pragma unroll 1
-  for (int rr = 0; rr < 16; rr += RB) {
-    const int r0 = 16 * warp + rr;
-    if (r0 >= M.n) {
-#pragma unroll
-      for (int j = 0; j < RB; j++) {
-        chunk[b_tile_index(rr + j, lane)] = 0.0;
-        chunk[b_tile_index(rr + j, lane + 32)] = 0.0;
-      }
-      continue;
+// mbarrier wait that cannot hang the GPU: a protocol error traps (the launch fails) instead of spinning for ever
+__device__ __forceinline__ void mbar_wait_guarded(unsigned long long* bar, unsigned parity) {
+  unsigned done = 0;
+  long long t0 = 0;
+  for (unsigned long long spin = 0; !done; spin++) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (!done && (spin & 1023) == 1023) {        // ~2 s of waiting is a protocol error, not a slow copy
+      if (t0 == 0) t0 = clock64();
+      else if (clock64() - t0 > 4000000000ll) __trap();
     }
-    double s[RB][2], pr[RB][2], hs[NUG ? RB : 1][2];
-#pragma unroll
-    for (int j = 0; j < RB; j++) {
-      s[j][0] = s[j][1] = 0.0;
-      pr[j][0] = pr[j][1] = 1.0;
-      if (NUG) hs[j][0] = hs[j][1] = 0.0;
-    }
-    const double* Xr = Xs + (size_t)r0 * d;
-#pragma unroll 1
-    for (int k = 0; k < d; k++) {
-      const double wk = M.w[k];
-      const double c0 = __dmul_rn(xs[k * SBN + lane], wk), c1 = __dmul_rn(xs[k * SBN + lane + 32], wk);
-      const double iwk = NUG ? M.iw[k] : 0.0;
-#pragma unroll
-      for (int j = 0; j < RB; j++) {
-        const double xr = Xr[j * d + k];
-#pragma unroll
-        for (int e = 0; e < 2; e++) {
-          const double a = fabs(__dsub_rn(xr, e ? c1 : c0));
-          if (NUG) hs[j][e] = fma(a, iwk, hs[j][e]);
-          if (KERNEL == DK_GAUSS) s[j][e] = fma(0.5 * a, a, s[j][e]);
-          else if (KERNEL == DK_EXP) s[j][e] += a;
-          else if (KERNEL == DK_MATERN3_2) { pr[j][e] *= (1.0 + a); s[j][e] += a; }
-          else if (KERNEL == DK_MATERN5_2) { pr[j][e] *= fma(a, fma(a, 1.0 / 3.0, 1.0), 1.0); s[j][e] += a; }
-          else s[j][e] += pow(a, M.shape[k]);
-        }
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < RB; j++)
-#pragma unroll
-      for (int e = 0; e < 2; e++) {
-        double c = M.sd2 * pr[j][e] * exp(-s[j][e]);
-        if (NUG && hs[j][e] < 1e-15) c += M.nugget;
-        chunk[b_tile_index(rr + j, lane + 32 * e)] = (r0 + j < M.n) ? c : 0.0;
-      }
   }
 }
 
-__device__ __forceinline__ void covgen_small_any(const DevModel& M, const double* Xs, const double* xs, double* Rbuf, int warp,
-                                                 int lane) {
-#define DK_SCOV(K)                                                                   \
-  case K:                                                                            \
-    if (M.nugget_flag) covgen_small<K, true>(M, Xs, xs, Rbuf, warp, lane);           \
-    else covgen_small<K, false>(M, Xs, xs, Rbuf, warp, lane);                        \
+// covariance of the 16 design rows of k-chunk `chunk` with candidates 32 half .. 32 half + 31, written as B fragments.
+// The lane is the fragment's own (lane = 4 nl + kl): it owns row 4 k4 + kl of each of the chunk's four row groups and the
+// candidates nl + 8 g, so a warp's stores are whole conflict-free 16-byte fragment entries; 4 rows x 4 candidates = 16
+// chains per thread.  xsw holds the candidates already scaled by w_k (the arithmetic per pair is covgen_rows' own).
+template <int KERNEL, bool NUG>
+__device__ __forceinline__ void covgen_small(const DevModel& M, const double* __restrict__ Xs, const double* __restrict__ xsw,
+                                             double* __restrict__ Rbuf, int chunk, int half, int lane) {
+  const int d = M.d, kl = lane & 3, nl = lane >> 2;
+  const int nk4 = min(4, (M.n - 16 * chunk + 3) >> 2);      // row groups of this chunk that hold design rows
+  double* out = Rbuf + (size_t)chunk * B_TILE;
+  double s[4][4], pr[4][4], hs[NUG ? 4 : 1][4];
+#pragma unroll
+  for (int k4 = 0; k4 < 4; k4++)
+#pragma unroll
+    for (int g = 0; g < 4; g++) { s[k4][g] = 0.0; pr[k4][g] = 1.0; if (NUG) hs[k4][g] = 0.0; }
+  const double* Xr = Xs + (size_t)(16 * chunk + kl) * d;
+  const double* xc = xsw + 32 * half + nl;
+#pragma unroll 1
+  for (int k = 0; k < d; k++) {
+    const double iwk = NUG ? M.iw[k] : 0.0;
+    double c[4];
+#pragma unroll
+    for (int g = 0; g < 4; g++) c[g] = xc[k * SBN + 8 * g];
+#pragma unroll
+    for (int k4 = 0; k4 < 4; k4++) {
+      if (k4 < nk4) {
+        const double xr = Xr[(4 * k4) * d + k];
+#pragma unroll
+        for (int g = 0; g < 4; g++) {
+          const double a = fabs(__dsub_rn(xr, c[g]));
+          if (NUG) hs[k4][g] = fma(a, iwk, hs[k4][g]);
+          if (KERNEL == DK_GAUSS) s[k4][g] = fma(0.5 * a, a, s[k4][g]);
+          else if (KERNEL == DK_EXP) s[k4][g] += a;
+          else if (KERNEL == DK_MATERN3_2) { pr[k4][g] *= (1.0 + a); s[k4][g] += a; }
+          else if (KERNEL == DK_MATERN5_2) { pr[k4][g] *= fma(a, fma(a, 1.0 / 3.0, 1.0), 1.0); s[k4][g] += a; }
+          else s[k4][g] += pow(a, M.shape[k]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int k4 = 0; k4 < 4; k4++) {
+    const bool live = k4 < nk4 && 16 * chunk + 4 * k4 + kl < M.n;
+    double v[4];
+#pragma unroll
+    for (int g = 0; g < 4; g++) {
+      double c = 0.0;
+      if (live) {
+        c = M.sd2 * pr[k4][g] * exp(-s[k4][g]);
+        if (NUG && hs[k4][g] < 1e-15) c += M.nugget;
+      }
+      v[g] = c;
+    }
+#pragma unroll
+    for (int q = 0; q < 2; q++)   // fragment (k4, np = 2 half + q): candidates 8 (2 np) + nl and 8 (2 np + 1) + nl
+      *reinterpret_cast<double2*>(out + ((k4 * 4 + 2 * half + q) * 32 + lane) * 2) = make_double2(v[2 * q], v[2 * q + 1]);
+  }
+}
+
+__device__ __forceinline__ void covgen_small_any(const DevModel& M, const double* Xs, const double* xsw, double* Rbuf, int chunk,
+                                                 int half, int lane) {
+#define DK_SCOV(K)                                                                          \
+  case K:                                                                                   \
+    if (M.nugget_flag) covgen_small<K, true>(M, Xs, xsw, Rbuf, chunk, half, lane);          \
+    else covgen_small<K, false>(M, Xs, xsw, Rbuf, chunk, half, lane);                       \
     break;
   switch (M.kernel) {
     DK_SCOV(DK_GAUSS) DK_SCOV(DK_EXP) DK_SCOV(DK_MATERN3_2) DK_SCOV(DK_MATERN5_2)
@@ -125,45 +164,107 @@ __device__ __forceinline__ void mma_stage_small(double (&acc)[4][2][2], const do
   }
 }
 
+// per-candidate predict.km epilogue of one tile (cand_predict with the augmented rows read from shared memory)
+__device__ __forceinline__ void small_epilogue(const DevModel& M, const CritParams& P, const double* __restrict__ xs,
+                                               const double* __restrict__ aug, const double* __restrict__ s2acc, int c,
+                                               int64_t g, double* __restrict__ out_main, double* __restrict__ out_mean,
+                                               double* __restrict__ out_sd) {
+  const int p = M.p;
+  double S[DK_MAX_P], u[DK_MAX_P];
+  double mean = 0.0;
+  for (int j = 0; j < p; j++) {
+    const double fj = (j == 0) ? 1.0 : xs[(j - 1) * SBN + c];
+    mean = fma(fj, __ldg(M.beta + j), mean);
+    u[j] = fj + aug[(1 + j) * SBN + c];
+  }
+  mean += -aug[c];
+  double s2 = M.total_sd2 - (((s2acc[c] + s2acc[SBN + c]) + s2acc[2 * SBN + c]) + s2acc[3 * SBN + c]);
+  if (P.type == DK_UK) {
+    double s22 = 0.0;
+    for (int j = 0; j < p; j++) {
+      double t = u[j];
+      for (int i = 0; i < j; i++) t -= __ldg(M.RM + i + j * p) * S[i];
+      S[j] = t / __ldg(M.RM + j + j * p);
+      s22 = fma(S[j], S[j], s22);
+    }
+    s2 += s22;
+  }
+  const double sd = sqrt(fmax(s2, 0.0));
+  if (out_mean) out_mean[g] = mean;
+  if (out_sd) out_sd[g] = sd;
+  if (out_main) {
+    double v = crit_value(P, mean, sd);
+    if (P.combine == COMBINE_MUL) v *= out_main[g];
+    else if (P.combine == COMBINE_MIN) v = fmin(v, out_main[g]);
+    out_main[g] = v;
+  }
+}
+
 __global__ void __launch_bounds__(NTS, 1)
-k_predict_small(const DevModel M, const CritParams P, const double* __restrict__ x, int64_t N, int64_t ntiles,
-                double* __restrict__ out_main, double* __restrict__ out_mean, double* __restrict__ out_sd) {
+k_predict_small(const DevModel M, const CritParams P, const SmallLayout L, const double* __restrict__ x, int64_t N,
+                int64_t ntiles, double* __restrict__ out_main, double* __restrict__ out_mean, double* __restrict__ out_sd) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, wm = warp >> 2, wn = warp & 3;
-  double* Rbuf = reinterpret_cast<double*>(smem + SS_RBUF);
-  double* ring = reinterpret_cast<double*>(smem + SS_RING);
-  double* Xs = ring;   // ALL design rows (<= 256 x d doubles = 48 KB), staged here while the ring is idle
-  double* xs = reinterpret_cast<double*>(smem + SS_CAND);
-  double* s2acc = reinterpret_cast<double*>(smem + SS_S2);
-  double* aug = reinterpret_cast<double*>(smem + SS_AUG);
-  unsigned long long* full = reinterpret_cast<unsigned long long*>(smem + SS_BAR);
-  unsigned long long* empty = full + S_STAGES;
+  unsigned long long* full = reinterpret_cast<unsigned long long*>(smem);            // ring: tile landed
+  unsigned long long* empty = full + SMALL_MAX_STAGES;                                // ring: slot consumed (16 warps)
+  double* s2acc = reinterpret_cast<double*>(smem + 256);
+  double* aug = reinterpret_cast<double*>(smem + L.off_aug);
+  double* cand = reinterpret_cast<double*>(smem + L.off_cand);                        // [2][plain | scaled][d][64]
+  double* Xs = reinterpret_cast<double*>(smem + L.off_xs);
+  double* Rbuf = reinterpret_cast<double*>(smem + L.off_rbuf);
+  double* ring = reinterpret_cast<double*>(smem + L.off_ring);
   const int n = M.n, d = M.d, p = M.p, nrb = M.nblk;
   const int live16 = (M.n_aug + 15) >> 4;        // 16-row pairs that hold real rows (design + augmented)
   const int nchunks = (n + 15) >> 4;             // k-chunks with a non-zero right-hand side (covariance rows)
+  const int nstages = L.stages;
+  const int nunits = 2 * nchunks;                // covariance work: (chunk, candidate half), dealt from warp 15 downwards
   if (tid == 0) {
-    for (int s = 0; s < S_STAGES; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], NTS / 32); }
+    for (int s = 0; s < nstages; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], NTS / 32); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  __syncthreads();
-  unsigned stage_base = 0;
-#pragma unroll 1
-  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+  for (int i = tid; i < M.n_pad * d; i += NTS) Xs[i] = __ldg(M.Xrm_s + i);   // the design does not depend on the tile
+  auto load_candidates = [&](int64_t tile, double* xs) {
     const int64_t c0 = tile * SBN;
-    __syncthreads();   // the previous tile's epilogue has read xs / aug / s2acc
     for (int i = tid; i < d * SBN; i += NTS) {
       const int k = i / SBN, j = i % SBN;
       const int64_t g = c0 + j;
-      xs[i] = (g < N) ? x[g + (int64_t)k * N] : x[(N - 1) + (int64_t)k * N];
+      const double v = (g < N) ? x[g + (int64_t)k * N] : x[(N - 1) + (int64_t)k * N];
+      xs[i] = v;
+      xs[d * SBN + i] = __dmul_rn(v, M.w[k]);   // never contracted into an FMA: a pair's value cannot depend on its tile position
     }
-    // ---- covariance tile of all row blocks at once, as B fragments ----
-    __syncthreads();   // Xs free (the previous tile's ring reads are over), xs visible
-    for (int i = tid; i < nrb * BM * d; i += NTS) Xs[i] = __ldg(M.Xrm_s + i);
-    __syncthreads();
-    if (warp < nrb * CHUNKS_PER_BLOCK) covgen_small_any(M, Xs, xs, Rbuf, warp, lane);
-    // Xs (generic-proxy writes) gives the ring back to the bulk copies; Rbuf must be complete before any warp reads it
-    asm volatile("fence.proxy.async;" ::: "memory");
-    __syncthreads();
+  };
+  load_candidates(blockIdx.x, cand);
+  __syncthreads();
+
+  // factor-tile stream: row block 0's nk0 chunks, then row block 1's, the same list for every candidate tile
+  const int nk0 = min(CHUNKS_PER_BLOCK, nchunks), per_tile = nk0 + (nrb > 1 ? nchunks : 0);
+  const int64_t my_tiles = (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+  const int64_t total = my_tiles * per_tile;
+  int64_t issued = 0;
+  int i_pos = 0, i_slot = 0; unsigned i_par = 0;     // thread 0: next list position / slot / parity to issue
+  int c_slot = 0; unsigned c_par = 0;                // every warp: next slot / parity to consume
+  auto issue = [&]() {   // thread 0 only
+    mbar_wait_guarded(&empty[i_slot], i_par ^ 1);
+    mbar_arrive_expect_tx(&full[i_slot], A_TILE * 8);
+    const double* src = M.tiles_small + (i_pos < nk0 ? (size_t)i_pos : small_tile_base(1) + (size_t)(i_pos - nk0)) * A_TILE;
+    bulk_load(ring + (size_t)i_slot * A_TILE, src, A_TILE * 8, &full[i_slot]);
+    if (++i_pos == per_tile) i_pos = 0;
+    if (++i_slot == nstages) { i_slot = 0; i_par ^= 1; }
+    issued++;
+  };
+  if (tid == 0)
+    while (issued < total && issued < nstages - 1) issue();
+
+  int it = 0;
+  int64_t prev = -1;
+#pragma unroll 1
+  for (int64_t tile = blockIdx.x; tile < ntiles; prev = tile, tile += gridDim.x, it++) {
+    const double* xs = cand + (size_t)(it & 1) * 2 * d * SBN;
+    // ---- epilogue of the previous tile (warps 0, 1) beside the covariance tile of this one ----
+    if (prev >= 0 && tid < SBN && prev * SBN + tid < N)
+      small_epilogue(M, P, cand + (size_t)((it - 1) & 1) * 2 * d * SBN, aug, s2acc, tid, prev * SBN + tid, out_main, out_mean, out_sd);
+    for (int u = NTS / 32 - 1 - warp; u < nunits; u += NTS / 32) covgen_small_any(M, Xs, xs + d * SBN, Rbuf, u >> 1, u & 1, lane);
+    __syncthreads();   // Rbuf complete; aug / s2acc free
     double s2p[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
     // ---- V = inv(L_aug) c, row block by row block, all stages on one pipeline ----
 #pragma unroll 1
@@ -173,30 +274,19 @@ k_predict_small(const DevModel M, const CritParams P, const double* __restrict__
       for (int mi = 0; mi < 4; mi++)
 #pragma unroll
         for (int ni = 0; ni < 2; ni++) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
-      const int nk = min(CHUNKS_PER_BLOCK * (rb + 1), nchunks);
-      const double* Atiles = M.tiles_small + small_tile_base(rb) * A_TILE;
+      const int nk = rb == 0 ? nk0 : nchunks;
       const int plo = CHUNKS_PER_BLOCK * rb + 2 * wm, phi = plo + 1;   // this warp's global pair indices
-      auto issue = [&](int idx) {   // thread 0 only
-        const unsigned gi = stage_base + idx, slot = gi % S_STAGES, par = (gi / S_STAGES) & 1;
-        mbar_wait(&empty[slot], par ^ 1);
-        mbar_arrive_expect_tx(&full[slot], A_TILE * 8);
-        bulk_load(ring + slot * A_TILE, Atiles + (size_t)idx * A_TILE, A_TILE * 8, &full[slot]);
-      };
-      if (tid == 0)
-        for (int s = 0; s < S_STAGES - 1 && s < nk; s++) issue(s);
 #pragma unroll 1
       for (int kc = 0; kc < nk; kc++) {
-        if (tid == 0 && kc + S_STAGES - 1 < nk) issue(kc + S_STAGES - 1);
-        const unsigned gi = stage_base + kc, slot = gi % S_STAGES, par = (gi / S_STAGES) & 1;
-        mbar_wait(&full[slot], par);
+        if (tid == 0 && issued < total) issue();   // nstages - 1 tiles ahead: the slot this warp consumed one step ago
+        mbar_wait_guarded(&full[c_slot], c_par);
         // the inverse is lower triangular: pair q needs chunks 0..q; pairs made of padding take no part
         const bool lo = kc <= plo && plo < live16, hi = kc <= phi && phi < live16;
-        if (lo || hi) mma_stage_small(acc, ring + slot * A_TILE, Rbuf + (size_t)kc * B_TILE, wm, wn, lane, lo, hi);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        if (lo || hi) mma_stage_small(acc, ring + (size_t)c_slot * A_TILE, Rbuf + (size_t)kc * B_TILE, wm, wn, lane, lo, hi);
         __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[slot]);
+        if (lane == 0) mbar_arrive(&empty[c_slot]);
+        if (++c_slot == nstages) { c_slot = 0; c_par ^= 1; }
       }
-      stage_base += nk;
       // ---- sum of v^2 over the design rows; the augmented rows go to `aug` ----
 #pragma unroll
       for (int mi = 0; mi < 4; mi++) {
@@ -221,41 +311,12 @@ k_predict_small(const DevModel M, const CritParams P, const double* __restrict__
         v += __shfl_xor_sync(0xffffffffu, v, 16);
         if (lane < 4) s2acc[wm * SBN + 16 * wn + 8 * ni + 2 * lane + e] = v;
       }
-    __syncthreads();
-    // ---- per-candidate predict.km epilogue (cand_predict with the augmented rows read from shared memory) ----
-    if (tid < SBN && c0 + tid < N) {
-      const int c = tid;
-      double S[DK_MAX_P], u[DK_MAX_P];
-      double mean = 0.0;
-      for (int j = 0; j < p; j++) {
-        const double fj = (j == 0) ? 1.0 : xs[(j - 1) * SBN + c];
-        mean = fma(fj, __ldg(M.beta + j), mean);
-        u[j] = fj + aug[(1 + j) * SBN + c];
-      }
-      mean += -aug[c];
-      double s2 = M.total_sd2 - (((s2acc[c] + s2acc[SBN + c]) + s2acc[2 * SBN + c]) + s2acc[3 * SBN + c]);
-      if (P.type == DK_UK) {
-        double s22 = 0.0;
-        for (int j = 0; j < p; j++) {
-          double t = u[j];
-          for (int i = 0; i < j; i++) t -= __ldg(M.RM + i + j * p) * S[i];
-          S[j] = t / __ldg(M.RM + j + j * p);
-          s22 = fma(S[j], S[j], s22);
-        }
-        s2 += s22;
-      }
-      const double sd = sqrt(fmax(s2, 0.0));
-      const int64_t g = c0 + c;
-      if (out_mean) out_mean[g] = mean;
-      if (out_sd) out_sd[g] = sd;
-      if (out_main) {
-        double v = crit_value(P, mean, sd);
-        if (P.combine == COMBINE_MUL) v *= out_main[g];
-        else if (P.combine == COMBINE_MIN) v = fmin(v, out_main[g]);
-        out_main[g] = v;
-      }
-    }
+    // the next tile's candidates, into the buffer the epilogue above has finished with
+    if (tile + gridDim.x < ntiles) load_candidates(tile + gridDim.x, cand + (size_t)((it + 1) & 1) * 2 * d * SBN);
+    __syncthreads();   // aug / s2acc / candidates visible; every warp is done with Rbuf
   }
+  if (prev >= 0 && tid < SBN && prev * SBN + tid < N)
+    small_epilogue(M, P, cand + (size_t)((it - 1) & 1) * 2 * d * SBN, aug, s2acc, tid, prev * SBN + tid, out_main, out_mean, out_sd);
 }
 
 }  // namespace dk

@@ -151,6 +151,37 @@ def predict_km(model, newdata, type="UK"):
     return {"mean": mean, "sd": np.sqrt(s2), "c": c, "Tinv.c": v, "S": S}
 
 
+def back_solve(T, B):
+    """backsolve(T, B): T upper (float64 values), long-double substitution from the last row up."""
+    T = _ld(T); V = _ld(B).copy()
+    if V.ndim == 1:
+        V = V[:, None]
+    n = T.shape[0]
+    for i in range(n - 1, -1, -1):
+        if i < n - 1:
+            V[i] -= T[i, i + 1:] @ V[i + 1:]
+        V[i] /= T[i, i]
+    return V
+
+
+def predict_sensitivity(model, newdata, type="UK"):
+    """How far predict.km's mean and sd^2 move when every entry of the covariance vector c(x) is off by a relative delta:
+    |d mean| <= delta * sum_i |w_i c_i| with w = T^-1 z, and |d sd^2| <= delta * 2 sum_i |g_i c_i| with
+    g = T^-1 (v + M TM^-1 S) (UK) or T^-1 v (SK).  Any float64 evaluation carries delta of a few ulp (exp, the scaled
+    distance), so on an ill-conditioned design (w of size 1e6 with alternating signs) this is the error no float64
+    implementation can avoid; tests use it as the allowance where the float64 oracle itself misses the tolerance."""
+    pr = predict_km(model, newdata, type=type)
+    c, v = pr["c"], pr["Tinv.c"]
+    w = back_solve(model.T, _ld(model.z))[:, 0]
+    g = v
+    if type == "UK":
+        M = _ld(np.atleast_2d(model.M).reshape(model.n, -1))
+        TM = _chol_upper(M.T @ M)
+        g = v + M @ back_solve(TM, pr["S"])
+    g = back_solve(model.T, g)
+    return {"mean": np.abs(w)[:, None].T @ np.abs(c), "sd2": 2.0 * np.einsum("ij,ij->j", np.abs(g), np.abs(c))}
+
+
 def EI(x, model, plugin=None, type="UK", minimization=True, proxy=False, pred=None):
     """R/EI.R:112-132 over the rows of x."""
     if plugin is None:

@@ -47,15 +47,17 @@ def assert_close_adjudicated(got, ref, hi_of, rtol=1e-10, floor=0.0, loose=2e-9,
     the reference's formula decides: hi_of(indices) returns the extended-precision restatement (oracle/hiprec.py) at the
     offending entries.  The GPU must then be within rtol of THAT or, where no float64 evaluation reaches rtol (sd^2 - |v|^2
     cancelling on a gauss-kernel design: 1.4e-10 measured at n = 40), not further from it than four times the float64 oracle
-    is; and within `loose` of
-    the oracle in any case."""
+    is at that entry, or than the oracle's own worst relative error over the offending entries (the conditioning belongs
+    to the model, and which entry a float64 evaluation happens to hit well is chance); and within `loose` of the oracle in
+    any case."""
     got = np.asarray(got, float); ref = np.asarray(ref, float)
     bad = np.flatnonzero(~(np.abs(got - ref) <= rtol * np.abs(ref) + floor))
     if bad.size == 0:
         return 0
     hi = np.asarray(hi_of(bad), dtype=np.longdouble)
     g = got[bad].astype(np.longdouble); o = ref[bad].astype(np.longdouble)
-    allowed = np.maximum(rtol * np.abs(hi) + floor, 4.0 * np.abs(o - hi))
+    oracle_worst = np.max(np.abs(o - hi) / np.maximum(np.abs(hi), 1e-300))
+    allowed = np.maximum(rtol * np.abs(hi) + floor, np.maximum(4.0 * np.abs(o - hi), oracle_worst * np.abs(hi)))
     assert np.all(np.abs(g - hi) <= allowed), (what, "GPU vs long double", float(np.max(np.abs(g - hi) / np.maximum(np.abs(hi), 1e-300))),
                                                "oracle vs long double", float(np.max(np.abs(o - hi) / np.maximum(np.abs(hi), 1e-300))))
     assert np.all(np.abs(got[bad] - ref[bad]) <= loose * np.abs(ref[bad]) + floor), (what, "GPU vs oracle", float(np.max(np.abs(got[bad] - ref[bad]))))
