@@ -211,6 +211,9 @@ k_grad_fused(const DevModel M, const CritParams P, const double* __restrict__ x,
       double g[DK_MAX_D];
 #pragma unroll
       for (int k = 0; k < DK_MAX_D; k++) g[k] = 0.0;
+#ifdef DK_X_NOGRADACC  // what-if build: skip the gradient reduction (timing only)
+      if (M.n < 0)
+#endif
       if constexpr (KSEL >= 0) grad_accumulate<KSEL>(M, xs, cpanel, wpanel, c, slice, cA, cW, g);
       else switch (M.kernel) {
         case DK_GAUSS: grad_accumulate<DK_GAUSS>(M, xs, cpanel, wpanel, c, slice, cA, cW, g); break;

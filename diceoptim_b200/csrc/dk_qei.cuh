@@ -288,21 +288,38 @@ k_qei_cdf(const double* __restrict__ moments, int64_t B, int q, double plugin, i
   }
   double term = 0.0;           // this lane's first_term[k] + sum_i sym[k,i] Sigma_k[i,k]
   double symrow[4] = {0.0, 0.0, 0.0, 0.0}, nonsym[4] = {0.0, 0.0, 0.0, 0.0};
-  double first = 0.0;
+  double first = 0.0, handed = 0.0;
   const bool active = valid && qq >= 2 && k < qq;
-  if (active) {
+  // The second term needs sym[k][i] for i >= k: 4, 3, 2, 1 (q - 1)-variate CDFs on lanes 0..3.  Lane 0 hands its last
+  // entry, sym[0][qq - 1], to the lane with the least work (qq - 1; lane 2 when qq = 2), so a group's lanes evaluate
+  // 3, 3, 2, 2 of them: the warp runs three rounds instead of four.  The entry is computed from the same inputs by the same
+  // code (one loop body), so the result does not depend on the lane that evaluates it.
+  const int helper = (qq == 2) ? 2 : qq - 1;
+  const bool helps = valid && qq >= 2 && k == helper;
+  const int nown = active ? ((k == 0) ? qq - 1 : qq - k) : 0;
+  if (active || helps) {
     double Sk[16], mk[4], bk[4], xk[4];
-    covzk_dev(qq, Sg, k, Sk);
-    for (int i = 0; i < qq; i++) {
-      mk[i] = (i == k) ? -mu[k] : mu[i] - mu[k];
-      bk[i] = (i == k) ? -plugin : 0.0;
-      if (minimization) { mk[i] = -mk[i]; bk[i] = -bk[i]; }
-      xk[i] = bk[i] - mk[i];
+    auto setup = [&](int kk) {   // Z^(kk): covariance, mean and bounds (R/qEI.R:145-156)
+      covzk_dev(qq, Sg, kk, Sk);
+      for (int i = 0; i < qq; i++) {
+        mk[i] = (i == kk) ? -mu[kk] : mu[i] - mu[kk];
+        bk[i] = (i == kk) ? -plugin : 0.0;
+        if (minimization) { mk[i] = -mk[i]; bk[i] = -bk[i]; }
+        xk[i] = bk[i] - mk[i];
+      }
+    };
+    if (active) {
+      setup(k);
+      const double pk = pmnorm_dev(qq, xk, Sk);
+      first = (mu[k] - plugin) * pk;
+      if (minimization) first = -first;
+      for (int i = 0; i < qq; i++) nonsym[i] = Sk[i * 4 + k];
     }
-    const double pk = pmnorm_dev(qq, xk, Sk);
-    first = (mu[k] - plugin) * pk;
-    if (minimization) first = -first;
-    for (int i = k; i < qq; i++) {
+    const int ntask = nown + (helps ? 1 : 0);
+    for (int s = 0; s < ntask; s++) {
+      const bool foreign = s >= nown;
+      if (foreign) setup(0);
+      const int i = foreign ? qq - 1 : k + s;
       const double sii = Sk[i * 4 + i], sdi = sqrt(sii);
       const double phi_ik = dnorm_std((bk[i] - mk[i]) / sdi) / sdi;
       // get_cik / get_sigmaik (R/qEI.R:196-227): condition Z^(k) on component i
@@ -319,9 +336,14 @@ k_qei_cdf(const double* __restrict__ moments, int64_t B, int q, double plugin, i
         }
         r++;
       }
-      symrow[i] = phi_ik * pmnorm_dev(qq - 1, cik, sik);
+      const double val = phi_ik * pmnorm_dev(qq - 1, cik, sik);
+      if (foreign) handed = val;
+      else symrow[i] = val;
     }
-    for (int i = 0; i < qq; i++) nonsym[i] = Sk[i * 4 + k];
+  }
+  {  // sym[0][qq - 1] back to lane 0 of the group
+    const double hv = __shfl_sync(0xffffffffu, handed, (threadIdx.x & 28) + (helper & 3));
+    if (active && k == 0) symrow[qq - 1] = hv;
   }
   // exchange the upper-triangular sym entries inside the 4-lane group: sym[k][i] = sym[i][k] for i < k
   const int base = threadIdx.x & 28;
