@@ -394,7 +394,7 @@ def max_qEI(model: KM, npoints, lower, upper, crit="exact", minimization=True, o
     lo = np.tile(lower, npoints); up = np.tile(upper, npoints)
     plugin_v = float(np.min(model.y)) if minimization else float(np.max(model.y))
     plugin_g = float(np.min(model.y)) if minimization else -float(np.max(model.y))
-    optimizer = oc.get("optimizer", "device" if (minimization and 2 <= npoints <= 4) else "batched")
+    optimizer = oc.get("optimizer", "device" if (minimization and 2 <= npoints <= 10) else "batched")
     if optimizer == "device":
         # all nStarts runs advance together ON THE DEVICE (dk_polish): one qEI + one qEI.grad launch per trip.  (Maximisation
         # keeps the host variant: the reference evaluates value and gradient with different plugins there, R/qEI.R:130 vs

@@ -196,7 +196,6 @@ int dk_multi_qei(dk_multi* mm, const double* x, int64_t B, int q, double plugin,
   int rc = check_multi(mm, x, B);
   if (rc) return rc;
   if (q < 1 || q > DK_MAX_Q_LATTICE) return fail(DK_ERR_ARG, "qEI batch size q=%d outside 1..%d", q, DK_MAX_Q_LATTICE);
-  if (out_grad && q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI.grad is implemented for 2 <= q <= %d", DK_MAX_Q);
   if (out_grad && q < 2) return fail(DK_ERR_ARG, "qEI.grad needs q >= 2 (use dk_multi_ei_grad for q = 1)");
   if (!out && !out_grad) return fail(DK_ERR_ARG, "both outputs are NULL");
   const int G = (int)mm->models.size();

@@ -268,7 +268,7 @@ extern "C" int dk_polish(dk_model* m, const dk_crit_spec* crit, int q, const dou
   if (S == 0) return DK_OK;
   const bool qei = crit->criterion == DK_CRIT_QEI;
   if (!qei) q = 1;
-  if (q < 1 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "dk_polish: q = %d outside 1..%d", q, DK_MAX_Q);
+  if (q < 1 || q > DK_MAX_Q_LATTICE) return fail(DK_ERR_ARG, "dk_polish: q = %d outside 1..%d", q, DK_MAX_Q_LATTICE);
   if (qei && q < 2) return fail(DK_ERR_ARG, "dk_polish: qEI needs q >= 2 (q = 1 is EI)");
   dk_lbfgs_options o{100, 8, 0.0, 1e7, 25};
   if (opt) o = *opt;

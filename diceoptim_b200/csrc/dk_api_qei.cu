@@ -1,6 +1,6 @@
 // dk_api_qei.cu — C ABI entry points of the qEI family (include/dk_b200.h): dk_qei*, dk_qei_grad*, dk_mvn_cdf.
 #include "dk_host.h"
-#include "dk_qei_gen.cuh"
+#include "dk_qei_grad_gen.cuh"
 
 using namespace dk;
 
@@ -119,11 +119,48 @@ extern "C" int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q,
                                int minimization, double* d_grad, void* stream) {
   int rc = check_call(m, d_x, B);
   if (rc) return rc;
-  if (q < 2 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI.grad batch size q=%d outside 2..%d (use dk_ei_grad for q = 1)", q, DK_MAX_Q);
+  if (q < 2 || q > DK_MAX_Q_LATTICE)
+    return fail(DK_ERR_ARG, "qEI.grad batch size q=%d outside 2..%d (use dk_ei_grad for q = 1)", q, DK_MAX_Q_LATTICE);
   if (!d_grad) return fail(DK_ERR_ARG, "d_grad is NULL");
   if (B == 0) return DK_OK;
   DeviceGuard guard(m->device);
   if ((rc = ensure_bwd(m))) return rc;
+  if (q > DK_MAX_Q) {
+    // 5 .. 10 points per batch: general-q derivatives + one CTA per batch for the gradient of the lattice CDFs (dk_qei_grad_gen.cuh)
+    static bool gen_attr_done[64] = {};
+    if (m->device < 64 && !gen_attr_done[m->device]) {
+      DK_CUDA_TRY(cudaFuncSetAttribute(k_qei_grad_moments_gen, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL + PIPE_SMEM));
+      DK_CUDA_TRY(cudaFuncSetAttribute(k_qei_grad_cdf_gen, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(GenGradShared)));
+      gen_attr_done[m->device] = true;
+    }
+    if ((rc = ensure_mom(m, (size_t)B * gen_mom_stride(q)))) return rc;
+    // derivatives of every batch, then the q summands of every batch's gradient
+    const size_t deriv_part = (size_t)B * qei_deriv_stride_gen(q, m->d);
+    const size_t need = deriv_part + (size_t)B * q * q * m->d;
+    if (m->deriv_doubles < need) {
+      if (m->d_deriv) { cudaFree(m->d_deriv); m->device_bytes -= m->deriv_doubles * 8; m->d_deriv = nullptr; m->deriv_doubles = 0; }
+      if ((rc = dev_alloc(m, &m->d_deriv, need))) return rc;
+      m->deriv_doubles = need;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int nb = BN / q;
+    const int64_t ntiles = (B + nb - 1) / nb;
+    if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev0, st));
+    k_qei_grad_moments_gen<<<(int)std::min<int64_t>(ntiles, m->grid), NT, SM_TOTAL + PIPE_SMEM, st>>>(
+        m->dm, type, q, d_x, B, ntiles, m->d_vscratch, m->d_wscratch, m->d_cscratch, m->scratch_doubles_per_cta, m->d_mom,
+        m->d_deriv);
+    DK_CUDA_TRY(cudaGetLastError());
+    if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev_mid, st));
+    double* d_partial = m->d_deriv + deriv_part;
+    k_qei_grad_cdf_gen<<<(unsigned)std::min<int64_t>(B * q, 8 * (int64_t)m->num_sms), CDF_THREADS, sizeof(GenGradShared), st>>>(
+        m->d_mom, m->d_deriv, B, q, m->d, plugin, minimization, m->dm.sd2, d_partial);
+    DK_CUDA_TRY(cudaGetLastError());
+    k_qei_grad_sum_gen<<<(unsigned)std::min<int64_t>(B, 8 * (int64_t)m->num_sms), CDF_THREADS, 0, st>>>(d_partial, B, q, m->d, d_grad);
+    if (m->timing) { DK_CUDA_TRY(cudaEventRecord(m->ev1, st)); m->ev_valid = true; m->ev_mid_valid = true; }
+    m->launches += 3;
+    DK_CUDA_TRY(cudaGetLastError());
+    return DK_OK;
+  }
   if ((rc = ensure_qei(m, B))) return rc;
   static bool attr_done[64] = {};
   if (m->device < 64 && !attr_done[m->device]) {
@@ -157,7 +194,8 @@ extern "C" int dk_qei_grad(dk_model* m, const double* x, int64_t B, int q, doubl
                            double* out_grad) {
   int rc = check_call(m, x, B);
   if (rc) return rc;
-  if (q < 2 || q > DK_MAX_Q) return fail(DK_ERR_ARG, "qEI.grad batch size q=%d outside 2..%d (use dk_ei_grad for q = 1)", q, DK_MAX_Q);
+  if (q < 2 || q > DK_MAX_Q_LATTICE)
+    return fail(DK_ERR_ARG, "qEI.grad batch size q=%d outside 2..%d (use dk_ei_grad for q = 1)", q, DK_MAX_Q_LATTICE);
   if (!out_grad) return fail(DK_ERR_ARG, "out_grad is NULL");
   return host_qei(m, x, B * q, 0, B, q, plugin, type, minimization, nullptr, out_grad);
 }

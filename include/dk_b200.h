@@ -45,7 +45,7 @@ enum {
 #define DK_MAX_D 24   /* input dimension limit of the fused kernels */
 #define DK_MAX_P 25   /* trend columns (1 for ~1, d+1 for ~.) */
 #define DK_MAX_Q 4    /* qEI / qEI.grad batch size served by the deterministic CDF kernels */
-#define DK_MAX_Q_LATTICE 10 /* qEI batch size served by the fixed-lattice Genz CDF (5 .. 10 points, values only) */
+#define DK_MAX_Q_LATTICE 10 /* qEI / qEI.grad batch size served by the fixed-lattice Genz CDF (5 .. 10 points) */
 
 typedef struct dk_model dk_model;
 
@@ -194,7 +194,7 @@ int dk_screen(dk_model* m, const double* x, int x_on_device, const dk_uniform_sp
  * history, step lengths) stays in device memory, the host reads one int per trip (starts still running).
  * Projected L-BFGS with Armijo backtracking along the projection arc; same stopping rules as optim's L-BFGS-B (factr,
  * pgtol, maxit).  x0 / out_x: (S q) x d column-major, rows s q .. s q + q - 1 = start s (q = 1 except for DK_CRIT_QEI,
- * 2 <= q <= DK_MAX_Q); lower / upper: d (NULL = 0 / 1); out_val[S] = criterion at out_x; out_iters[S] may be NULL. */
+ * 2 <= q <= DK_MAX_Q_LATTICE); lower / upper: d (NULL = 0 / 1); out_val[S] = criterion at out_x; out_iters[S] may be NULL. */
 typedef struct {
   int maxit;          /* iterations per start (optim's maxit; default 100) */
   int history;        /* (s, y) pairs kept, 1..16 (default 8; optim's lmm is 5) */
@@ -253,7 +253,7 @@ int dk_akg_grad_dev(dk_model* m, const double* d_x, int64_t N, double new_noise_
 
 /* qEI(x, model, plugin, type, minimization) for B batches of q points — replaces
  * /root/reference/R/qEI.R:119-261 (incl. covZk / get_cik / get_sigmaik and the duplicate test of
- * R/qEI.R:124-128).  x is (B*q) x d column-major; rows b*q .. b*q+q-1 form batch b.  1 <= q <= DK_MAX_Q.
+ * R/qEI.R:124-128).  x is (B*q) x d column-major; rows b*q .. b*q+q-1 form batch b.  1 <= q <= DK_MAX_Q_LATTICE.
  * plugin must be given (R default: min(y), or max(y) when !minimization, R/qEI.R:129-130).
  * The q-variate normal CDFs (mnormt::pmnorm in the reference) are deterministic Genz bivariate /
  * Plackett trivariate and quadrivariate rules; the exact second term is returned for fastCompute
@@ -261,11 +261,12 @@ int dk_akg_grad_dev(dk_model* m, const double* d_x, int64_t N, double new_noise_
 int dk_qei(dk_model* m, const double* x, int64_t B, int q, double plugin, int type, int minimization, double* out);
 int dk_qei_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type, int minimization,
                double* d_out, void* stream);
-/* qEI.grad for B batches of q points (2 <= q <= DK_MAX_Q; q = 1 is dk_ei_grad) — replaces
+/* qEI.grad for B batches of q points (2 <= q <= DK_MAX_Q_LATTICE; q = 1 is dk_ei_grad) — replaces
  * /root/reference/R/qEI.grad.R:267-424 with krigingDeriv / decompo / GPhi / HPhi (:1-142).  out_grad is
  * (B*q) x d column-major, row b*q + l = gradient with respect to point l of batch b.  plugin must be given
  * (R default: min(y), or -max(y) when !minimization, R/qEI.grad.R:272-276,297).  Exact term B for both
- * values of fastCompute. */
+ * values of fastCompute.  q > DK_MAX_Q: the CDFs of dimension >= 5 inside GPhi / HPhi / term B come from the fixed
+ * lattice (one CTA per batch; 5160 of them at q = 10, about 0.15 s per batch). */
 int dk_qei_grad(dk_model* m, const double* x, int64_t B, int q, double plugin, int type, int minimization, double* out_grad);
 int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type, int minimization,
                     double* d_grad, void* stream);

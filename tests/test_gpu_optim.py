@@ -162,6 +162,12 @@ def test_device_polish_quantile_and_qei(gpu_lib):
     v0 = qEI(xb, km, plugin=pl)
     assert np.all(r2["f"] >= v0 * (1 - 1e-12))
     assert np.allclose(qEI(r2["x"].reshape(5, 3, 2), km, plugin=pl), r2["f"], rtol=1e-10)
+    # q = 5: value and gradient from the general-q kernels (lattice CDFs)
+    xb5 = np.random.default_rng(7).random((3, 5, 2))
+    r5 = device_polish(km, "qEI", xb5.reshape(3, 10), lo, up, q=5, plugin=pl, maxit=15)
+    v5 = qEI(xb5, km, plugin=pl)
+    assert np.all(r5["f"] >= v5 * (1 - 1e-12)) and np.any(r5["f"] > v5 * 1.01)
+    assert np.allclose(qEI(r5["x"].reshape(3, 5, 2), km, plugin=pl), r5["f"], rtol=1e-10)
     km.release()
 
 

@@ -187,6 +187,57 @@ def test_qei_general_q_matches_oracle(gpu_lib, q, trend, type):
     km.release()
 
 
+@pytest.mark.parametrize("q,trend,type", [(5, "const", "UK"), (5, "linear", "UK"), (6, "const", "SK"), (7, "const", "UK")])
+def test_qei_grad_general_q_matches_oracle(gpu_lib, q, trend, type):
+    """qEI.grad for q > 4 (csrc/dk_qei_grad_gen.cuh) against the oracle's restatement of R/qEI.grad.R:267-424, which evaluates
+    its normal CDFs by the same rules (deterministic up to dimension 4, the fixed lattice above); the q - 3 .. q variate CDFs
+    of GPhi / HPhi / term B all take part.  1e-8 of the largest entry (sums of a few hundred CDF terms of both signs)."""
+    from diceoptim_b200 import qEI_grad
+    from oracle import diceoptim as do
+    km = small_model("matern5_2", trend, n=60, d=2, seed=80 + q, noise_var=0.02)
+    ko = to_oracle(km)
+    rng = np.random.default_rng(20 + q)
+    B = 3 if q <= 6 else 2
+    xb = rng.random((B, q, 2))
+    plugin = float(np.median(km.y))
+    got = qEI_grad(xb, km, plugin=plugin, type=type)
+    assert got.shape == (B, q, 2)
+    for b in range(B):
+        ref = do.qEI_grad(xb[b], ko, plugin=plugin, type=type, fastCompute=False)
+        assert np.max(np.abs(ref)) > 1e-6
+        assert np.max(np.abs(got[b] - ref)) <= 1e-8 * np.max(np.abs(ref)), (b, np.max(np.abs(got[b] - ref)), np.max(np.abs(ref)))
+    if q == 5:
+        gm = qEI_grad(xb[:1], km, plugin=-plugin, type=type, minimization=False)
+        ref = do.qEI_grad(xb[0], ko, plugin=-plugin, type=type, minimization=False, fastCompute=False)
+        assert np.max(np.abs(gm[0] - ref)) <= 1e-8 * np.max(np.abs(ref))
+        xd = xb[:1].copy(); xd[0, 3] = km.X[7]                     # a duplicate of the design -> zero matrix
+        assert np.all(qEI_grad(xd, km, plugin=plugin, type=type) == 0.0)
+    km.release()
+
+
+def test_qei_grad_general_q_is_the_derivative_of_the_device_value(gpu_lib):
+    """Independent of the oracle: central differences of the device qEI (q = 6; its CDFs come from the same fixed lattice, so
+    the value is a smooth function of x) against the device gradient."""
+    from diceoptim_b200 import qEI, qEI_grad
+    km = small_model("matern5_2", "const", n=50, d=2, seed=91)
+    x = np.random.default_rng(5).random((6, 2))
+    plugin = float(np.median(km.y))
+    g = qEI_grad(x, km, plugin=plugin)
+    h = 1e-5
+    xs = []
+    for l in range(6):
+        for j in range(2):
+            for sgn in (1.0, -1.0):
+                xp = x.copy(); xp[l, j] += sgn * h
+                xs.append(xp)
+    v = qEI(np.stack(xs), km, plugin=plugin).reshape(6, 2, 2)
+    fd = (v[:, :, 0] - v[:, :, 1]) / (2 * h)
+    assert np.max(np.abs(g)) > 1e-4
+    # the lattice value carries a 1e-5-relative quadrature error whose derivative is not controlled: 1e-3 of the largest entry
+    assert np.max(np.abs(fd - g)) <= 1e-3 * np.max(np.abs(g)), (fd, g)
+    km.release()
+
+
 def test_qei_q10_against_monte_carlo_reference_example(gpu_lib):
     """The reference's own self-check (R/qEI.R:66-115): hartman4, 3^4 = 81-point factorial design, q = 10, exact qEI against
     the Monte-Carlo mean improvement over draws of the conditional Gaussian vector."""
