@@ -629,6 +629,34 @@ def main():
             lat["model_append_ms_per_point"] = 1e3 * (time.perf_counter() - t0) / 4
             hc.close()
             extra["latency"] = lat
+            # ---- the small BASELINE configs at their own sizes (cfg2: EI over 10^6 points; cfg1: EI on the 100 x 100 grid) ----
+            small = {}
+            for key, label in (("cfg2_hartman4_n200", "cfg2"), ("cfg1_branin2_n20", "cfg1")):
+                kms = synth.config_model(key)
+                hs = kms.handle(local)
+                lib.dk_model_set_timing(hs.ptr, 1)
+                xh = np.asfortranarray(synth.config_candidates(key))
+                Ns = xh.shape[0]
+                xd = torch.from_numpy(np.ascontiguousarray(xh.T)).to("cuda")          # d x N row-major = N x d column-major
+                eo = torch.empty(Ns, dtype=torch.float64, device="cuda"); eh = np.empty(Ns)
+                pls = float(np.min(kms.y)); ks = []
+                for _ in range(6):
+                    _lib.check(lib.dk_ei_dev(hs.ptr, vp(xd), Ns, pls, 1, 1, 0, vp(eo), None, None, sptr), "dk_ei_dev")
+                    torch.cuda.synchronize(); ks.append(lib.dk_model_last_kernel_ms(hs.ptr))
+                kt = min(ks[1:])
+                ht = best_ms(lambda: _lib.check(lib.dk_ei(hs.ptr, vp(xh), Ns, pls, 1, 1, 0, vp(eh), None, None), "dk_ei"))
+                assert np.array_equal(eo.cpu().numpy(), eh, equal_nan=True)
+                fls = flops_per_candidate(kms.n, kms.p)
+                ach = fls * Ns / (kt * 1e-3) * 1e-12
+                small[label] = {"workload": key, "n": kms.n, "d": kms.d, "candidates": int(Ns), "value": Ns / (kt * 1e-3), "unit": UNIT,
+                                "kernel": "k_predict_small" if lib.dk_model_small_kernel(hs.ptr) else "k_predict_fused_tma",
+                                "kernel_ms": kt, "roofline": {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                                                              "flops_per_candidate": fls},
+                                "e2e": {"value": Ns / (ht * 1e-3), "unit": UNIT, "ms": ht, "h2d_bytes": int(Ns * kms.d * 8),
+                                        "d2h_bytes": int(Ns * 8), "host_memory": "pageable"}}
+                del xd, eo
+                kms.release()
+            extra["small_designs"] = small
         if extra:
             line["extra"] = extra
         print(json.dumps(line), flush=True)

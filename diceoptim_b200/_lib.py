@@ -99,6 +99,7 @@ SIGNATURES = {
     "dk_qei_dev": (_I, [_V, _V, _L, _I, _D, _I, _I, _V, _V]),
     "dk_qei_grad": (_I, [_V, _V, _L, _I, _D, _I, _I, _V]),
     "dk_qei_grad_dev": (_I, [_V, _V, _L, _I, _D, _I, _I, _V, _V]),
+    "dk_qei_value_grad_dev": (_I, [_V, _V, _L, _I, _D, _I, _I, _V, _V, _V]),
     "dk_mvn_cdf": (_I, [_I, _L, _V, _V, _V]),
     "dk_multi_create": (_I, [C.POINTER(dk_model_desc), _V, _I, C.POINTER(_V)]),
     "dk_multi_destroy": (None, [_V]),

@@ -4,7 +4,7 @@ Each function mirrors the R function of the same name (argument names, defaults,
 behaviour); matrices of candidates are evaluated in one fused kernel launch.  Differences from
 the reference are limited to what a GPU batch cannot give back: ``envir`` receives the
 per-candidate scalars (xcr, xcr.prob, xcr.dens, kriging.sd) but not the n x N matrices ``c`` and
-``Tinv.c`` (SURVEY 8(b) "envir contract").
+``Tinv.c`` (SURVEY 8(b) "envir contract"); ``qEI(x, envir)`` leaves the finished gradient there for ``qEI_grad(x, envir)``.
 """
 from __future__ import annotations
 
@@ -279,6 +279,22 @@ def qEI(x, model: KM, plugin=None, type="UK", minimization=True, fastCompute=Tru
     rows = np.asfortranarray(x.reshape(B * q, d))
     out = np.empty(B)
     h = model.handle(device)
+    if envir is not None and minimization and 2 <= q:
+        # qEI(x, envir) ... qEI.grad(x, envir) (R/qEI.R:190-198, R/qEI.grad.R:299-316): the reference stores the kriging moments
+        # and CDF terms for the gradient call that optim issues at the same x.  Here one pass over the model gives value and
+        # gradient (dk_qei_value_grad_dev, the value at x itself rather than at round(x, 8)); the gradient waits in envir.
+        import torch
+        with torch.cuda.device(h.device):
+            xd = torch.from_numpy(np.ascontiguousarray(rows.T)).cuda()
+            vd = torch.empty(B, dtype=torch.float64, device="cuda"); gd = torch.empty((d, B * q), dtype=torch.float64, device="cuda")
+            _lib.check(_lib.load().dk_qei_value_grad_dev(h.ptr, C.c_void_p(xd.data_ptr()), B, q, float(plugin), _type_id(type), 1,
+                                                         C.c_void_p(vd.data_ptr()), C.c_void_p(gd.data_ptr()), None),
+                       "dk_qei_value_grad_dev")
+            torch.cuda.synchronize()
+            out = vd.cpu().numpy()
+            envir.update({"qEI.x": rows.copy(), "qEI.args": (float(plugin), type, q),
+                          "qEI.grad": np.ascontiguousarray(gd.cpu().numpy().T).reshape(B, q, d)})
+        return float(out[0]) if single else out
     _lib.check(_lib.load().dk_qei(h.ptr, _vp(rows), B, q, float(plugin), _type_id(type), int(bool(minimization)),
                                   _vp(out)), "dk_qei")
     return float(out[0]) if single else out
@@ -293,6 +309,13 @@ def AKG(x, model: KM, new_noise_var=0.0, type="UK", envir=None, device=0):
     N = x.shape[0]
     out = np.empty(N)
     h = model.handle(device)
+    if envir is not None:
+        # AKG(x, envir) ... AKG.grad(x, envir) (R/AKG.R:221-228 stores its intermediate terms for R/AKG.grad.R:84-94): the
+        # gradient kernel returns the value too, so one launch serves both calls; the gradient waits in envir
+        grad = np.empty((N, model.d), order="F")
+        _lib.check(_lib.load().dk_akg_grad(h.ptr, _vp(x), N, float(new_noise_var), _type_id(type), _vp(grad), _vp(out)), "dk_akg_grad")
+        envir.update({"AKG.x": np.array(x, copy=True), "AKG.args": (float(new_noise_var), type), "AKG.grad": grad})
+        return float(out[0]) if single else out
     _lib.check(_lib.load().dk_akg(h.ptr, _vp(x), N, float(new_noise_var), _type_id(type), _vp(out)), "dk_akg")
     return float(out[0]) if single else out
 
@@ -359,6 +382,10 @@ def qEI_grad(x, model: KM, plugin=None, type="UK", minimization=True, fastComput
         g = np.asarray(EI_grad(x[:, 0, :], model, plugin=plugin, type=type, device=device)).reshape(B, 1, d)
         return g[0] if single else g
     rows = np.asfortranarray(x.reshape(B * q, d))
+    if (envir is not None and minimization and "qEI.grad" in envir and envir.get("qEI.args") == (float(plugin), type, q)
+            and np.array_equal(envir["qEI.x"], rows)):
+        g = envir["qEI.grad"]                # left there by qEI(x, envir) at this very x
+        return g[0] if single else g
     out = np.empty((B * q, d), order="F")
     h = model.handle(device)
     _lib.check(_lib.load().dk_qei_grad(h.ptr, _vp(rows), B, q, float(plugin), _type_id(type), int(bool(minimization)),
@@ -433,10 +460,15 @@ def max_qEI(model: KM, npoints, lower, upper, crit="exact", minimization=True, o
 
 
 def AKG_grad(x, model: KM, new_noise_var=0.0, type="UK", envir=None, device=0):
-    """Gradient of AKG, R/AKG.grad.R:65-281 (envir = NULL path): length d for one point, N x d for a matrix."""
+    """Gradient of AKG, R/AKG.grad.R:65-281: length d for one point, N x d for a matrix.  With the ``envir`` that
+    ``AKG(x, envir)`` filled at the same x the stored gradient is returned (the reference reuses its stored terms)."""
     single = np.asarray(x).ndim <= 1
     x = _as_candidates(x, model.d)
     N = x.shape[0]
+    if (envir is not None and "AKG.grad" in envir and envir.get("AKG.args") == (float(new_noise_var), type)
+            and np.array_equal(envir["AKG.x"], x)):
+        grad = envir["AKG.grad"]             # left there by AKG(x, envir) at this very x
+        return grad[0].copy() if single else grad
     grad = np.empty((N, model.d), order="F")
     h = model.handle(device)
     _lib.check(_lib.load().dk_akg_grad(h.ptr, _vp(x), N, float(new_noise_var), _type_id(type), _vp(grad), None), "dk_akg_grad")

@@ -214,9 +214,8 @@ int evaluate(dk_model* m, const dk_crit_spec& c, int q, const double* d_x, int64
     case DK_CRIT_EQI: return dk_eqi_grad_dev(m, d_x, rows, c.plugin, c.new_noise_var, c.qnorm_beta, c.type, d_grad, d_val, st);
     case DK_CRIT_AKG: return dk_akg_grad_dev(m, d_x, rows, c.new_noise_var, c.type, d_grad, d_val, st);
     case DK_CRIT_QEI: {
-      int rc = dk_qei_dev(m, d_x, rows / q, q, c.plugin, c.type, c.minimization, d_val, st);
-      if (rc) return rc;
-      return dk_qei_grad_dev(m, d_x, rows / q, q, c.plugin, c.type, c.minimization, d_grad, st);
+      // value and gradient from one pass over the model (the envir reuse of R/max_qEI.R:205-222's optim loop)
+      return dk_qei_value_grad_dev(m, d_x, rows / q, q, c.plugin, c.type, c.minimization, d_val, d_grad, st);
     }
   }
   return fail(DK_ERR_ARG, "criterion %d has no gradient entry point", c.criterion);

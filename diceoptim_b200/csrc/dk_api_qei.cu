@@ -115,8 +115,43 @@ extern "C" int dk_qei(dk_model* m, const double* x, int64_t B, int q, double plu
   return host_qei(m, x, B * q, 0, B, q, plugin, type, minimization, out, nullptr);
 }
 
+namespace {
+// the value CDF kernels of dk_qei_dev on moments that are already in m->d_mom
+int launch_qei_value_cdf(dk_model* m, int64_t B, int q, double plugin, int minimization, double* d_out, cudaStream_t st) {
+  if (q > DK_MAX_Q) {
+    k_qei_cdf_gen<<<(unsigned)std::min<int64_t>(B, 8 * (int64_t)m->num_sms), CDF_THREADS, 0, st>>>(m->d_mom, B, q, plugin,
+                                                                                                minimization, d_out);
+  } else {
+    static const int64_t warp_below = [] { const char* e = std::getenv("DK_QEI_WARP_BELOW"); return e ? std::atoll(e) : (int64_t)12288; }();
+    if (B < warp_below) k_qei_cdf_warp<<<(unsigned)((B + 3) / 4), 128, 0, st>>>(m->d_mom, B, q, plugin, minimization, d_out);
+    else k_qei_cdf<<<(unsigned)((B * 4 + 127) / 128), 128, 0, st>>>(m->d_mom, B, q, plugin, minimization, d_out);
+  }
+  m->launches += 1;
+  DK_CUDA_TRY(cudaGetLastError());
+  return DK_OK;
+}
+
+int qei_grad_impl(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type, int minimization, double* d_val,
+                  double* d_grad, void* stream);
+}  // namespace
+
 extern "C" int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type,
                                int minimization, double* d_grad, void* stream) {
+  return qei_grad_impl(m, d_x, B, q, plugin, type, minimization, nullptr, d_grad, stream);
+}
+
+/* qEI and qEI.grad of the same batches from ONE pass over the model: what qEI(x, envir) followed by qEI.grad(x, envir) saves
+ * in the reference (R/qEI.R:190-198 stores the kriging mean / covariance and the CDF terms, R/qEI.grad.R:299-316 reads them).
+ * The value is taken at x itself, as the gradient is (dk_qei rounds x to 8 digits first, R/qEI.R:126-128). */
+extern "C" int dk_qei_value_grad_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type,
+                                     int minimization, double* d_val, double* d_grad, void* stream) {
+  if (!d_val) return fail(DK_ERR_ARG, "d_val is NULL");
+  return qei_grad_impl(m, d_x, B, q, plugin, type, minimization, d_val, d_grad, stream);
+}
+
+namespace {
+int qei_grad_impl(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type, int minimization, double* d_val,
+                  double* d_grad, void* stream) {
   int rc = check_call(m, d_x, B);
   if (rc) return rc;
   if (q < 2 || q > DK_MAX_Q_LATTICE)
@@ -151,6 +186,7 @@ extern "C" int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q,
         m->d_deriv);
     DK_CUDA_TRY(cudaGetLastError());
     if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev_mid, st));
+    if (d_val && (rc = launch_qei_value_cdf(m, B, q, plugin, minimization, d_val, st))) return rc;
     double* d_partial = m->d_deriv + deriv_part;
     k_qei_grad_cdf_gen<<<(unsigned)std::min<int64_t>(B * q, 8 * (int64_t)m->num_sms), CDF_THREADS, sizeof(GenGradShared), st>>>(
         m->d_mom, m->d_deriv, B, q, m->d, plugin, minimization, m->dm.sd2, d_partial);
@@ -181,6 +217,7 @@ extern "C" int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q,
                                                   m->d_cscratch, m->scratch_doubles_per_cta, m->d_aux, m->d_mom, m->d_deriv);
   DK_CUDA_TRY(cudaGetLastError());
   if (m->timing) DK_CUDA_TRY(cudaEventRecord(m->ev_mid, st));
+  if (d_val && (rc = launch_qei_value_cdf(m, B, q, plugin, minimization, d_val, st))) return rc;
   const int64_t threads = B * 4;
   k_qei_grad_cdf<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(m->d_mom, m->d_deriv, B, q, m->d, plugin, minimization,
                                                                    m->dm.sd2, d_grad);
@@ -189,6 +226,7 @@ extern "C" int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q,
   DK_CUDA_TRY(cudaGetLastError());
   return DK_OK;
 }
+}  // namespace
 
 extern "C" int dk_qei_grad(dk_model* m, const double* x, int64_t B, int q, double plugin, int type, int minimization,
                            double* out_grad) {

@@ -270,6 +270,12 @@ int dk_qei_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, 
 int dk_qei_grad(dk_model* m, const double* x, int64_t B, int q, double plugin, int type, int minimization, double* out_grad);
 int dk_qei_grad_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type, int minimization,
                     double* d_grad, void* stream);
+/* qEI and qEI.grad of the same batches from ONE pass over the model — what qEI(x, envir) followed by qEI.grad(x, envir) saves in
+ * the reference (R/qEI.R:190-198 stores the kriging mean / covariance and the CDF terms, R/qEI.grad.R:299-316 reads them back;
+ * the optim loop of R/max_qEI.R:205-222 relies on it).  d_val[B], d_grad as dk_qei_grad_dev.  The value is taken at x itself,
+ * as the gradient is (dk_qei rounds x to 8 digits first, R/qEI.R:126-128). */
+int dk_qei_value_grad_dev(dk_model* m, const double* d_x, int64_t B, int q, double plugin, int type, int minimization,
+                          double* d_val, double* d_grad, void* stream);
 /* pmnorm(h_b, varcov = S_b) for B independent q-variate problems (q <= DK_MAX_Q_LATTICE): the device CDFs behind
  * dk_qei, exposed for parity tests against mnormt-class references.  h: B x q, S: B x q x q, row-major, host. */
 int dk_mvn_cdf(int q, int64_t B, const double* h, const double* S, double* out);

@@ -135,3 +135,18 @@ def test_aei_grad_and_eqi_grad_match_oracle(gpu_lib, trend, type):
         assert np.max(np.abs(ga[j] - ra)) <= 1e-10 * np.max(np.abs(ra)) + 1e-14
         assert np.max(np.abs(ge[j] - re)) <= 1e-10 * np.max(np.abs(re)) + 1e-14
     km.release()
+
+
+def test_akg_envir_reuse(gpu_lib):
+    """AKG(x, envir) then AKG.grad(x, envir) (R/AKG.R:221-228, R/AKG.grad.R:84-94): one launch serves both calls."""
+    from diceoptim_b200 import AKG, AKG_grad
+    km = small_model("matern5_2", "const", n=50, d=2, seed=12, noise_var=0.05)
+    x = np.random.default_rng(2).random((6, 2))
+    env = {}
+    v = AKG(x, km, new_noise_var=0.05, envir=env)
+    g = AKG_grad(x, km, new_noise_var=0.05, envir=env)
+    assert g is env["AKG.grad"]
+    assert np.array_equal(g, AKG_grad(x, km, new_noise_var=0.05))
+    assert np.allclose(v, AKG(x, km, new_noise_var=0.05), rtol=1e-12, atol=1e-15)
+    assert AKG_grad(x[:3], km, new_noise_var=0.05, envir=env) is not env["AKG.grad"]
+    km.release()

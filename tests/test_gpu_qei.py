@@ -133,6 +133,26 @@ def test_qei_grad_matches_oracle(gpu_lib, q, trend, type):
     km.release()
 
 
+@pytest.mark.parametrize("q", [3, 5])
+def test_qei_envir_reuse_gives_the_gradient_of_the_same_pass(gpu_lib, q):
+    """qEI(x, envir) then qEI.grad(x, envir) (R/qEI.R:190-198, R/qEI.grad.R:299-316): one pass over the model; the gradient
+    equals the separate call's bit for bit, the value is qEI at x itself (the separate call rounds x to 8 digits first)."""
+    from diceoptim_b200 import qEI, qEI_grad
+    km = small_model("matern5_2", "const", n=60, d=2, seed=17)
+    xb = np.random.default_rng(3).random((4, q, 2))
+    pl = float(np.median(km.y))
+    env = {}
+    v = qEI(xb, km, plugin=pl, envir=env)
+    g = qEI_grad(xb, km, plugin=pl, envir=env)
+    assert g is env["qEI.grad"]
+    assert np.array_equal(g, qEI_grad(xb, km, plugin=pl))
+    assert np.allclose(v, qEI(xb, km, plugin=pl), rtol=0, atol=1e-7)           # x moved by up to 5e-9 in the separate call
+    assert np.array_equal(qEI(xb, km, plugin=pl), qEI(np.round(xb, 8), km, plugin=pl, envir={}))   # same x -> same bits
+    g2 = qEI_grad(xb + 1e-3, km, plugin=pl, envir=env)                             # another x: computed, not reused
+    assert g2 is not env["qEI.grad"] and not np.array_equal(g2, g)
+    km.release()
+
+
 def test_qei_grad_guards(gpu_lib):
     """Zero matrix when a batch point duplicates the design (R/qEI.grad.R:293-295); q = 1 -> EI.grad."""
     from diceoptim_b200 import qEI_grad, EI_grad
