@@ -211,7 +211,8 @@ def test_qei_general_q_matches_oracle(gpu_lib, q, trend, type):
 def test_qei_grad_general_q_matches_oracle(gpu_lib, q, trend, type):
     """qEI.grad for q > 4 (csrc/dk_qei_grad_gen.cuh) against the oracle's restatement of R/qEI.grad.R:267-424, which evaluates
     its normal CDFs by the same rules (deterministic up to dimension 4, the fixed lattice above); the q - 3 .. q variate CDFs
-    of GPhi / HPhi / term B all take part.  1e-8 of the largest entry (sums of a few hundred CDF terms of both signs)."""
+    of GPhi / HPhi / term B all take part.  1e-9 of the largest entry (sums of a few hundred CDF terms of both signs; measured
+    5e-12 at cfg3's model, profiles/parity_r02.md)."""
     from diceoptim_b200 import qEI_grad
     from oracle import diceoptim as do
     km = small_model("matern5_2", trend, n=60, d=2, seed=80 + q, noise_var=0.02)
@@ -225,11 +226,11 @@ def test_qei_grad_general_q_matches_oracle(gpu_lib, q, trend, type):
     for b in range(B):
         ref = do.qEI_grad(xb[b], ko, plugin=plugin, type=type, fastCompute=False)
         assert np.max(np.abs(ref)) > 1e-6
-        assert np.max(np.abs(got[b] - ref)) <= 1e-8 * np.max(np.abs(ref)), (b, np.max(np.abs(got[b] - ref)), np.max(np.abs(ref)))
+        assert np.max(np.abs(got[b] - ref)) <= 1e-9 * np.max(np.abs(ref)), (b, np.max(np.abs(got[b] - ref)), np.max(np.abs(ref)))
     if q == 5:
         gm = qEI_grad(xb[:1], km, plugin=-plugin, type=type, minimization=False)
         ref = do.qEI_grad(xb[0], ko, plugin=-plugin, type=type, minimization=False, fastCompute=False)
-        assert np.max(np.abs(gm[0] - ref)) <= 1e-8 * np.max(np.abs(ref))
+        assert np.max(np.abs(gm[0] - ref)) <= 1e-9 * np.max(np.abs(ref))
         xd = xb[:1].copy(); xd[0, 3] = km.X[7]                     # a duplicate of the design -> zero matrix
         assert np.all(qEI_grad(xd, km, plugin=plugin, type=type) == 0.0)
     km.release()

@@ -18,9 +18,11 @@ def main():
     t0 = time.time()
     for name, fn in [
         ("cfg1", lambda: pc.ei_family("cfg1_branin2_n20", N=None, n_hi=64, n_grad_hi=64, full_grid=True)),
-        ("cfg2", lambda: pc.ei_family("cfg2_hartman4_n200", N=4096, n_hi=64, n_grad_hi=32)),
+        ("cfg2", lambda: pc.ei_family("cfg2_hartman4_n200", N=8192, n_hi=64, n_grad_hi=32)),   # > 4736: the single-block kernel
         ("cfg3p", lambda: pc.ei_family("cfg3_rosenbrock4_n500", N=2048, n_hi=48, n_grad_hi=16)),
         ("cfg3", lambda: pc.qei_family(B=256)),
+        ("cfg3_q5", lambda: pc.qei_family(B=32, q=5)),            # the general-q kernels (fixed-lattice CDFs on both sides)
+        ("cfg3_q7", lambda: pc.qei_family(B=16, q=7)),
         ("cfg4", lambda: pc.ei_family("cfg4_sphere10_n2000", N=2048, n_hi=32, n_grad_hi=8)),
         ("cfg5_noise", lambda: pc.akg_family(noise_kind="noise_var", N=256, n_hi=32)),
         ("cfg5_nugget", lambda: pc.akg_family(noise_kind="nugget", N=256, n_hi=32)),
