@@ -71,6 +71,33 @@ __device__ __forceinline__ double dlogk_dev(const DevModel& M, int k, double dif
   }
 }
 
+// Does candidate column c equal a design row after rounding to 8 digits (R/qEI.R:124-128)?  Rows slice, slice + 4, ... of the
+// rounded design (Xrm_r8, rounded once per model); a row is dismissed on its first coordinate.  Eight rows' first coordinates
+// are loaded together: one dependent L2 load per row made this scan a fifth of k_qei_moments' warp samples at n = 500.
+__device__ __forceinline__ bool design_duplicate(const DevModel& M, const double* __restrict__ xs, int c, int slice) {
+  const int n = M.n, d = M.d;
+  const double x0 = round8(xs[c]);
+  bool dup = false;
+#pragma unroll 1
+  for (int i0 = slice; i0 < n && !dup; i0 += 32) {
+    double f[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+      const int i = i0 + 4 * u;
+      f[u] = (i < n) ? __ldg(M.Xrm_r8 + (size_t)i * d) : nan("");
+    }
+#pragma unroll
+    for (int u = 0; u < 8; u++)
+      if (f[u] == x0) {
+        const int i = i0 + 4 * u;
+        bool same = true;
+        for (int k = 1; k < d && same; k++) same = (__ldg(M.Xrm_r8 + (size_t)i * d + k) == round8(xs[k * BN + c]));
+        dup = dup || same;
+      }
+  }
+  return dup;
+}
+
 // One tile of 16 batches: forward solve with Gram accumulation, then mu / Sigma / duplicate mask to
 // `moments`.  When `coef` is non-NULL it also receives r = tuuinv (F.newdata - v'M)' per column (rows
 // 2.. of the coefficient block, as the backward solve of the gradient kernels expects).
@@ -166,14 +193,7 @@ __device__ __forceinline__ void qei_tile_moments(const DevModel& M, int type, in
   {
     // 4 threads per candidate scan the design for a row equal after rounding to 8 digits
     const int c = tid & (BN - 1), slice = tid >> 6;
-    bool dup = false;
-    const double x0 = round8(xs[c]);   // the design is rounded once per model (Xrm_r8); a row is dismissed on its first coordinate
-    for (int i = slice; i < n && !dup; i += 4) {
-      bool same = (__ldg(M.Xrm_r8 + (size_t)i * d) == x0);
-      for (int k = 1; k < d && same; k++) same = (__ldg(M.Xrm_r8 + (size_t)i * d + k) == round8(xs[k * BN + c]));
-      dup = same;
-    }
-    if (dup) atomicOr(&dupflag[c], 1);
+    if (design_duplicate(M, xs, c, slice)) atomicOr(&dupflag[c], 1);
   }
   if (tid < BN) {
     const int c = tid;

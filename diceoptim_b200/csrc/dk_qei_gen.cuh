@@ -152,14 +152,7 @@ k_qei_moments_gen(const DevModel M, int type, int q, const double* __restrict__ 
     __syncthreads();
     {
       const int c = tid & (BN - 1), slice = tid >> 6;
-      bool dup = false;
-      const double x0 = xs[c];
-      for (int i = slice; i < n && !dup; i += 4) {
-        bool same = (__ldg(M.Xrm_r8 + (size_t)i * d) == x0);
-        for (int k = 1; k < d && same; k++) same = (__ldg(M.Xrm_r8 + (size_t)i * d + k) == xs[k * BN + c]);
-        dup = same;
-      }
-      if (dup) atomicOr(&dupflag[c], 1);
+      if (design_duplicate(M, xs, c, slice)) atomicOr(&dupflag[c], 1);   // xs is rounded already: round8 is idempotent
     }
     if (tid < BN) {
       const int c = tid;

@@ -99,14 +99,7 @@ k_qei_grad_moments_gen(const DevModel M, int type, int q, const double* __restri
     __syncthreads();
     {
       const int c = tid & (BN - 1), slice = tid >> 6;
-      bool dup = false;
-      const double x0 = round8(xs[c]);
-      for (int i = slice; i < n && !dup; i += 4) {
-        bool same = (__ldg(M.Xrm_r8 + (size_t)i * d) == x0);
-        for (int k = 1; k < d && same; k++) same = (__ldg(M.Xrm_r8 + (size_t)i * d + k) == round8(xs[k * BN + c]));
-        dup = same;
-      }
-      if (dup) atomicOr(&dupflag[c], 1);
+      if (design_duplicate(M, xs, c, slice)) atomicOr(&dupflag[c], 1);
     }
     if (tid < BN) {
       const int c = tid;
