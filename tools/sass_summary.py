@@ -6,7 +6,8 @@ so = os.path.join(ROOT, "diceoptim_b200", "libdk_b200.so")
 txt = subprocess.run(["cuobjdump", "-sass", so], capture_output=True, text=True).stdout
 funcs = re.split(r"\n\s*Function : ", txt)[1:]
 HOT = ["k_predict_fused_tmaILi3ELb0", "k_predict_narrow", "k_grad_fusedILi3", "k_grad_narrow", "k_akg_fusedILb0", "k_qei_moments", "k_qei_cdfE",
-       "k_qei_cdf_gen", "k_qei_moments_gen", "k_topk_pass", "k_gen_uniform", "k_polish_prepare"]
+       "k_qei_cdf_gen", "k_qei_moments_gen", "k_topk_pass", "k_gen_uniform", "k_polish_prepare", "k_predict_small", "k_qei_grad_moments_gen",
+       "k_qei_grad_cdf_gen"]
 pat = {"DMMA": r"\bDMMA", "UBLKCP": r"\bUBLKCP", "SYNCS": r"\bSYNCS", "LDS.128": r"\bLDS\.128", "BAR.SYNC": r"\bBAR\.SYNC", "DFMA": r"\bDFMA",
        "DADD/DMUL": r"\bD(ADD|MUL)", "MUFU": r"\bMUFU", "UTMALDG/UTC*MMA": r"\b(UTMALDG|UTC\w*MMA|LDTM|STTM)"}
 print("# SASS evidence, round 2 (`cuobjdump -sass diceoptim_b200/libdk_b200.so`, sm_100a)\n")
