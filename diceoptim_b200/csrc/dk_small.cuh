@@ -33,7 +33,7 @@ constexpr int SMALL_MAX_PAD = 256;
 constexpr int SMALL_MAX_STAGES = 8;
 constexpr int SMALL_SMEM_MAX = 232448;  // 227 KB of dynamic shared memory per CTA
 
-// Shared-memory map, sized for the model: what the fixed parts leave goes to the ring (cfg2: 7 stages).  Designs whose
+// Shared-memory map, sized for the model: what the fixed parts leave goes to the ring (cfg2: 6 stages).  Designs whose
 // rows x d leave fewer than 3 stages stay on the blocked kernel.
 __host__ inline SmallLayout small_layout(int n, int n_pad, int d, int p) {
   SmallLayout L{};
