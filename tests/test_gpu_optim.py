@@ -55,9 +55,10 @@ def test_max_qei_batched_matches_sequential(gpu_lib):
     b = max_qEI(km, 2, lo, up, optimcontrol={"parinit": par0, "maxit": 60, "optimizer": "scipy"})
     assert a["par"].shape == (2, 2) and np.all(a["par"] >= lo) and np.all(a["par"] <= up)
     assert a["value"] >= b["value"] * (1 - 1e-4), (a["value"], b["value"])
-    assert abs(qEI(a["par"], km) - a["value"]) <= 1e-10 * abs(a["value"]) + 1e-15
+    # the device polish reports qEI at x itself; qEI() rounds x to 8 digits first (R/qEI.R:126-128)
+    assert abs(qEI(a["par"], km) - a["value"]) <= 1e-6 * abs(a["value"]) + 1e-12
     start_vals = qEI(par0, km)
-    assert a["value"] >= np.max(start_vals)
+    assert a["value"] >= np.max(start_vals) * (1 - 1e-6)
     km.release()
 
 
@@ -160,14 +161,15 @@ def test_device_polish_quantile_and_qei(gpu_lib):
     pl = float(np.median(km.y))
     r2 = device_polish(km, "qEI", xb.reshape(5, 6), lo, up, q=3, plugin=pl, maxit=40)
     v0 = qEI(xb, km, plugin=pl)
-    assert np.all(r2["f"] >= v0 * (1 - 1e-12))
-    assert np.allclose(qEI(r2["x"].reshape(5, 3, 2), km, plugin=pl), r2["f"], rtol=1e-10)
+    assert np.all(r2["f"] >= v0 * (1 - 1e-6))
+    # dk_polish takes qEI at x itself (one pass with the gradient), dk_qei at round(x, 8) as R/qEI.R:126-128 does
+    assert np.allclose(qEI(r2["x"].reshape(5, 3, 2), km, plugin=pl), r2["f"], rtol=1e-6, atol=1e-9)
     # q = 5: value and gradient from the general-q kernels (lattice CDFs)
     xb5 = np.random.default_rng(7).random((3, 5, 2))
     r5 = device_polish(km, "qEI", xb5.reshape(3, 10), lo, up, q=5, plugin=pl, maxit=15)
     v5 = qEI(xb5, km, plugin=pl)
-    assert np.all(r5["f"] >= v5 * (1 - 1e-12)) and np.any(r5["f"] > v5 * 1.01)
-    assert np.allclose(qEI(r5["x"].reshape(3, 5, 2), km, plugin=pl), r5["f"], rtol=1e-10)
+    assert np.all(r5["f"] >= v5 * (1 - 1e-6)) and np.any(r5["f"] > v5 * 1.01)
+    assert np.allclose(qEI(r5["x"].reshape(3, 5, 2), km, plugin=pl), r5["f"], rtol=1e-6, atol=1e-9)
     km.release()
 
 
