@@ -18,7 +18,8 @@
 // per tile 11.2 / 3.7; warp-specialised (8 producer warps generating the covariance of the next 32 candidates while 8
 // consumer warps multiply) 13.9 / 3.0 — eight warps with eight accumulators each do not keep the DMMA pipe busy; both
 // row blocks advancing together (16 accumulators per warp, the B fragments read once) 16.2 / 3.2: over the 128-register
-// limit of a 512-thread CTA.
+// limit of a 512-thread CTA; this kernel as two 256-thread CTAs of 32 candidates per SM (3-stage ring each) 13.2 / 2.5:
+// twice the factor-tile traffic from L2 (3.2 TB/s) costs more than the overlap of the two CTAs' phases gains.
 // The explicit inverse of the whole factor is less accurate than the blocked substitution on ill-conditioned factors
 // (the off-diagonal block of the inverse cancels against the diagonal one), so dk_model_create enables this kernel only
 // when a probe against long-double substitution shows it loses nothing (small_inverse_is_accurate, dk_api.cu).
