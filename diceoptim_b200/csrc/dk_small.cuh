@@ -246,9 +246,13 @@ k_predict_small(const DevModel M, const CritParams P, const SmallLayout L, const
   int c_slot = 0; unsigned c_par = 0;                // every warp: next slot / parity to consume
   auto issue = [&]() {   // thread 0 only
     mbar_wait_guarded(&empty[i_slot], i_par ^ 1);
+#ifdef DK_X_SMALL_NOLOAD   // what-if build (timing only): the factor tiles are never fetched
+    mbar_arrive(&full[i_slot]);
+#else
     mbar_arrive_expect_tx(&full[i_slot], A_TILE * 8);
     const double* src = M.tiles_small + (i_pos < nk0 ? (size_t)i_pos : small_tile_base(1) + (size_t)(i_pos - nk0)) * A_TILE;
     bulk_load(ring + (size_t)i_slot * A_TILE, src, A_TILE * 8, &full[i_slot]);
+#endif
     if (++i_pos == per_tile) i_pos = 0;
     if (++i_slot == nstages) { i_slot = 0; i_par ^= 1; }
     issued++;
