@@ -56,7 +56,8 @@ __host__ __device__ __forceinline__ size_t tile_base(int I) { return (size_t)4 *
 // Shared-memory map of k_predict_small (dk_small.cuh), sized for the model by small_layout()
 struct SmallLayout {
   int off_aug, off_cand, off_xs, off_rbuf, off_ring;   // bytes; barriers at 0, s2acc at 256
-  int stages;                                          // ring depth (3 .. 8); 0: the design does not fit
+  int stages;                                          // ring depth (2 .. 8); 0: the design does not fit
+  int tps;                                             // factor tiles (k-chunks) per ring stage, 1 .. 4
   int total;                                           // bytes of dynamic shared memory
 };
 

@@ -32,6 +32,7 @@ constexpr int SBN = BN;                 // 64 candidates per tile; B tiles in th
 constexpr int NTS = 512;                // 16 warps: 4 (rows) x 4 (columns), warp tile 32 x 16
 constexpr int SMALL_MAX_PAD = 256;
 constexpr int SMALL_MAX_STAGES = 8;
+constexpr int SMALL_MAX_TPS = 4;        // most k-chunks (16 KB factor tiles) per ring stage
 constexpr int SMALL_SMEM_MAX = 232448;  // 227 KB of dynamic shared memory per CTA
 
 // Shared-memory map, sized for the model: what the fixed parts leave goes to the ring (cfg2: 6 stages).  Designs whose
@@ -45,10 +46,20 @@ __host__ inline SmallLayout small_layout(int n, int n_pad, int d, int p) {
   L.off_xs = L.off_cand + 4 * d * SBN * 8;   // [2 buffers][plain | scaled by w][d][64]
   L.off_rbuf = L.off_xs + n_pad * d * 8;
   L.off_ring = L.off_rbuf + nchunks * B_TILE * 8;
-  const int room = (SMALL_SMEM_MAX - L.off_ring) / (A_TILE * 8);
-  if (L.off_ring > SMALL_SMEM_MAX || room < 3) return L;
-  L.stages = room < SMALL_MAX_STAGES ? room : SMALL_MAX_STAGES;
-  L.total = L.off_ring + L.stages * A_TILE * 8;
+  // several k-chunks per ring stage: every stage costs each warp two mbarrier hand-shakes, and the factor tiles of a row
+  // block are consecutive in memory, so a stage is still ONE bulk copy.  The most chunks per stage that leave two stages
+  // (the copies themselves are cheap: a build that never fetches them is 1.4 % faster); DK_SMALL_TPS overrides (A/B runs).
+  if (L.off_ring > SMALL_SMEM_MAX) return L;
+  static const int forced = [] { const char* e = std::getenv("DK_SMALL_TPS"); return e ? std::atoi(e) : 0; }();
+  for (int tps = SMALL_MAX_TPS; tps >= 1; tps--) {
+    if (forced >= 1 && forced <= SMALL_MAX_TPS && tps != forced) continue;
+    const int room = (SMALL_SMEM_MAX - L.off_ring) / (tps * A_TILE * 8);
+    if (room < 2) continue;
+    L.tps = tps;
+    L.stages = room < SMALL_MAX_STAGES ? room : SMALL_MAX_STAGES;
+    L.total = L.off_ring + L.stages * tps * A_TILE * 8;
+    break;
+  }
   return L;
 }
 // first tile of row block rb in the small tile array: row block rb' < rb holds 8 (rb' + 1) tiles
@@ -237,8 +248,12 @@ k_predict_small(const DevModel M, const CritParams P, const SmallLayout L, const
   load_candidates(blockIdx.x, cand);
   __syncthreads();
 
-  // factor-tile stream: row block 0's nk0 chunks, then row block 1's, the same list for every candidate tile
-  const int nk0 = min(CHUNKS_PER_BLOCK, nchunks), per_tile = nk0 + (nrb > 1 ? nchunks : 0);
+  // factor-tile stream: row block 0's nk0 chunks, then row block 1's, L.tps chunks (consecutive tiles, one bulk copy) per
+  // ring stage; the same list of stages for every candidate tile
+  const int nk0 = min(CHUNKS_PER_BLOCK, nchunks);
+  const int tps = L.tps;
+  const int ns0 = (nk0 + tps - 1) / tps, ns1 = nrb > 1 ? (nchunks + tps - 1) / tps : 0;
+  const int per_tile = ns0 + ns1;
   const int64_t my_tiles = (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
   const int64_t total = my_tiles * per_tile;
   int64_t issued = 0;
@@ -246,12 +261,14 @@ k_predict_small(const DevModel M, const CritParams P, const SmallLayout L, const
   int c_slot = 0; unsigned c_par = 0;                // every warp: next slot / parity to consume
   auto issue = [&]() {   // thread 0 only
     mbar_wait_guarded(&empty[i_slot], i_par ^ 1);
+    const int rb = i_pos < ns0 ? 0 : 1, st = i_pos - (rb ? ns0 : 0), kc = st * tps;
+    const int ntl = min(tps, (rb ? nchunks : nk0) - kc);
 #ifdef DK_X_SMALL_NOLOAD   // what-if build (timing only): the factor tiles are never fetched
     mbar_arrive(&full[i_slot]);
 #else
-    mbar_arrive_expect_tx(&full[i_slot], A_TILE * 8);
-    const double* src = M.tiles_small + (i_pos < nk0 ? (size_t)i_pos : small_tile_base(1) + (size_t)(i_pos - nk0)) * A_TILE;
-    bulk_load(ring + (size_t)i_slot * A_TILE, src, A_TILE * 8, &full[i_slot]);
+    mbar_arrive_expect_tx(&full[i_slot], ntl * A_TILE * 8);
+    const double* src = M.tiles_small + (small_tile_base(rb) + (size_t)kc) * A_TILE;
+    bulk_load(ring + (size_t)i_slot * tps * A_TILE, src, ntl * A_TILE * 8, &full[i_slot]);
 #endif
     if (++i_pos == per_tile) i_pos = 0;
     if (++i_slot == nstages) { i_slot = 0; i_par ^= 1; }
@@ -268,7 +285,12 @@ k_predict_small(const DevModel M, const CritParams P, const SmallLayout L, const
     // ---- epilogue of the previous tile (warps 0, 1) beside the covariance tile of this one ----
     if (prev >= 0 && tid < SBN && prev * SBN + tid < N)
       small_epilogue(M, P, cand + (size_t)((it - 1) & 1) * 2 * d * SBN, aug, s2acc, tid, prev * SBN + tid, out_main, out_mean, out_sd);
-    for (int u = NTS / 32 - 1 - warp; u < nunits; u += NTS / 32) covgen_small_any(M, Xs, xs + d * SBN, Rbuf, u >> 1, u & 1, lane);
+#ifndef DK_X_SMALL_NOCOV   // what-if build (timing only): the covariance tile is never written
+    for (int u = NTS / 32 - 1 - warp; u < nunits; u += NTS / 32)
+#else
+    for (int u = nunits; u < nunits; u++)
+#endif
+      covgen_small_any(M, Xs, xs + d * SBN, Rbuf, u >> 1, u & 1, lane);
     __syncthreads();   // Rbuf complete; aug / s2acc free
     double s2p[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
     // ---- V = inv(L_aug) c, row block by row block, all stages on one pipeline ----
@@ -282,12 +304,21 @@ k_predict_small(const DevModel M, const CritParams P, const SmallLayout L, const
       const int nk = rb == 0 ? nk0 : nchunks;
       const int plo = CHUNKS_PER_BLOCK * rb + 2 * wm, phi = plo + 1;   // this warp's global pair indices
 #pragma unroll 1
-      for (int kc = 0; kc < nk; kc++) {
-        if (tid == 0 && issued < total) issue();   // nstages - 1 tiles ahead: the slot this warp consumed one step ago
+      for (int kc0 = 0; kc0 < nk; kc0 += tps) {
+        if (tid == 0 && issued < total) issue();   // nstages - 1 stages ahead: the slot this warp consumed one step ago
         mbar_wait_guarded(&full[c_slot], c_par);
-        // the inverse is lower triangular: pair q needs chunks 0..q; pairs made of padding take no part
-        const bool lo = kc <= plo && plo < live16, hi = kc <= phi && phi < live16;
-        if (lo || hi) mma_stage_small(acc, ring + (size_t)c_slot * A_TILE, Rbuf + (size_t)kc * B_TILE, wm, wn, lane, lo, hi);
+#pragma unroll 1
+        for (int t = 0; t < tps; t++) {
+          const int kc = kc0 + t;
+          // the inverse is lower triangular: pair q needs chunks 0..q; pairs made of padding take no part
+          const bool lo = kc < nk && kc <= plo && plo < live16, hi = kc < nk && kc <= phi && phi < live16;
+#ifndef DK_X_SMALL_NOMMA   // what-if build (timing only): no DMMA work
+          if (lo || hi)
+#else
+          if (false)
+#endif
+            mma_stage_small(acc, ring + ((size_t)c_slot * tps + t) * A_TILE, Rbuf + (size_t)kc * B_TILE, wm, wn, lane, lo, hi);
+        }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[c_slot]);
         if (++c_slot == nstages) { c_slot = 0; c_par ^= 1; }
@@ -316,6 +347,7 @@ k_predict_small(const DevModel M, const CritParams P, const SmallLayout L, const
         v += __shfl_xor_sync(0xffffffffu, v, 16);
         if (lane < 4) s2acc[wm * SBN + 16 * wn + 8 * ni + 2 * lane + e] = v;
       }
+    // the next tile's candidates, into the buffer the epilogue above has finished with
     // the next tile's candidates, into the buffer the epilogue above has finished with
     if (tile + gridDim.x < ntiles) load_candidates(tile + gridDim.x, cand + (size_t)((it + 1) & 1) * 2 * d * SBN);
     __syncthreads();   // aug / s2acc / candidates visible; every warp is done with Rbuf
