@@ -19,7 +19,10 @@
 // consumer warps multiply) 13.9 / 3.0 — eight warps with eight accumulators each do not keep the DMMA pipe busy; both
 // row blocks advancing together (16 accumulators per warp, the B fragments read once) 16.2 / 3.2: over the 128-register
 // limit of a 512-thread CTA; this kernel as two 256-thread CTAs of 32 candidates per SM (3-stage ring each) 13.2 / 2.5:
-// twice the factor-tile traffic from L2 (3.2 TB/s) costs more than the overlap of the two CTAs' phases gains.
+// twice the factor-tile traffic from L2 (3.2 TB/s) costs more than the overlap of the two CTAs' phases gains; a dataflow
+// form without CTA barriers (per-chunk mbarriers, covariance units taken by idle warps) 14.2 / 2.3.  What did pay: several
+// k-chunks per ring stage (12.1 / 11.2 / 10.9 ms for one / two / three at cfg2): the hand-shakes, not the DMMA pipe or the
+// copies, were the cost (what-if builds -DDK_X_SMALL_NOMMA / NOCOV / NOLOAD: skeleton 2.2, covariance 3.3, DMMA 6.5 ms).
 // The explicit inverse of the whole factor is less accurate than the blocked substitution on ill-conditioned factors
 // (the off-diagonal block of the inverse cancels against the diagonal one), so dk_model_create enables this kernel only
 // when a probe against long-double substitution shows it loses nothing (small_inverse_is_accurate, dk_api.cu).
@@ -292,6 +295,18 @@ k_predict_small(const DevModel M, const CritParams P, const SmallLayout L, const
 #endif
       covgen_small_any(M, Xs, xs + d * SBN, Rbuf, u >> 1, u & 1, lane);
     __syncthreads();   // Rbuf complete; aug / s2acc free
+    // the next tile's candidates: asynchronous copies issued now land in shared memory while the GEMM runs (no registers held)
+    const bool have_next = tile + gridDim.x < ntiles;
+    double* xn = cand + (size_t)((it + 1) & 1) * 2 * d * SBN;
+    if (have_next) {
+      const int64_t c1 = (tile + gridDim.x) * SBN;
+      for (int i = tid; i < d * SBN; i += NTS) {
+        const int64_t g = c1 + (i % SBN);
+        const double* src = x + min(g, N - 1) + (int64_t)(i / SBN) * N;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(xn + i)), "l"(src) : "memory");
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    }
     double s2p[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
     // ---- V = inv(L_aug) c, row block by row block, all stages on one pipeline ----
 #pragma unroll 1
@@ -348,8 +363,11 @@ k_predict_small(const DevModel M, const CritParams P, const SmallLayout L, const
         if (lane < 4) s2acc[wm * SBN + 16 * wn + 8 * ni + 2 * lane + e] = v;
       }
     // the next tile's candidates, into the buffer the epilogue above has finished with
-    // the next tile's candidates, into the buffer the epilogue above has finished with
-    if (tile + gridDim.x < ntiles) load_candidates(tile + gridDim.x, cand + (size_t)((it + 1) & 1) * 2 * d * SBN);
+    // ... and their copy scaled by w_k, by the thread that fetched them
+    if (have_next) {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      for (int i = tid; i < d * SBN; i += NTS) xn[d * SBN + i] = __dmul_rn(xn[i], M.w[i / SBN]);   // never contracted into an FMA
+    }
     __syncthreads();   // aug / s2acc / candidates visible; every warp is done with Rbuf
   }
   if (prev >= 0 && tid < SBN && prev * SBN + tid < N)
