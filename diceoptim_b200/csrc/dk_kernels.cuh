@@ -304,30 +304,39 @@ __device__ __forceinline__ void solve_block_row(double (&acc)[4][4][2], const do
     // CTA meets, and only then does thread 0 start issuing bulk copies into / from those locations.
     asm volatile("fence.proxy.async;" ::: "memory");
     __syncthreads();
+    // DK_TPS k-chunks per ring stage (consecutive tiles of the factor and of the panel: still two bulk copies per stage)
+    // and STAGES / DK_TPS stages: fewer mbarrier hand-shakes per block row for the same shared memory
+#ifndef DK_TPS
+#define DK_TPS 2
+#endif
+    constexpr int TPS = DK_TPS, NS = STAGES / TPS;
+    static_assert(NS >= 2 && NS * TPS == STAGES && CHUNKS_PER_BLOCK % TPS == 0, "DK_TPS must divide the ring into >= 2 stages");
+    const int nst = nk / TPS;
     auto issue = [&](int idx) {  // thread 0 only
-      const unsigned gi = base + idx, slot = gi % STAGES, par = (gi / STAGES) & 1;
+      const unsigned gi = base + idx, slot = gi % NS, par = (gi / NS) & 1;
       mbar_wait(&empty[slot], par ^ 1);  // every warp has released the slot's previous contents
-      double* dst = ring + slot * (A_TILE + B_TILE);
-      mbar_arrive_expect_tx(&full[slot], STAGE_BYTES);
-      bulk_load(dst, Atiles + (size_t)idx * A_TILE, A_TILE * 8, &full[slot]);
-      bulk_load(dst + A_TILE, panel + (size_t)idx * B_TILE, B_TILE * 8, &full[slot]);
+      double* dst = ring + slot * TPS * (A_TILE + B_TILE);
+      mbar_arrive_expect_tx(&full[slot], TPS * STAGE_BYTES);
+      bulk_load(dst, Atiles + (size_t)idx * TPS * A_TILE, TPS * A_TILE * 8, &full[slot]);
+      bulk_load(dst + TPS * A_TILE, panel + (size_t)idx * TPS * B_TILE, TPS * B_TILE * 8, &full[slot]);
     };
     if (tid == 0)
-      for (int s = 0; s < STAGES - 1 && s < nk; s++) issue(s);
+      for (int s = 0; s < NS - 1 && s < nst; s++) issue(s);
 #pragma unroll 1
-    for (int kc = 0; kc < nk; kc++) {
-      if (tid == 0 && kc + STAGES - 1 < nk) issue(kc + STAGES - 1);
-      const unsigned gi = base + kc, slot = gi % STAGES, par = (gi / STAGES) & 1;
+    for (int kc = 0; kc < nst; kc++) {
+      if (tid == 0 && kc + NS - 1 < nst) issue(kc + NS - 1);
+      const unsigned gi = base + kc, slot = gi % NS, par = (gi / NS) & 1;
       mbar_wait(&full[slot], par);
-      const double* s = ring + slot * (A_TILE + B_TILE);
-      mma_stage_live(acc, s, s + A_TILE, wm, wn, lane, live16);
+      const double* s = ring + slot * TPS * (A_TILE + B_TILE);
+#pragma unroll
+      for (int t = 0; t < TPS; t++) mma_stage_live(acc, s + t * A_TILE, s + TPS * A_TILE + t * B_TILE, wm, wn, lane, live16);
       // this slot is refilled through the async proxy: order this lane's generic-proxy reads of it before that
       // (without this fence the refill raced the LDS reads: about one corrupted tile in a thousand)
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[slot]);
     }
-    *stage_base = base + nk;
+    *stage_base = base + nst;
     __syncthreads();  // every warp is done with the ring: region 0 can change role
     DK_MARK(2);
   } else {

@@ -334,6 +334,9 @@ k_predict_small(const DevModel M, const CritParams P, const SmallLayout L, const
 #endif
             mma_stage_small(acc, ring + ((size_t)c_slot * tps + t) * A_TILE, Rbuf + (size_t)kc * B_TILE, wm, wn, lane, lo, hi);
         }
+        // the slot is refilled through the async proxy: order this lane's generic-proxy reads of it before that (the blocked
+        // kernel's ring raced without this fence: about one corrupted tile in a thousand, dk_kernels.cuh)
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[c_slot]);
         if (++c_slot == nstages) { c_slot = 0; c_par ^= 1; }
