@@ -116,3 +116,28 @@ def test_small_kernel_cfg2_shape_and_other_criteria(gpu_lib):
     assert np.max(np.abs(q - qref)) <= 1e-10 * (np.max(np.abs(km.y)) + np.sqrt(km.covariance.sd2))
     assert np.array_equal(ei, EI(x, km))
     km.release()
+
+
+def test_small_kernel_follows_model_append(gpu_lib):
+    """dk_model_append re-forms the whole-factor inverse and its shared-memory map (refresh_small_tiles): a model grown in
+    place from 100 to 130 rows (one row block -> two) against a handle created for the grown model, both on large batches."""
+    from diceoptim_b200 import EI, synth
+    from diceoptim_b200.update import update_km
+    X = synth.lhs(100, 3, 7); y = np.sin(3 * X.sum(1)) + 0.3 * X[:, 1]
+    km = synth.make_km(X, y, "matern5_2", 0.5, float(np.var(y)), trend="const", noise_var=0.01)
+    x = np.random.default_rng(8).random((N_BIG, 3))
+    EI(x, km)                                                            # the handle exists before it grows
+    assert gpu_lib.dk_model_small_kernel(km.handle(0).ptr) == 1
+    pts = np.random.default_rng(9).random((30, 3))
+    fresh = km                                                           # same updates, handle built from scratch at the end
+    for i, xn in enumerate(pts):
+        fresh = update_km(fresh, xn, float(np.cos(i)), new_noise_var=0.01, reuse_handles=False)
+    cur = km
+    for i, xn in enumerate(pts):
+        cur = update_km(cur, xn, float(np.cos(i)), new_noise_var=0.01)
+    assert gpu_lib.dk_model_n(cur.handle(0).ptr) == 130 and gpu_lib.dk_model_small_kernel(cur.handle(0).ptr) == 1
+    pl = float(np.median(y))
+    a = EI(x, cur, plugin=pl)
+    b, _, _ = _ei(gpu_lib, fresh, x, 1, pl)                               # WIDE: the blocked kernel on a fresh handle
+    assert np.all(np.abs(a - b) <= 1e-9 * np.abs(b) + 1e-12 * b.max())
+    cur.release(); fresh.release()
