@@ -484,7 +484,10 @@ def main():
 
         # ---- cfg5: AKG + kriging.quantile, n = 5000, d = 20, noise.var and nugget ----
         full5 = args.cfg5_full or world == 8
-        N5T = 10_000_000 if full5 else (1 << 16) * world
+        # below the full configuration: a sample of four whole waves of the persistent grid per GPU (2 CTAs per SM x 64
+        # candidates), so that the rate is not that of a half-empty last wave (the full 10^7 is 66 waves per GPU)
+        wave = 2 * torch.cuda.get_device_properties(local).multi_processor_count * 64
+        N5T = 10_000_000 if full5 else 4 * wave * world
         a_lo, a_hi = parallel.shard_range(N5T, rank, world)
         N5 = a_hi - a_lo
         x5_host = candidate_rows(CFG5, a_lo, a_hi, 20)
